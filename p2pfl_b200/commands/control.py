@@ -1,0 +1,152 @@
+"""Handlers for the small control messages (SURVEY §2.6 catalogue).
+
+One class per wire command, same command strings as the reference so a mixed
+deployment interoperates: ``beat``, ``start_learning``, ``stop_learning``,
+``model_initialized``, ``vote_train_set``, ``models_aggregated``,
+``models_ready``, ``metrics``.
+"""
+
+from __future__ import annotations
+
+from typing import Any, Callable
+
+from p2pfl_b200.commands.command import Command
+from p2pfl_b200.management.logger import logger
+from p2pfl_b200.node_state import NodeState
+
+
+class HeartbeatCommand(Command):
+    """``beat [time]`` (reference: commands/heartbeat_command.py:39-52)."""
+
+    def __init__(self, heartbeater: Any) -> None:
+        self._hb = heartbeater
+
+    @staticmethod
+    def get_name() -> str:
+        return "beat"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        self._hb.beat(source, float(args[0]))
+
+
+class StartLearningCommand(Command):
+    """``start_learning [rounds, epochs]`` (reference: commands/start_learning_command.py:39-60)."""
+
+    def __init__(self, start_learning_fn: Callable[[int, int], None]) -> None:
+        self._start = start_learning_fn
+
+    @staticmethod
+    def get_name() -> str:
+        return "start_learning"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        self._start(int(args[0]), int(args[1]))
+
+
+class StopLearningCommand(Command):
+    """``stop_learning`` (reference: commands/stop_learning_command.py:40-61);
+    tolerates an idle node (Q22)."""
+
+    def __init__(self, stop_learning_fn: Callable[[], None]) -> None:
+        self._stop = stop_learning_fn
+
+    @staticmethod
+    def get_name() -> str:
+        return "stop_learning"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        self._stop()
+
+
+class ModelInitializedCommand(Command):
+    """``model_initialized``: the sender holds the initial weights
+    (reference: commands/model_initialized_command.py:48)."""
+
+    def __init__(self, state: NodeState) -> None:
+        self._state = state
+
+    @staticmethod
+    def get_name() -> str:
+        return "model_initialized"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        self._state.nei_status[source] = max(self._state.nei_status.get(source, -1), -1)
+        self._state.notify()
+
+
+class VoteTrainSetCommand(Command):
+    """``vote_train_set [cand, weight, ...]`` for ``round``
+    (reference: commands/vote_train_set_command.py:54-67).  Votes are filed under
+    their round, so an early vote for the next round is kept."""
+
+    def __init__(self, state: NodeState) -> None:
+        self._state = state
+
+    @staticmethod
+    def get_name() -> str:
+        return "vote_train_set"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        st = self._state
+        if st.round is None or round not in (st.round, st.round + 1):
+            logger.debug(st.addr, f"vote from {source} for round {round} ignored (mine: {st.round})")
+            return
+        if len(args) % 2:
+            raise ValueError("vote_train_set needs (candidate, weight) pairs")
+        votes = {args[i]: int(args[i + 1]) for i in range(0, len(args), 2)}
+        st.train_set_votes.setdefault(round, {})[source] = votes
+        st.notify()
+
+
+class ModelsAggregatedCommand(Command):
+    """``models_aggregated [contributors...]``: what the sender already holds
+    this round (reference: commands/models_agregated_command.py:49-51)."""
+
+    def __init__(self, state: NodeState) -> None:
+        self._state = state
+
+    @staticmethod
+    def get_name() -> str:
+        return "models_aggregated"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        st = self._state
+        if round == st.round:
+            st.models_aggregated[source] = list(args)
+            st.notify()
+
+
+class ModelsReadyCommand(Command):
+    """``models_ready``: the sender finished aggregation of ``round``
+    (reference: commands/models_ready_command.py:52-54).  Records the message's
+    round, monotonically (Q18)."""
+
+    def __init__(self, state: NodeState) -> None:
+        self._state = state
+
+    @staticmethod
+    def get_name() -> str:
+        return "models_ready"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        st = self._state
+        if st.round is None:
+            return
+        if round in (st.round - 1, st.round, st.round + 1):
+            st.nei_status[source] = max(st.nei_status.get(source, -1), round)
+            st.notify()
+
+
+class MetricsCommand(Command):
+    """``metrics [name, value, ...]`` (reference: commands/metrics_command.py:50-55)."""
+
+    def __init__(self, state: NodeState) -> None:
+        self._state = state
+
+    @staticmethod
+    def get_name() -> str:
+        return "metrics"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        for i in range(0, len(args) - 1, 2):
+            logger.log_metric(source, args[i], float(args[i + 1]), round=round if round >= 0 else None)

@@ -1,0 +1,132 @@
+"""Handlers for model-carrying messages: ``init_model`` and ``add_model``.
+
+A payload that cannot be decoded or does not match the local layout stops the
+receiving node, as in the reference (init_model_command.py:104-114,
+add_model_command.py:95-105) - the fault tests rely on it.
+"""
+
+from __future__ import annotations
+
+from typing import Any, Callable, List, Optional
+
+from p2pfl_b200.commands.command import Command
+from p2pfl_b200.exceptions import DecodingParamsError, ModelNotMatchingError
+from p2pfl_b200.management.logger import logger
+from p2pfl_b200.node_state import NodeState
+
+
+class InitModelCommand(Command):
+    """Initial weights from the experiment's initiator (or a neighbour that
+    already has them)."""
+
+    def __init__(self, state: NodeState, stop_fn: Callable[[], None], aggregator: Any, protocol: Any) -> None:
+        self._state = state
+        self._stop = stop_fn
+        self._aggregator = aggregator
+        self._protocol = protocol
+
+    @staticmethod
+    def get_name() -> str:
+        return "init_model"
+
+    def execute(
+        self,
+        source: str,
+        round: int,
+        *args: Any,
+        weights: Any = None,
+        contributors: Optional[List[str]] = None,
+        weight: int = 1,
+        **kwargs: Any,
+    ) -> None:
+        st = self._state
+        if weights is None:
+            raise ValueError("init_model without weights")
+        if st.model_initialized.is_set():
+            return
+        with st.stash_lock:
+            learner = st.learner if st.round is not None else None
+            if learner is None:
+                # the learner is still being built: keep the payload, StartLearningStage applies it
+                st.pending_init = lambda: self.execute(
+                    source, round, weights=weights, contributors=contributors, weight=weight
+                )
+                logger.debug(st.addr, "init_model stashed: learner not ready yet")
+                return
+        if st.model_initialized.is_set():
+            logger.debug(st.addr, "init_model ignored: already initialised")
+            return
+        if round != st.round:
+            logger.debug(st.addr, f"init_model for round {round} ignored (mine: {st.round})")
+            return
+        try:
+            learner.set_parameters(learner.decode_parameters(weights))
+        except (DecodingParamsError, ModelNotMatchingError) as e:
+            logger.error(st.addr, f"initial model unusable ({e!r}); stopping node")
+            self._stop()
+            return
+        except Exception as e:
+            logger.error(st.addr, f"unexpected error applying the initial model ({e!r}); stopping node")
+            self._stop()
+            return
+        st.model_initialized.set()
+        st.notify()
+        logger.info(st.addr, f"initial model received from {source}")
+        self._protocol.broadcast(self._protocol.build_msg("model_initialized"))
+
+
+class AddModelCommand(Command):
+    """A (partial or full) aggregate for the current round."""
+
+    def __init__(self, state: NodeState, stop_fn: Callable[[], None], aggregator: Any, protocol: Any) -> None:
+        self._state = state
+        self._stop = stop_fn
+        self._aggregator = aggregator
+        self._protocol = protocol
+
+    @staticmethod
+    def get_name() -> str:
+        return "add_model"
+
+    def execute(
+        self,
+        source: str,
+        round: int,
+        *args: Any,
+        weights: Any = None,
+        contributors: Optional[List[str]] = None,
+        weight: int = 1,
+        **kwargs: Any,
+    ) -> None:
+        st = self._state
+        if weights is None or contributors is None:
+            raise ValueError("add_model needs weights and contributors")
+        learner = st.learner
+        if st.round is None or learner is None:
+            logger.debug(st.addr, "add_model ignored: not learning")
+            return
+        if round != st.round:
+            logger.debug(st.addr, f"add_model from {source} for round {round} ignored (mine: {st.round})")
+            return
+        with st.stash_lock:
+            if not self._aggregator.get_train_set():
+                # vote still running here: keep the payload, Train/Wait stage replays it
+                st.pending_models.append(
+                    (round, lambda: self.execute(source, round, weights=weights, contributors=contributors, weight=weight))
+                )
+                logger.debug(st.addr, f"add_model from {source} stashed: train set not armed yet")
+                return
+        try:
+            model = learner.decode_parameters(weights)
+            learner.check_parameters(model)
+            held = self._aggregator.add_model(model, list(contributors), int(weight))
+        except (DecodingParamsError, ModelNotMatchingError) as e:
+            logger.error(st.addr, f"received model unusable ({e!r}); stopping node")
+            self._stop()
+            return
+        except Exception as e:
+            logger.error(st.addr, f"unexpected error adding a model ({e!r}); stopping node")
+            self._stop()
+            return
+        if held:
+            self._protocol.broadcast(self._protocol.build_msg("models_aggregated", held, round=st.round))

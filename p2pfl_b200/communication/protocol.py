@@ -1,0 +1,324 @@
+"""Communication protocol: interface and the transport-independent engine.
+
+``CommunicationProtocol`` is the abstract surface the node and the stages use
+(reference: p2pfl/communication/communication_protocol.py:27-190).
+
+``BaseProtocol`` implements all of it once - neighbour table, heartbeats,
+flooding gossip with TTL and duplicate suppression, command dispatch, eviction
+on failure - on top of a small :class:`Transport` (open/close a link, deliver
+one envelope, run a server).  The reference writes this logic twice, once per
+transport (grpc_server.py:102-197 and memory_server.py:100-186); here the
+in-memory, gRPC and NVLink protocols differ only in their ``Transport``.
+"""
+
+from __future__ import annotations
+
+import abc
+import threading
+from typing import Any, Callable, Dict, List, Optional, Union
+
+from p2pfl_b200.commands.command import Command
+from p2pfl_b200.communication.gossiper import Gossiper
+from p2pfl_b200.communication.heartbeater import HEARTBEAT_CMD, Heartbeater
+from p2pfl_b200.communication.messages import Message, Weights, new_message_id
+from p2pfl_b200.communication.neighbors import Neighbors
+from p2pfl_b200.exceptions import CommunicationError, NeighborNotConnectedError
+from p2pfl_b200.management.logger import logger
+from p2pfl_b200.settings import Settings
+
+Envelope = Union[Message, Weights]
+
+
+class CommunicationProtocol(abc.ABC):
+    """What a node needs from its network stack."""
+
+    @abc.abstractmethod
+    def start(self) -> None: ...
+
+    @abc.abstractmethod
+    def stop(self) -> None: ...
+
+    @abc.abstractmethod
+    def add_command(self, cmds: Union[Command, List[Command]]) -> None: ...
+
+    @abc.abstractmethod
+    def build_msg(self, cmd: str, args: Optional[List[str]] = None, round: Optional[int] = None) -> Message: ...
+
+    @abc.abstractmethod
+    def build_weights(
+        self, cmd: str, round: int, serialized_model: Any, contributors: Optional[List[str]] = None, weight: int = 1
+    ) -> Weights: ...
+
+    @abc.abstractmethod
+    def send(self, nei: str, msg: Envelope, create_connection: bool = False) -> None: ...
+
+    @abc.abstractmethod
+    def broadcast(self, msg: Message, node_list: Optional[List[str]] = None) -> None: ...
+
+    @abc.abstractmethod
+    def connect(self, addr: str, non_direct: bool = False) -> bool: ...
+
+    @abc.abstractmethod
+    def disconnect(self, nei: str, disconnect_msg: bool = True) -> None: ...
+
+    @abc.abstractmethod
+    def get_neighbors(self, only_direct: bool = False) -> Dict[str, Any]: ...
+
+    @abc.abstractmethod
+    def get_address(self) -> str: ...
+
+    @abc.abstractmethod
+    def wait_for_termination(self) -> None: ...
+
+    @abc.abstractmethod
+    def gossip_weights(
+        self,
+        early_stopping_fn: Callable[[], bool],
+        get_candidates_fn: Callable[[], List[str]],
+        status_fn: Callable[[], Any],
+        model_fn: Callable[[str], Any],
+        period: Optional[float] = None,
+        create_connection: bool = False,
+        wait_fn: Optional[Callable[[float], None]] = None,
+    ) -> None: ...
+
+
+class Transport(abc.ABC):
+    """L1: moves one envelope to one peer and runs the inbound endpoint.
+
+    The engine installs itself with :meth:`attach`; inbound traffic is handed
+    to ``engine.on_message / on_weights / on_handshake / on_disconnect``."""
+
+    engine: "BaseProtocol"
+
+    def attach(self, engine: "BaseProtocol") -> None:
+        self.engine = engine
+
+    @abc.abstractmethod
+    def address(self) -> str:
+        """Final address of this endpoint (port chosen, socket path fixed)."""
+
+    @abc.abstractmethod
+    def start(self) -> None: ...
+
+    @abc.abstractmethod
+    def stop(self) -> None: ...
+
+    @abc.abstractmethod
+    def wait_for_termination(self) -> None: ...
+
+    @abc.abstractmethod
+    def open_link(self, addr: str, handshake: bool) -> Any:
+        """Open a link to ``addr``; raise on failure."""
+
+    @abc.abstractmethod
+    def close_link(self, addr: str, link: Any, disconnect_msg: bool) -> None: ...
+
+    @abc.abstractmethod
+    def deliver(self, addr: str, link: Any, env: Envelope) -> Optional[str]:
+        """Send and wait for the answer; returns the peer's error string or
+        None.  Raises on transport failure."""
+
+
+class _ServerHandle:
+    """``protocol._server.stop()`` is reached into by the fault-injection tests
+    (reference: test/communication_test.py:195)."""
+
+    def __init__(self, transport: Transport) -> None:
+        self._t = transport
+
+    def stop(self) -> None:
+        self._t.stop()
+
+
+class BaseProtocol(CommunicationProtocol):
+    """Transport-independent protocol engine."""
+
+    def __init__(self, transport: Transport) -> None:
+        self._transport = transport
+        transport.attach(self)
+        self.addr = transport.address()
+        self._commands: Dict[str, Command] = {}
+        self._on_neighbors_change: Optional[Callable[[], None]] = None
+        self._neighbors = Neighbors(
+            self.addr, transport.open_link, transport.close_link, on_change=self._neighbors_changed
+        )
+        self._gossiper = Gossiper(self.addr, self.send)
+        self._heartbeater = Heartbeater(self.addr, self._neighbors, self._broadcast_beat)
+        self._server = _ServerHandle(transport)
+        from p2pfl_b200.commands.control import HeartbeatCommand
+
+        self.add_command(HeartbeatCommand(self._heartbeater))
+        self._running = False
+        self._terminated = threading.Event()
+
+    # ------------------------------------------------------------ lifecycle
+    def start(self) -> None:
+        self._transport.start()
+        self._heartbeater.start()
+        self._gossiper.start()
+        self._running = True
+
+    def stop(self) -> None:
+        self._running = False
+        self._heartbeater.stop()
+        self._gossiper.stop()
+        self._neighbors.clear_neighbors()
+        self._transport.stop()
+        self._terminated.set()
+
+    def wait_for_termination(self) -> None:
+        self._transport.wait_for_termination()
+
+    def get_address(self) -> str:
+        return self.addr
+
+    def set_neighbors_listener(self, fn: Optional[Callable[[], None]]) -> None:
+        """Called (from arbitrary threads) whenever the neighbour set changes."""
+        self._on_neighbors_change = fn
+
+    def _neighbors_changed(self) -> None:
+        fn = self._on_neighbors_change
+        if fn is not None:
+            try:
+                fn()
+            except Exception:
+                pass
+
+    # ------------------------------------------------------------- commands
+    def add_command(self, cmds: Union[Command, List[Command]]) -> None:
+        for c in cmds if isinstance(cmds, list) else [cmds]:
+            self._commands[c.get_name()] = c
+
+    # -------------------------------------------------------------- builders
+    def build_msg(self, cmd: str, args: Optional[List[Any]] = None, round: Optional[int] = None) -> Message:
+        return Message(
+            source=self.addr,
+            cmd=cmd,
+            args=[str(a) for a in (args or [])],
+            round=-1 if round is None else int(round),
+            ttl=Settings.TTL,
+            hash=new_message_id(),
+        )
+
+    def build_weights(
+        self, cmd: str, round: int, serialized_model: Any, contributors: Optional[List[str]] = None, weight: int = 1
+    ) -> Weights:
+        return Weights(
+            source=self.addr,
+            cmd=cmd,
+            round=int(round),
+            weights=serialized_model,
+            contributors=list(contributors or []),
+            weight=int(weight),
+        )
+
+    # ------------------------------------------------------------- outbound
+    def send(self, nei: str, msg: Envelope, create_connection: bool = False) -> None:
+        """Deliver to one neighbour.  Any failure or error answer evicts the
+        neighbour (reference: grpc_client.py:159-179, Q11)."""
+        temp_link = None
+        try:
+            try:
+                entry = self._neighbors.get(nei)
+            except KeyError:
+                entry = None
+            link = entry.link if entry is not None and entry.direct else None
+            if link is None:
+                if not create_connection:
+                    raise NeighborNotConnectedError(f"{nei} is not a direct neighbour of {self.addr}")
+                temp_link = self._transport.open_link(nei, False)
+                link = temp_link
+            err = self._transport.deliver(nei, link, msg)
+            if err:
+                raise CommunicationError(f"{nei} answered with error: {err}")
+        except NeighborNotConnectedError:
+            raise
+        except Exception as e:
+            logger.info(self.addr, f"send of '{msg.cmd}' to {nei} failed ({e}); removing neighbour")
+            self._neighbors.remove(nei, disconnect_msg=True)
+        finally:
+            if temp_link is not None:
+                try:
+                    self._transport.close_link(nei, temp_link, False)
+                except Exception:
+                    pass
+
+    def broadcast(self, msg: Message, node_list: Optional[List[str]] = None) -> None:
+        targets = node_list if node_list is not None else list(self._neighbors.get_all(only_direct=True))
+        for nei in targets:
+            try:
+                self.send(nei, msg)
+            except NeighborNotConnectedError:
+                pass
+
+    def _broadcast_beat(self, now: float) -> None:
+        self.broadcast(self.build_msg(HEARTBEAT_CMD, [str(now)]))
+
+    # ------------------------------------------------------------ neighbours
+    def connect(self, addr: str, non_direct: bool = False) -> bool:
+        return self._neighbors.add(addr, non_direct=non_direct)
+
+    def disconnect(self, nei: str, disconnect_msg: bool = True) -> None:
+        self._neighbors.remove(nei, disconnect_msg=disconnect_msg)
+
+    def get_neighbors(self, only_direct: bool = False) -> Dict[str, Any]:
+        return self._neighbors.get_all(only_direct)
+
+    def gossip_weights(self, *args: Any, **kwargs: Any) -> None:
+        self._gossiper.gossip_weights(*args, **kwargs)
+
+    # -------------------------------------------------------------- inbound
+    def on_handshake(self, addr: str) -> Optional[str]:
+        """Peer opened a link to us: add it as a direct neighbour without
+        hand-shaking back (reference: grpc_server.py:102-114)."""
+        if not self._running:
+            return "node not running"
+        if self._neighbors.add(addr, non_direct=False, handshake=False):
+            return None
+        # already a direct neighbour is fine (both sides connected at once)
+        try:
+            if self._neighbors.get(addr).direct:
+                return None
+        except KeyError:
+            pass
+        return "cannot add the neighbour"
+
+    def on_disconnect(self, addr: str) -> None:
+        self._neighbors.remove(addr, disconnect_msg=False)
+
+    def on_message(self, msg: Message) -> Optional[str]:
+        """Flooding gossip: drop duplicates, relay while TTL lasts, dispatch
+        (reference: grpc_server.py:130-166)."""
+        if not self._running:
+            return "node not running"
+        if not self._gossiper.check_and_set_processed(msg.hash):
+            return None
+        if msg.ttl > 1:
+            targets = [n for n in self._neighbors.get_all(only_direct=True) if n != msg.source]
+            if targets:
+                self._gossiper.add_message(msg.relay_copy(), targets)
+        cmd = self._commands.get(msg.cmd)
+        if cmd is None:
+            logger.error(self.addr, f"unknown command '{msg.cmd}' from {msg.source}")
+            return f"Unknown command: {msg.cmd}"
+        try:
+            cmd.execute(msg.source, msg.round, *msg.args)
+        except Exception as e:
+            logger.error(self.addr, f"command '{msg.cmd}' from {msg.source} failed: {e!r}")
+            return f"Error while processing command: {msg.cmd} {msg.args}: {e}"
+        return None
+
+    def on_weights(self, w: Weights) -> Optional[str]:
+        """Model message: no dedupe, no relay (reference: grpc_server.py:168-197)."""
+        if not self._running:
+            return "node not running"
+        cmd = self._commands.get(w.cmd)
+        if cmd is None:
+            return f"Unknown command: {w.cmd}"
+        try:
+            cmd.execute(w.source, w.round, weights=w.weights, contributors=list(w.contributors), weight=w.weight)
+        except Exception as e:
+            logger.error(self.addr, f"weights command '{w.cmd}' from {w.source} failed: {e!r}")
+            return f"Error while processing model: {w.cmd}: {e}"
+        return None

@@ -1,0 +1,109 @@
+"""Per-node mutable state shared by stages, commands and the logger.
+
+Field names follow the reference's ``NodeState`` (p2pfl/node_state.py:26-115)
+because tests and helpers read them directly (``state.round is None`` is the
+"experiment finished" signal, p2pfl/utils.py:105).  The reference uses bare
+``threading.Lock`` objects as latches; here they are ``Event``s plus one
+``Condition`` (``changed``) that every mutation notifies, so stage code can
+block on a predicate instead of sleeping a fixed period.
+"""
+
+from __future__ import annotations
+
+import threading
+from typing import Any, Callable, Dict, List, Optional
+
+
+class NodeState:
+    """State record of one node."""
+
+    def __init__(self, addr: str, simulation: bool = False) -> None:
+        self.addr = addr
+        self.simulation = simulation
+        self.status = "Idle"
+        self.actual_exp_name: Optional[str] = None
+        self.round: Optional[int] = None
+        self.total_rounds: Optional[int] = None
+        self.learner: Any = None
+
+        # who aggregated what this round: node -> list of contributors
+        self.models_aggregated: Dict[str, List[str]] = {}
+        # last round for which a neighbour is known to hold the model (-1 = initialised)
+        self.nei_status: Dict[str, int] = {}
+        self.train_set: List[str] = []
+        # votes are keyed by round so an early vote for round r+1 survives the
+        # round switch (the reference keeps one flat dict and relies on timing)
+        self.train_set_votes: Dict[int, Dict[str, Dict[str, int]]] = {}
+
+        # payloads that arrived before this node could use them (learner not
+        # built yet / train set not armed yet); replayed by the stages
+        self.stash_lock = threading.Lock()
+        self.pending_init: Optional[Callable[[], None]] = None
+        self.pending_models: List[Any] = []
+
+        # one condition for "something changed" - all waits are predicate waits
+        self.changed = threading.Condition()
+        self.start_thread_lock = threading.Lock()
+        # set once this node holds the experiment's initial weights
+        self.model_initialized = threading.Event()
+        # set when the experiment ended on this node (normally or by stop)
+        self.finished = threading.Event()
+        self.finished.set()
+
+    # ------------------------------------------------------------------ events
+    def notify(self) -> None:
+        """Wake every thread blocked in :meth:`wait_for`."""
+        with self.changed:
+            self.changed.notify_all()
+
+    def wait_for(self, predicate: Callable[[], bool], timeout: Optional[float]) -> bool:
+        """Block until ``predicate()`` holds or ``timeout`` seconds elapse."""
+        with self.changed:
+            return self.changed.wait_for(predicate, timeout)
+
+    # -------------------------------------------------------------- experiment
+    def set_experiment(self, exp_name: str, total_rounds: int) -> None:
+        """Begin an experiment (reference: node_state.py:83-95).  Unlike the
+        reference every per-experiment field is reset here (Q19)."""
+        self.status = "Learning"
+        self.actual_exp_name = exp_name
+        self.total_rounds = total_rounds
+        self.round = 0
+        self.models_aggregated = {}
+        self.train_set = []
+        self.train_set_votes = {}
+        self.finished.clear()
+        self.notify()
+
+    def increase_round(self) -> None:
+        """Advance one round (reference: node_state.py:97-108)."""
+        if self.round is None:
+            raise ValueError("round not initialised")
+        self.round += 1
+        self.models_aggregated = {}
+        # drop votes of rounds that are over
+        for r in [r for r in self.train_set_votes if r < self.round]:
+            del self.train_set_votes[r]
+        self.notify()
+
+    def clear(self) -> None:
+        """Back to idle (reference: node_state.py:110-115, plus Q19 full reset)."""
+        self.status = "Idle"
+        self.actual_exp_name = None
+        self.round = None
+        self.total_rounds = None
+        self.models_aggregated = {}
+        self.nei_status = {}
+        self.train_set = []
+        self.train_set_votes = {}
+        self.pending_init = None
+        self.pending_models = []
+        self.model_initialized.clear()
+        self.finished.set()
+        self.notify()
+
+    def __repr__(self) -> str:
+        return (
+            f"NodeState(addr={self.addr}, status={self.status}, exp={self.actual_exp_name}, "
+            f"round={self.round}/{self.total_rounds}, train_set={self.train_set})"
+        )

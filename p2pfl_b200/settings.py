@@ -1,0 +1,97 @@
+"""Global run-time configuration.
+
+Same knob names and defaults as the reference's static ``Settings`` class
+(reference: p2pfl/settings.py:26-115) so scripts that assign
+``Settings.TRAIN_SET_SIZE = 8`` keep working.  Values are read at use time.
+
+Knobs that do not exist in the reference are grouped at the bottom; each one
+either switches a documented reference quirk back on or
+configures the B200 data plane.
+"""
+
+from __future__ import annotations
+
+
+class Settings:
+    """Mutable class-attribute configuration (no instances)."""
+
+    # ---- transport -----------------------------------------------------
+    GRPC_TIMEOUT: float = 10.0
+    """Per-RPC timeout in seconds."""
+
+    # ---- logging -------------------------------------------------------
+    LOG_LEVEL: str = "INFO"
+    """DEBUG also makes the learning thread re-raise instead of stopping the node."""
+    LOG_DIR: str = "logs"
+    LOG_TO_FILE: bool = False
+    """The reference always writes logs/p2pfl.log; here it is opt-in."""
+
+    # ---- heartbeats ----------------------------------------------------
+    HEARTBEAT_PERIOD: float = 2.0
+    HEARTBEAT_TIMEOUT: float = 5.0
+
+    # ---- control-message gossip ---------------------------------------
+    GOSSIP_PERIOD: float = 0.1
+    TTL: int = 10
+    GOSSIP_MESSAGES_PER_PERIOD: int = 100
+    AMOUNT_LAST_MESSAGES_SAVED: int = 100
+
+    # ---- model gossip --------------------------------------------------
+    GOSSIP_MODELS_PERIOD: float = 1.0
+    """Upper bound on the pause between two model-gossip ticks.  The loop is
+    event driven: it wakes as soon as node state changes (SURVEY Appendix C.6)."""
+    GOSSIP_MODELS_PER_ROUND: int = 2
+    GOSSIP_EXIT_ON_X_EQUAL_ROUNDS: int = 10
+
+    # ---- learning ------------------------------------------------------
+    TRAIN_SET_SIZE: int = 4
+    VOTE_TIMEOUT: float = 60.0
+    AGGREGATION_TIMEOUT: float = 300.0
+    WAIT_HEARTBEATS_CONVERGENCE: float = 0.2 * HEARTBEAT_TIMEOUT
+
+    # ---- monitoring ----------------------------------------------------
+    RESOURCE_MONITOR_PERIOD: float = 1.0
+
+    # ===== additions (not in the reference) =============================
+    VOTE_EVERY_ROUND: bool = True
+    """True: re-vote the train set each round (BASELINE config 4).  False
+    reproduces the reference's vote-once behaviour (SURVEY Q1)."""
+    RESET_OPTIMIZER_EACH_ROUND: bool = True
+    """The reference builds a new Trainer (=> new Adam state) per round (Q16)."""
+    INIT_MODEL_TIMEOUT: float = 120.0
+    """Bounded wait for the initial weights (reference waits forever, Q23)."""
+    GRPC_MAX_MESSAGE_BYTES: int = 1 << 30
+    """Raised from gRPC's 4 MiB default so >4 MiB models fit (Q9)."""
+    GRPC_SERVER_WORKERS: int = 4
+    WIRE_DTYPE: str = "bf16"
+    """Wire dtype of the device data plane: 'bf16' (inbox mode B) or 'fp32'."""
+    DEVICE_TILE_ELEMS: int = 16384
+    """Elements per data-plane tile (one arrival flag per tile)."""
+    TRAINER_DIFFUSION_GRACE: float = 0.5
+    """Seconds a finished node waits before spending a full-model transfer on a
+    train-set peer that has not yet announced ``models_ready``."""
+    DEVICE: str = "auto"
+    """Default learner device: "auto" (current CUDA device if any), "cpu", "cuda:N"."""
+    SAFE_UNPICKLE: bool = True
+    """Decode host-path payloads with a numpy-only unpickler (Q21)."""
+
+
+def set_test_settings() -> None:
+    """Shrink every timeout so the suites run in seconds
+    (reference: p2pfl/utils.py:37-53)."""
+    Settings.GRPC_TIMEOUT = 0.5
+    Settings.HEARTBEAT_PERIOD = 0.5
+    Settings.HEARTBEAT_TIMEOUT = 2
+    Settings.GOSSIP_PERIOD = 0
+    Settings.TTL = 10
+    Settings.GOSSIP_MESSAGES_PER_PERIOD = 100
+    Settings.AMOUNT_LAST_MESSAGES_SAVED = 100
+    Settings.GOSSIP_MODELS_PERIOD = 1
+    Settings.GOSSIP_MODELS_PER_ROUND = 4
+    Settings.GOSSIP_EXIT_ON_X_EQUAL_ROUNDS = 4
+    Settings.TRAIN_SET_SIZE = 4
+    Settings.VOTE_TIMEOUT = 60
+    Settings.AGGREGATION_TIMEOUT = 60
+    Settings.WAIT_HEARTBEATS_CONVERGENCE = 0.2 * Settings.HEARTBEAT_TIMEOUT
+    Settings.INIT_MODEL_TIMEOUT = 30
+    Settings.LOG_LEVEL = "DEBUG"

@@ -1,0 +1,105 @@
+"""Stage 3a (trainers): evaluate, train, contribute, exchange partial aggregates
+(reference: p2pfl/stages/base_node/train_stage.py:42-184).
+
+Exchange policy: a trainer keeps pushing, to every train-set peer that still
+lacks something it holds, the aggregate of exactly the entries that peer does
+not have (``models_aggregated`` announcements tell who has what).  The loop is
+woken by those announcements instead of sleeping a period.
+"""
+
+from __future__ import annotations
+
+import time
+from typing import Any, List, Optional, Type
+
+from p2pfl_b200.management.logger import logger
+from p2pfl_b200.stages.common import evaluate_and_share, pack_model
+from p2pfl_b200.stages.stage import LearningContext, Stage
+from p2pfl_b200.stages.stage_factory import StageFactory
+
+
+class TrainStage(Stage):
+    @staticmethod
+    def name() -> str:
+        return "TrainStage"
+
+    @staticmethod
+    def execute(ctx: LearningContext) -> Optional[Type[Stage]]:
+        st, proto, agg = ctx.state, ctx.communication_protocol, ctx.aggregator
+        if st.learner is None or st.round is None:
+            return None
+        t0 = time.time()
+        agg.set_nodes_to_aggregate(st.train_set)
+        TrainStage.replay_early_models(ctx)
+        st.learner.begin_round(st.round)
+
+        if ctx.early_stopping_fn():
+            return None
+        evaluate_and_share(ctx)
+        t1 = time.time()
+
+        if ctx.early_stopping_fn():
+            return None
+        logger.info(st.addr, "training")
+        st.learner.fit()
+        t2 = time.time()
+
+        if ctx.early_stopping_fn():
+            return None
+        held = agg.add_model(st.learner.export_model(), [st.addr], st.learner.get_num_samples()[0])
+        proto.broadcast(proto.build_msg("models_aggregated", held, round=st.round))
+        TrainStage._gossip_partial_aggregates(ctx)
+        t3 = time.time()
+        for k, dt in (("evaluate", t1 - t0), ("fit", t2 - t1), ("exchange", t3 - t2)):
+            ctx.timings[k] = ctx.timings.get(k, 0.0) + dt
+        if ctx.early_stopping_fn():
+            return None
+        return StageFactory.get_stage("GossipModelStage")
+
+    @staticmethod
+    def replay_early_models(ctx: LearningContext) -> None:
+        """Models that arrived before the vote finished were stashed by
+        AddModelCommand; hand them to the aggregator now."""
+        st = ctx.state
+        with st.stash_lock:
+            stash, st.pending_models = st.pending_models, []
+        for rnd, thunk in stash:
+            if rnd == st.round:
+                thunk()
+
+    @staticmethod
+    def _gossip_partial_aggregates(ctx: LearningContext) -> None:
+        st, proto, agg = ctx.state, ctx.communication_protocol, ctx.aggregator
+
+        def has(n: str) -> List[str]:
+            return st.models_aggregated.get(n, [])
+
+        def candidates() -> List[str]:
+            mine = set(agg.get_aggregated_models())
+            known = proto.get_neighbors(only_direct=False)
+            return [n for n in st.train_set if n != st.addr and n in known and (mine - set(has(n)))]
+
+        def status() -> Any:
+            return sorted((n, tuple(sorted(has(n)))) for n in st.train_set if n != st.addr)
+
+        cache = {}
+
+        def model_fn(n: str) -> Any:
+            if st.learner is None or st.round is None:
+                return None
+            model, contributors, weight = agg.get_partial_aggregation(has(n))
+            if model is None:
+                return None
+            key = tuple(sorted(contributors))
+            if key not in cache:  # same partial for several peers: pack once (Q13)
+                cache[key] = pack_model(proto, st.learner, model)
+            return proto.build_weights("add_model", st.round, cache[key], contributors, weight)
+
+        def changed(snapshot: Any) -> bool:
+            return ctx.early_stopping_fn() or status() != snapshot or not candidates()
+
+        def wait_fn(t: float) -> None:
+            snap = status()
+            st.wait_for(lambda: changed(snap), t)
+
+        proto.gossip_weights(ctx.early_stopping_fn, candidates, status, model_fn, create_connection=True, wait_fn=wait_fn)

@@ -1,0 +1,36 @@
+"""Helpers shared by the stages."""
+
+from __future__ import annotations
+
+from typing import Any, Dict, List
+
+from p2pfl_b200.management.logger import logger
+
+
+def pack_model(protocol: Any, learner: Any, params: Any) -> Any:
+    """Serialise ``params`` the way ``protocol`` wants it: a device payload for
+    data planes that move device memory themselves, pickled bytes otherwise."""
+    if getattr(protocol, "device_payloads", False) and hasattr(learner, "export_payload"):
+        return learner.export_payload(params)
+    return learner.encode_parameters(params=params)
+
+
+def broadcast_metrics(protocol: Any, state: Any, results: Dict[str, float]) -> None:
+    """Share evaluation results with every node
+    (reference: stages/base_node/train_stage.py:103-112)."""
+    if not results:
+        return
+    flat: List[str] = []
+    for k, v in results.items():
+        flat += [str(k), str(v)]
+    protocol.broadcast(protocol.build_msg("metrics", flat, round=state.round))
+
+
+def evaluate_and_share(ctx: Any) -> None:
+    st = ctx.state
+    if st.learner is None:
+        return
+    logger.debug(st.addr, "evaluating")
+    results = st.learner.evaluate()
+    logger.debug(st.addr, f"evaluated: {results}")
+    broadcast_metrics(ctx.communication_protocol, st, results)

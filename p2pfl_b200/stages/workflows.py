@@ -1,0 +1,39 @@
+"""Workflow runner (reference: p2pfl/stages/workflows.py:35-55).
+
+A workflow object is single-use: ``Node`` builds a fresh one per experiment,
+which is what makes a second ``set_start_learning`` on the same node work
+(the reference keeps ``current_stage`` across runs).
+"""
+
+from __future__ import annotations
+
+import time
+from typing import List, Optional, Type
+
+from p2pfl_b200.management.logger import logger
+from p2pfl_b200.stages.stage import LearningContext, Stage
+from p2pfl_b200.stages.stage_factory import StageFactory
+
+
+class StageWorkflow:
+    def __init__(self, first_stage: Type[Stage]) -> None:
+        self.current_stage: Optional[Type[Stage]] = first_stage
+        self.history: List[str] = []
+        self.finished = False
+
+    def run(self, ctx: LearningContext) -> None:
+        while self.current_stage is not None:
+            stage = self.current_stage
+            self.history.append(stage.name())
+            logger.debug(ctx.state.addr, f"running stage {stage.name()}")
+            t0 = time.time()
+            self.current_stage = stage.execute(ctx)
+            ctx.timings["stage:" + stage.name()] = ctx.timings.get("stage:" + stage.name(), 0.0) + time.time() - t0
+        self.finished = True
+
+
+class LearningWorkflow(StageWorkflow):
+    """StartLearning -> VoteTrainSet -> (Train | WaitAggregatedModels) -> GossipModel -> RoundFinished -> ..."""
+
+    def __init__(self) -> None:
+        super().__init__(StageFactory.get_stage("StartLearningStage"))
