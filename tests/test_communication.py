@@ -1,0 +1,197 @@
+"""Integration tests of the control plane with real nodes on loopback
+(mirrors reference test/communication_test.py) - run over both transports."""
+
+import time
+
+import pytest
+
+from p2pfl_b200.communication.grpc import GrpcCommunicationProtocol
+from p2pfl_b200.communication.grpc.address import AddressParser
+from p2pfl_b200.communication.memory import InMemoryCommunicationProtocol
+from p2pfl_b200.communication.messages import Message
+from p2pfl_b200.node import Node
+from p2pfl_b200.settings import Settings
+from p2pfl_b200.utils import full_connection, wait_convergence
+
+PROTOCOLS = [InMemoryCommunicationProtocol, GrpcCommunicationProtocol]
+
+
+def _nodes(n, protocol):
+    nodes = [Node(None, None, protocol=protocol) for _ in range(n)]
+    for x in nodes:
+        x.start()
+    return nodes
+
+
+def _stop(nodes):
+    for x in nodes:
+        x.stop()
+
+
+@pytest.mark.parametrize("protocol", PROTOCOLS)
+def test_connect_invalid_node(protocol):
+    n = Node(None, None, protocol=protocol)
+    n.start()
+    n.connect("google.es:80")
+    n.connect("holadani.holaenrique")
+    assert len(n.get_neighbors()) == 0
+    n.stop()
+
+
+@pytest.mark.parametrize("protocol", PROTOCOLS)
+def test_basic_node_pairing(protocol):
+    n1, n2 = _nodes(2, protocol)
+    try:
+        assert n1.connect(n2.addr)
+        wait_convergence([n1, n2], 1, only_direct=True)
+        n2.disconnect(n1.addr)
+        wait_convergence([n1, n2], 0, only_direct=True, wait=Settings.HEARTBEAT_PERIOD * 2 + 1)
+    finally:
+        _stop([n1, n2])
+
+
+@pytest.mark.parametrize("protocol", PROTOCOLS)
+def test_full_connected(protocol):
+    n1, n2, n3, n4 = nodes = _nodes(4, protocol)
+    try:
+        n1.connect(n2.addr)
+        wait_convergence([n1, n2], 1, only_direct=True)
+        full_connection(n3, [n1, n2])
+        wait_convergence([n1, n2, n3], 2, only_direct=True)
+        full_connection(n4, [n1, n2, n3])
+        wait_convergence(nodes, 3, only_direct=True)
+        n1.stop()
+        wait_convergence([n2, n3, n4], 2, only_direct=True)
+        n2.stop()
+        wait_convergence([n3, n4], 1, only_direct=True)
+        n3.stop()
+        wait_convergence([n4], 0, only_direct=True)
+    finally:
+        _stop(nodes)
+
+
+@pytest.mark.parametrize("protocol", PROTOCOLS)
+def test_network_neighbors_star(protocol):
+    """Indirect discovery through TTL-flooded heartbeats on a star."""
+    nodes = _nodes(6, protocol)
+    hub, leaves = nodes[0], nodes[1:]
+    try:
+        for leaf in leaves:
+            leaf.connect(hub.addr)
+        wait_convergence(nodes, 5, only_direct=False, wait=6)
+        assert len(hub.get_neighbors(only_direct=True)) == 5
+        assert all(len(l.get_neighbors(only_direct=True)) == 1 for l in leaves)
+        leaves[-1].stop()
+        wait_convergence(nodes[:-1], 4, only_direct=False, wait=8)
+    finally:
+        _stop(nodes)
+
+
+@pytest.mark.parametrize("protocol", PROTOCOLS)
+def test_bad_msg_evicts(protocol):
+    n1, n2 = _nodes(2, protocol)
+    try:
+        n1.connect(n2.addr)
+        wait_convergence([n1, n2], 1, only_direct=True)
+        proto = n1._communication_protocol
+        proto.broadcast(proto.build_msg("BAD_MSG"))
+        wait_convergence([n1, n2], 0, only_direct=True, wait=4)
+    finally:
+        _stop([n1, n2])
+
+
+@pytest.mark.parametrize("protocol", PROTOCOLS)
+def test_node_abrupt_down(protocol):
+    """Fault injection: kill only the heartbeater of one node, only the server
+    of another; the survivors must evict them."""
+    n1, n2, n3 = nodes = _nodes(3, protocol)
+    try:
+        n1.connect(n2.addr)
+        n3.connect(n1.addr)
+        n3.connect(n2.addr)
+        wait_convergence(nodes, 2, only_direct=True)
+        n1._communication_protocol._heartbeater.stop()
+        wait_convergence([n2, n3], 1, only_direct=False, wait=10)
+        n2._communication_protocol._server.stop()
+        wait_convergence([n3], 0, only_direct=False, wait=10)
+    finally:
+        _stop(nodes)
+
+
+def test_ttl_bounds_reach_and_relay_copies_message():
+    """A message floods exactly TTL hops down a line, and the relay works on a
+    copy (the reference decrements the shared dict, Q6)."""
+    Settings.TTL = 3
+    nodes = _nodes(6, InMemoryCommunicationProtocol)
+    seen = []
+    try:
+        from p2pfl_b200.commands.command import Command
+
+        class Probe(Command):
+            def __init__(self, who):
+                self.who = who
+
+            @staticmethod
+            def get_name():
+                return "probe"
+
+            def execute(self, source, round, *args, **kw):
+                seen.append(self.who)
+
+        for i, n in enumerate(nodes):
+            n._communication_protocol.add_command(Probe(i))
+        for i in range(5):
+            nodes[i + 1].connect(nodes[i].addr)
+        wait_convergence(nodes[1:5], 2, only_direct=True)
+        proto = nodes[0]._communication_protocol
+        msg = proto.build_msg("probe")
+        proto.broadcast(msg)
+        time.sleep(0.5)
+        assert sorted(seen) == [1, 2, 3]
+        assert msg.ttl == 3  # original untouched
+    finally:
+        _stop(nodes)
+
+
+def test_duplicate_filter_ring():
+    Settings.AMOUNT_LAST_MESSAGES_SAVED = 3
+    n = Node(None, None, protocol=InMemoryCommunicationProtocol)
+    g = n._communication_protocol._gossiper
+    assert g.check_and_set_processed(1) and not g.check_and_set_processed(1)
+    for h in (2, 3, 4):
+        assert g.check_and_set_processed(h)
+    assert g.check_and_set_processed(1)  # fell out of the ring
+
+
+def test_address_parser():
+    assert AddressParser("127.0.0.1:5000").get_parsed_address() == "127.0.0.1:5000"
+    assert AddressParser("[::1]:5000").get_parsed_address() == "[::1]:5000"
+    assert AddressParser("unix:///tmp/x.sock").get_parsed_address() == "unix:///tmp/x.sock"
+    bare = AddressParser("127.0.0.1")
+    assert bare.port and bare.get_parsed_address() == f"127.0.0.1:{bare.port}"
+    with pytest.raises(ValueError):
+        AddressParser("host:notaport")
+
+
+def test_proto_wire_bytes():
+    """Field numbers/types match node.proto (hand-checked protobuf encoding)."""
+    from p2pfl_b200.communication.grpc import proto
+
+    pb = proto.PbMessage(source="a", ttl=2, hash=5, cmd="c", args=["x"])
+    pb.round = 7
+    assert pb.SerializeToString() == b"\x0a\x01a\x10\x02\x18\x05\x22\x01c\x2a\x01x\x30\x07"
+    w = proto.PbWeights(source="s", round=1, weights=b"\x00\x01", contributors=["p", "q"], weight=3, cmd="add_model")
+    assert w.SerializeToString() == b"\x0a\x01s\x10\x01\x1a\x02\x00\x01\x22\x01p\x22\x01q\x28\x03\x32\x09add_model"
+    assert not proto.PbResponseMessage().HasField("error")
+
+
+def test_unix_socket_transport(tmp_path):
+    a = Node(None, None, address=f"unix://{tmp_path}/a.sock", protocol=GrpcCommunicationProtocol)
+    b = Node(None, None, address=f"unix://{tmp_path}/b.sock", protocol=GrpcCommunicationProtocol)
+    a.start()
+    b.start()
+    try:
+        assert a.connect(b.addr)
+        wait_convergence([a, b], 1, only_direct=True)
+    finally:
+        _stop([a, b])
