@@ -1,0 +1,395 @@
+// D[M,N] = A[M,K] . B[N,K]^T on Blackwell 5th-gen tensor cores.
+//
+// reference sites replaced: mlp.py:63-67 / cnn.py:84-85 (nn.Linear forward,
+// cuBLAS sgemm + bias + ReLU) and their autograd dgrad / wgrad GEMMs
+// (SURVEY.md K1, K2, K4, K8).
+//
+// Structure (one 128 x BN output tile per CTA, 6 warps):
+//   warp 0      TMA producer : cp.async.bulk.tensor (128B swizzle) global->smem,
+//                              4-stage ring, mbarrier complete_tx
+//   warp 1      MMA issuer   : one elected lane issues tcgen05.mma (kind::f16,
+//                              bf16 x bf16 -> fp32) with smem descriptors;
+//                              accumulator lives in TMEM; tcgen05.commit frees
+//                              smem stages and finally signals the epilogue
+//   warps 2..5  epilogue     : tcgen05.ld TMEM->registers, fused
+//                              alpha / bias / ReLU / ReLU-mask / row-sum, then
+//                              up to four output layouts (fp32|bf16, direct|transposed)
+//
+// Operands are both K-major ("TN"); callers keep activations in both
+// orientations instead (see learning/b200_learner.py), which keeps every GEMM
+// of the train step on this one kernel.
+#include <cuda.h>
+
+#include "common.cuh"
+
+using namespace p2pfl;
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
+constexpr int kStages = 4;
+constexpr int kThreadsGemm = 192;
+constexpr uint32_t kTileABytes = BM * BK * 2;
+
+struct Epilogue {
+  const float* bias;
+  const __nv_bfloat16* mask;
+  float* out_f32;
+  __nv_bfloat16* out_bf16;
+  float* out_f32_t;
+  __nv_bfloat16* out_bf16_t;
+  float* rowsum;
+  float alpha;
+  int32_t ld_mask, ld_f32, ld_bf16, ld_f32_t, ld_bf16_t;
+  int32_t bias_per_row, relu;
+};
+
+// ------------------------------------------------------------------ PTX glue
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  const long long t0 = clock64();
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    // bring-up guard: a protocol bug must fault, not hang the GPU
+    if (clock64() - t0 > 4000000000LL) __trap();
+  }
+}
+
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint32_t bar, uint32_t dst, int crd_inner, int crd_outer) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(crd_inner), "r"(crd_outer)
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] . B[smem]^T, bf16 inputs, fp32 accumulate
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier once every previously issued MMA has completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128B-swizzled operand tile whose rows are 128 bytes:
+//   start address >> 4 | LBO (unused for swizzled K-major) | SBO = 8 rows * 128 B
+//   | descriptor version 1 (Blackwell) | layout type 2 = SWIZZLE_128B
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=BN
+template <int BN>
+__device__ __forceinline__ constexpr uint32_t make_idesc() {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+// ------------------------------------------------------------------- kernel
+template <int BN>
+__global__ void __launch_bounds__(kThreadsGemm, 1)
+gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, Epilogue ep, int M,
+               int N, int K) {
+  constexpr uint32_t kTileBBytes = BN * BK * 2;
+  constexpr uint32_t kStageBytes = kTileABytes + kTileBBytes;
+
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B tiles must start on 1024-byte boundaries
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ __align__(8) uint64_t empty_bar[kStages];
+  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
+  const int num_kb = (K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_a)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_b)) : "memory");
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), 1);
+    }
+    mbar_init(smem_u32(&tmem_full_bar), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % kStages;
+        const uint32_t phase = (uint32_t)(kb / kStages) & 1u;
+        mbar_wait(smem_u32(&empty_bar[s]), phase ^ 1u);
+        const uint32_t bar = smem_u32(&full_bar[s]);
+        mbar_expect_tx(bar, kStageBytes);
+        const uint32_t a_dst = smem_u32(smem + (size_t)s * kStageBytes);
+        tma_load_2d(&tma_a, bar, a_dst, kb * BK, m0);
+        tma_load_2d(&tma_b, bar, a_dst + kTileABytes, kb * BK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc<BN>();
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % kStages;
+      const uint32_t phase = (uint32_t)(kb / kStages) & 1u;
+      mbar_wait(smem_u32(&full_bar[s]), phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t a_addr = smem_u32(smem + (size_t)s * kStageBytes);
+        const uint64_t da = make_smem_desc(a_addr);
+        const uint64_t db = make_smem_desc(a_addr + kTileABytes);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the (addr >> 4) field
+          umma_bf16(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(smem_u32(&empty_bar[s]));  // smem stage reusable once these MMAs retire
+        if (kb == num_kb - 1) umma_commit(smem_u32(&tmem_full_bar));
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    // a warp may only touch the TMEM lane quarter given by (warp id % 4)
+    const int q = warp & 3;
+    const int m = m0 + q * 32 + lane;
+    mbar_wait(smem_u32(&tmem_full_bar), 0);
+    tc_fence_after();
+    const float bias_row = (ep.bias && ep.bias_per_row && m < M) ? ep.bias[m] : 0.f;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      const int nb = n0 + c * 32;
+      if (nb >= N) break;
+      uint32_t r[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), r);
+      float x[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        float v = __uint_as_float(r[j]) * ep.alpha;
+        if (ep.bias) v += ep.bias_per_row ? bias_row : ((nb + j < N) ? ep.bias[nb + j] : 0.f);
+        if (ep.relu) v = fmaxf(v, 0.f);
+        x[j] = v;
+      }
+      if (ep.mask && m < M) {
+        const __nv_bfloat16* mk = ep.mask + (size_t)m * ep.ld_mask + nb;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (nb + j < N && !(__bfloat162float(mk[j]) > 0.f)) x[j] = 0.f;
+      }
+      if (m < M) {
+        const int valid = (N - nb) < 32 ? (N - nb) : 32;
+        if (ep.rowsum) {
+          float s = 0.f;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < valid) s += x[j];
+          atomicAdd(ep.rowsum + m, s);
+        }
+        if (ep.out_f32) {
+          float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
+          if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < valid) o[j] = x[j];
+          }
+        }
+        if (ep.out_bf16) {
+          __nv_bfloat16* o = ep.out_bf16 + (size_t)m * ep.ld_bf16 + nb;
+          if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 u;
+              u.x = pack_bf16x2(x[j], x[j + 1]);
+              u.y = pack_bf16x2(x[j + 2], x[j + 3]);
+              u.z = pack_bf16x2(x[j + 4], x[j + 5]);
+              u.w = pack_bf16x2(x[j + 6], x[j + 7]);
+              *reinterpret_cast<uint4*>(o + j) = u;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < valid) o[j] = __float2bfloat16_rn(x[j]);
+          }
+        }
+        // transposed outputs: consecutive lanes hold consecutive m -> coalesced per column
+        if (ep.out_f32_t) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < valid) ep.out_f32_t[(size_t)(nb + j) * ep.ld_f32_t + m] = x[j];
+        }
+        if (ep.out_bf16_t) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < valid) ep.out_bf16_t[(size_t)(nb + j) * ep.ld_bf16_t + m] = __float2bfloat16_rn(x[j]);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BN);
+  }
+}
+
+// ------------------------------------------------------------- host: TMA maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 [rows, ld] row-major, logical width `cols` (<= ld); box = [64 x box_rows], 128B swizzle
+int make_map(CUtensorMap* map, const void* base, int rows, int cols, int ld, int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  P2PFL_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  P2PFL_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "GEMM operands must be 16-byte aligned");
+  P2PFL_REQUIRE(((size_t)ld * 2) % 16 == 0, "GEMM operand leading dimensions must be multiples of 8 elements");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%d cols=%d ld=%d box_rows=%d)", (int)r, rows, cols,
+              ld, box_rows);
+    return -2;
+  }
+  return 0;
+}
+
+template <int BN>
+int launch(int device, cudaStream_t stream, const p2pfl_gemm_args& a, const Epilogue& ep) {
+  CUtensorMap ma, mb;
+  if (int rc = make_map(&ma, a.A, a.M, a.K, a.lda, BM)) return rc;
+  if (int rc = make_map(&mb, a.B, a.N, a.K, a.ldb, BN)) return rc;
+  constexpr size_t smem = (size_t)kStages * (kTileABytes + BN * BK * 2) + 1024;
+  static bool attr_set[64] = {false};
+  if (device >= 0 && device < 64 && !attr_set[device]) {
+    P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_tn_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set[device] = true;
+  }
+  dim3 grid((a.M + BM - 1) / BM, (a.N + BN - 1) / BN, 1);
+  gemm_tn_kernel<BN><<<grid, kThreadsGemm, smem, stream>>>(ma, mb, ep, a.M, a.N, a.K);
+  P2PFL_LAUNCH_OK();
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* args) {
+  P2PFL_REQUIRE(args != nullptr, "null args");
+  const p2pfl_gemm_args& a = *args;
+  P2PFL_REQUIRE(a.A && a.B && a.M > 0 && a.N > 0 && a.K > 0, "bad GEMM shape or operands");
+  P2PFL_REQUIRE(a.out_f32 || a.out_bf16 || a.out_f32_t || a.out_bf16_t || a.rowsum, "GEMM needs an output");
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  Epilogue ep;
+  ep.bias = a.bias;
+  ep.mask = reinterpret_cast<const __nv_bfloat16*>(a.mask);
+  ep.out_f32 = a.out_f32;
+  ep.out_bf16 = reinterpret_cast<__nv_bfloat16*>(a.out_bf16);
+  ep.out_f32_t = a.out_f32_t;
+  ep.out_bf16_t = reinterpret_cast<__nv_bfloat16*>(a.out_bf16_t);
+  ep.rowsum = a.rowsum;
+  ep.alpha = a.alpha;
+  ep.ld_mask = a.ld_mask;
+  ep.ld_f32 = a.ld_f32;
+  ep.ld_bf16 = a.ld_bf16;
+  ep.ld_f32_t = a.ld_f32_t;
+  ep.ld_bf16_t = a.ld_bf16_t;
+  ep.bias_per_row = a.bias_per_row;
+  ep.relu = a.relu;
+  cudaStream_t s = as_stream(stream);
+  if (a.N <= 32) return launch<32>(device, s, a, ep);
+  if (a.N <= 64) return launch<64>(device, s, a, ep);
+  if (a.N <= 128) return launch<128>(device, s, a, ep);
+  return launch<256>(device, s, a, ep);
+}

@@ -1,0 +1,172 @@
+/*
+ * p2pfl_b200 - C ABI of the sm_100a kernel library (libp2pfl_b200.so).
+ *
+ * Every entry point returns 0 on success or a non-zero code; the text of the
+ * last failure on the calling thread is available from p2pfl_last_error().
+ * `stream` is a cudaStream_t passed as void*.  `device` is the CUDA ordinal the
+ * pointers live on; entry points make it current before launching.
+ * All kernels are asynchronous on `stream` unless stated otherwise.
+ *
+ * Reference citations name the site in Angel3245/p2pfl whose work the entry
+ * point replaces (see SURVEY.md section 2.5 for the K / C numbering).
+ */
+#ifndef P2PFL_B200_H
+#define P2PFL_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* p2pfl_last_error(void);
+int p2pfl_version(void);
+
+/* ------------------------------------------------------------------ runtime
+ * Device arenas that can be mapped into peer GPUs / peer processes.
+ * (No counterpart in the reference: it keeps models in host state_dicts.) */
+int p2pfl_rt_alloc(int device, uint64_t bytes, void** out_ptr);
+int p2pfl_rt_free(int device, void* ptr);
+int p2pfl_rt_ipc_export(int device, void* ptr, uint8_t out_handle[64]);
+int p2pfl_rt_ipc_open(int device, const uint8_t handle[64], void** out_ptr);
+int p2pfl_rt_ipc_close(int device, void* ptr);
+int p2pfl_rt_enable_peer(int device, int peer_device);
+int p2pfl_rt_can_access_peer(int device, int peer_device, int* out_yes);
+int p2pfl_rt_memset32(int device, void* stream, void* ptr, uint32_t value, uint64_t count);
+int p2pfl_rt_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, uint64_t* total_mem);
+
+/* --------------------------------------------------------------- optimizers
+ * K5: torch.optim.Adam.step (mlp.py:71-73, cnn.py:89-91) as ONE kernel over
+ * the flat parameter arena; optionally also refreshes the bf16 working copy.
+ * t = *step_ptr + step_offset is the 1-based Adam step (bias correction). */
+int p2pfl_adam_step(int device, void* stream, float* p, const float* g, float* m, float* v,
+                    void* p_bf16 /* nullable */, uint64_t n, float lr, float beta1, float beta2,
+                    float eps, float weight_decay, const int32_t* step_ptr, int32_t step_offset);
+int p2pfl_sgd_step(int device, void* stream, float* p, const float* g, float* mom /* nullable */,
+                   void* p_bf16 /* nullable */, uint64_t n, float lr, float momentum);
+int p2pfl_add_i32(int device, void* stream, int32_t* ptr, int32_t delta);
+/* fp32 -> bf16 cast of a flat vector */
+int p2pfl_cast_f32_bf16(int device, void* stream, const float* src, void* dst, uint64_t n);
+/* Batched 2-D transpose+cast: for each of `count` matrices (rows x cols fp32 at
+ * src_off) write the bf16 transpose (cols x rows, leading dim ld_t) at dst_off. */
+typedef struct {
+  uint64_t src_off; /* elements into src (fp32) */
+  uint64_t dst_off; /* elements into dst (bf16) */
+  int32_t rows, cols, ld_t, pad_;
+} p2pfl_transpose_desc;
+int p2pfl_transpose_cast(int device, void* stream, const float* src, void* dst,
+                         const p2pfl_transpose_desc* descs, int count);
+
+/* ------------------------------------------------------------------- losses
+ * K3/K9: log_softmax + cross_entropy forward AND backward in one kernel
+ * (mlp.py:68,78; cnn.py:73,96).  logits fp32 [B, ld_logits]; labels int32 [B].
+ * Writes dlogits (already divided by B) as bf16 in both layouts the GEMMs
+ * consume ([B, ld_d] and [C, ld_dt]), the last layer's bias gradient, and
+ * adds the summed loss to *loss_sum. */
+int p2pfl_softmax_xent(int device, void* stream, const float* logits, int ld_logits,
+                       const int32_t* labels, int B, int C, void* dlogits_bf16, int ld_d,
+                       void* dlogits_t_bf16, int ld_dt, float* dbias /* nullable */,
+                       float* loss_sum /* nullable */);
+/* K10: evaluation reduce: adds sum of per-sample loss and number of correct
+ * argmax predictions (mlp.py:96-99 torchmetrics Accuracy). */
+int p2pfl_eval_reduce(int device, void* stream, const float* logits, int ld_logits,
+                      const int32_t* labels, int B, int C, float* loss_sum, int32_t* correct);
+
+/* ------------------------------------------------------------------- FedAvg
+ * K12: fedavg.py:49-58 as one fused pass.  out = sum_i w[i] * model_i with the
+ * (already normalised) weights; model_i is fp32 (is_bf16[i]==0) or bf16. */
+#define P2PFL_MAX_MODELS 16
+int p2pfl_fedavg(int device, void* stream, int n_models, const void* const* models,
+                 const float* weights, const int32_t* is_bf16, float* out_f32 /* nullable */,
+                 void* out_bf16 /* nullable */, uint64_t n);
+
+/* ------------------------------------------------------------- gossip plane
+ * C1/C3/C4 + K12: model push over NVLink fused with FedAvg on arrival
+ * (gossiper.py:239 client.send + fedavg.py:49-58 + lightning_learner.py:152).
+ *
+ * An *inbox* lives in the receiver's arena: `slots` model-sized buffers in the
+ * wire dtype plus one uint32 arrival flag per (slot, tile).  A sender stores
+ * its tiles into slot[sender] of every peer and then publishes `seq` in the
+ * tile's flag with release semantics at system scope; the receiver acquires the
+ * flag before reading the tile.  `tile` is in elements. */
+#define P2PFL_MAX_PEERS 16
+typedef struct {
+  void* inbox[P2PFL_MAX_PEERS];     /* peer-mapped base of slot[me] in peer j's arena */
+  uint32_t* flags[P2PFL_MAX_PEERS]; /* peer-mapped base of flags[me] in peer j's arena */
+  int32_t n_peers;
+  int32_t wire_bf16; /* 1: bf16 wire, 0: fp32 wire */
+} p2pfl_push_table;
+
+typedef struct {
+  const void* slot[P2PFL_MAX_PEERS];     /* local base of slot[j] */
+  const uint32_t* flags[P2PFL_MAX_PEERS]; /* local base of flags[j] */
+  float weight[P2PFL_MAX_PEERS];          /* normalised FedAvg weight of contributor j */
+  int32_t n_slots;      /* contributors arriving through the inbox */
+  int32_t self_pos;     /* position of the local model in the summation order, -1: not a contributor */
+  float self_weight;
+  int32_t wire_bf16;
+  int32_t round_self;   /* 1: round the local model to the wire dtype first (bit-identical results on all nodes) */
+  int32_t pad_;
+} p2pfl_reduce_table;
+
+/* status words written by the reduce kernels (device memory, int32[4]):
+ * [0] = 1 if aborted/timeout, [1] = number of tiles finalised, [2],[3] reserved */
+
+/* G1/G3: push `src` (fp32, n elements) into every peer's inbox slot. */
+int p2pfl_gossip_push(int device, void* stream, const float* src, uint64_t n, uint32_t tile,
+                      uint32_t seq, const p2pfl_push_table* table);
+/* G2: wait per tile for every expected slot, weighted-accumulate in fp32,
+ * write the live parameters (fp32 and optional bf16 copy).  `abort_flag` is a
+ * host-writable word polled while spinning; `timeout_cycles` bounds each wait. */
+int p2pfl_gossip_reduce(int device, void* stream, float* params, void* params_bf16 /* nullable */,
+                        uint64_t n, uint32_t tile, uint32_t seq, const p2pfl_reduce_table* table,
+                        const uint32_t* abort_flag /* nullable */, uint64_t timeout_cycles,
+                        int32_t* status /* nullable */);
+/* G1+G2 in ONE kernel: push all local tiles, then reduce tiles as they land.
+ * Uses device scratch: `status` (int32[4]). */
+int p2pfl_gossip_fused(int device, void* stream, float* params, void* params_bf16 /* nullable */,
+                       uint64_t n, uint32_t tile, uint32_t seq, const p2pfl_push_table* push,
+                       const p2pfl_reduce_table* reduce, const uint32_t* abort_flag,
+                       uint64_t timeout_cycles, int32_t* status);
+/* Single-GPU emulation of R ranks exchanging through one cooperative launch
+ * (test harness for machines with fewer GPUs than ranks). */
+int p2pfl_gossip_fused_emulated(int device, void* stream, int n_ranks, float* const* params,
+                                uint64_t n, uint32_t tile, uint32_t seq,
+                                const p2pfl_push_table* push_tables,
+                                const p2pfl_reduce_table* reduce_tables, uint64_t timeout_cycles,
+                                int32_t* status /* int32[4 * n_ranks] */);
+
+/* --------------------------------------------------------------------- GEMM
+ * K1/K2/K4/K8: D[M,N] = A[M,K] . B[N,K]^T on tcgen05 tensor cores, operands bf16
+ * K-major staged by TMA (128B swizzle), fp32 accumulators in TMEM, fused
+ * epilogue (mlp.py:63-67 Linear+ReLU forward, autograd dgrad/wgrad backward).
+ * Epilogue, in order: + bias (per row if bias_per_row else per column), ReLU if
+ * relu, zero where mask<=0 (mask bf16 [M, ld_mask], same layout as D), then any
+ * of the four outputs (nullable), and row sums (rowsum[m] += sum_n D[m,n]). */
+typedef struct {
+  const void* A; int32_t lda;   /* bf16 [M, lda] */
+  const void* B; int32_t ldb;   /* bf16 [N, ldb] */
+  int32_t M, N, K;
+  const float* bias; int32_t bias_per_row;
+  int32_t relu;
+  const void* mask; int32_t ld_mask;
+  float* out_f32;   int32_t ld_f32;     /* [M, ld_f32] */
+  void*  out_bf16;  int32_t ld_bf16;    /* [M, ld_bf16] */
+  float* out_f32_t; int32_t ld_f32_t;   /* [N, ld_f32_t] (transposed) */
+  void*  out_bf16_t; int32_t ld_bf16_t; /* [N, ld_bf16_t] (transposed) */
+  float* rowsum;                        /* [M], atomically accumulated */
+  float alpha;                          /* scales the accumulator before the epilogue */
+} p2pfl_gemm_args;
+int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* args);
+
+/* ------------------------------------------------------------ data movement
+ * K11/N8: device-resident dataset; gather a shuffled epoch in bf16, both as
+ * [n, feat] and per-batch transposed [n/B][feat][B] for the wgrad GEMM. */
+int p2pfl_gather_rows(int device, void* stream, const float* src, const int32_t* perm,
+                      int n_rows, int feat, int batch, void* dst_bf16, void* dst_t_bf16 /* nullable */,
+                      const int32_t* labels_src /* nullable */, int32_t* labels_dst /* nullable */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* P2PFL_B200_H */

@@ -1,0 +1,428 @@
+"""Fused sm_100a learner: the local train step as hand-written kernels.
+
+Replaces what the reference does inside ``Trainer.fit`` / ``Trainer.test``
+(p2pfl/learning/pytorch/lightning_learner.py:180-236) for the
+MNIST-shaped MLP family (mlp.py:53-69):
+
+* parameters live in a peer-mappable device arena (fp32 master) with a bf16
+  working copy and a bf16 transposed copy of each weight for the dgrad GEMM;
+* every Linear forward / dgrad / wgrad is the tcgen05 GEMM (``ops.gemm_tn``)
+  in swap-AB form (out-features ride the 128-row MMA dimension, the batch is
+  N), bias + ReLU + ReLU-mask + bias-gradient fused in its epilogue;
+* log-softmax + cross-entropy forward and backward are one kernel; Adam over
+  the whole arena (+ bf16 refresh) is one kernel;
+* the dataset is resident on the device, shuffled by one gather kernel per
+  epoch, and a whole epoch is ONE CUDA graph launch (no host work per step).
+
+Models without a fused spec fall back to eager autograd for forward/backward
+(``TorchLearner``) but keep the arena, so the gossip data plane is identical.
+"""
+
+from __future__ import annotations
+
+import threading
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+from torch import nn
+
+from p2pfl_b200 import ops
+from p2pfl_b200.learning.params import FlatParams
+from p2pfl_b200.learning.torch_learner import TorchLearner
+from p2pfl_b200.management.logger import logger
+from p2pfl_b200.parallel.arena import DeviceArena
+from p2pfl_b200.settings import Settings
+
+_capture_lock = threading.Lock()
+
+
+def _pad8(x: int) -> int:
+    return (x + 7) // 8 * 8
+
+
+class _LinearSpec:
+    def __init__(self, name: str, in_f: int, out_f: int, w_off: int, b_off: int) -> None:
+        self.name, self.in_f, self.out_f, self.w_off, self.b_off = name, in_f, out_f, w_off, b_off
+        self.wt_off = -1  # offset of the bf16 transposed copy, -1: not needed (first layer)
+
+
+class B200Learner(TorchLearner):
+    """``Node(model, data, learner=B200Learner)``; needs a CUDA device."""
+
+    def __init__(
+        self,
+        model: Any,
+        data: Any,
+        self_addr: str = "unknown-node",
+        epochs: int = 1,
+        device: Optional[str] = None,
+        data_mode: str = "resident",
+        inbox_slots: Optional[int] = None,
+    ) -> None:
+        if not torch.cuda.is_available():
+            raise RuntimeError("B200Learner needs a CUDA device; use TorchLearner on the host")
+        ops.lib()  # the kernel library is mandatory on this path
+        self.data_mode = data_mode  # "resident": upload the splits once; "stream": H2D from pinned memory every round
+        self.inbox_slots = inbox_slots or Settings.DEVICE_INBOX_SLOTS
+        self.arena: Optional[DeviceArena] = None
+        self.fused = False
+        self._layers: List[_LinearSpec] = []
+        self._graphs: Dict[Tuple[str, int], Any] = {}
+        self._train_dev: Optional[Tuple[torch.Tensor, torch.Tensor]] = None
+        self._eval_dev: Dict[str, Tuple[torch.Tensor, torch.Tensor]] = {}
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+        self.kernel_launches_per_epoch = 0
+        super().__init__(model, data, self_addr, epochs, device)
+        self.stream = torch.cuda.Stream(device=self.device)
+
+    # --------------------------------------------------------------- storage
+    def _alloc_flat(self, total: int) -> torch.Tensor:
+        if self.arena is not None:
+            self.arena.close()
+        self.arena = DeviceArena(
+            total,
+            slots=self.inbox_slots,
+            tile=Settings.DEVICE_TILE_ELEMS,
+            wire_bf16=(Settings.WIRE_DTYPE == "bf16"),
+            device=self.device.index or 0,
+        )
+        return self.arena.params
+
+    def set_model(self, model: Any) -> None:
+        super().set_model(model)
+        dev = self.device
+        n = self.layout.total
+        self.w16 = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+        self.grads = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.adam_m = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.adam_v = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.adam_step = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._graphs = {}
+        self._plan_fused()
+        self._params_written()
+
+    def _plan_fused(self) -> None:
+        """A model qualifies for the fully fused path when it is a plain stack of
+        ``nn.Linear`` layers with ReLU in between (the reference MLP)."""
+        self.fused = False
+        self._layers = []
+        if getattr(self.model, "fused_spec", None) != "mlp":
+            return
+        linears = [(n, m) for n, m in self.model.named_children() if isinstance(m, nn.Linear)]
+        if not linears or len(linears) != len(list(self.model.children())):
+            return
+        if int(getattr(self.data, "batch_size", 32)) % 8:
+            return  # the batch is the K dimension of the wgrad GEMM: 16-byte row pitch
+        prev_out = None
+        for name, lin in linears:
+            if lin.bias is None or (prev_out is not None and lin.in_features != prev_out):
+                return
+            if lin.in_features % 8:
+                return  # TMA needs 16-byte row pitch on the K-major weight
+            w = self.layout.by_name[f"{name}.weight"]
+            b = self.layout.by_name[f"{name}.bias"]
+            self._layers.append(_LinearSpec(name, lin.in_features, lin.out_features, w.offset, b.offset))
+            prev_out = lin.out_features
+        # transposed bf16 weights (for dgrad) of every layer but the first
+        off = 0
+        self._tdescs = []
+        for L in self._layers[1:]:
+            L.wt_off = off
+            ld = _pad8(L.out_f)
+            self._tdescs.append((L.w_off, off, L.out_f, L.in_f, ld))
+            off += L.in_f * ld
+        self.wT16 = torch.zeros(max(off, 8), dtype=torch.bfloat16, device=self.device)
+        self.fused = True
+
+    def _params_written(self) -> None:
+        """fp32 master changed from outside: refresh the bf16 working copies."""
+        if getattr(self, "w16", None) is None:
+            return
+        with torch.cuda.stream(self._s()):
+            ops.cast_f32_bf16(self.flat, self.w16)
+            if self.fused and self._tdescs:
+                ops.transpose_cast(self.flat, self.wT16, self._tdescs)
+
+    def _s(self) -> torch.cuda.Stream:
+        return getattr(self, "stream", None) or torch.cuda.current_stream(self.device)
+
+    def close(self) -> None:
+        self._graphs = {}
+        if self.arena is not None:
+            torch.cuda.synchronize(self.device)
+            # views into the arena must not outlive it
+            self.flat = None
+            self.arena.close()
+            self.arena = None
+
+    # ------------------------------------------------------------ parameters
+    def export_model(self) -> FlatParams:
+        with torch.cuda.stream(self._s()):
+            out = FlatParams(self.flat.detach().clone(), self.layout, self._extra())
+        self._s().synchronize()
+        return out
+
+    def set_parameters(self, params: Any) -> None:
+        with torch.cuda.stream(self._s()):
+            if isinstance(params, FlatParams) and params.flat.is_cuda:
+                # the producer may have written it on another stream
+                self._s().wait_stream(torch.cuda.current_stream(params.flat.device))
+            super().set_parameters(params)
+        self._s().synchronize()
+
+    # ------------------------------------------------------------------ data
+    def _upload(self, split: str) -> Tuple[torch.Tensor, torch.Tensor]:
+        x, y = self.data.pinned_tensors(split) if hasattr(self.data, "pinned_tensors") else self.data.tensors(split)
+        xd = x.reshape(x.shape[0], -1).to(self.device, non_blocking=True)
+        yd = y.to(self.device, non_blocking=True).to(torch.int32)  # int64 travels, the cast is on the device
+        self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+        return xd, yd
+
+    def _train_data(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        if self.data_mode == "stream" or self._train_dev is None:
+            if self._train_dev is not None and self.data_mode == "stream":
+                # same device buffers every round so captured graphs stay valid
+                x, y = self.data.pinned_tensors("train")
+                self._train_dev[0].copy_(x.reshape(x.shape[0], -1), non_blocking=True)
+                self._train_dev[1].copy_(y.to(self.device, non_blocking=True))
+                self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+            else:
+                self._train_dev = self._upload("train")
+        return self._train_dev
+
+    def _eval_data(self, split: str) -> Tuple[torch.Tensor, torch.Tensor]:
+        cur = self._eval_dev.get(split)
+        if cur is None:
+            self._eval_dev[split] = cur = self._upload(split)
+        elif self.data_mode == "stream":
+            x, y = self.data.pinned_tensors(split)
+            cur[0].copy_(x.reshape(x.shape[0], -1), non_blocking=True)
+            cur[1].copy_(y.to(self.device, non_blocking=True))
+            self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+        return cur
+
+    # --------------------------------------------------------- fused forward
+    def _forward(self, x16: torch.Tensor, ldx: int, bsz: int, act: Dict[str, Any], train: bool) -> None:
+        """Swap-AB forward through every layer: D[out, bsz] = W[out, in] . X[bsz, in]^T."""
+        Ls = self._layers
+        for li, L in enumerate(Ls):
+            last = li == len(Ls) - 1
+            A = self.w16[L.w_off :]
+            Bm, ldb = (x16, ldx) if li == 0 else (act["H"][li - 1], _pad8(L.in_f))
+            bias = self.flat[L.b_off :]
+            if last:
+                ops.gemm_tn(A, L.in_f, Bm, ldb, L.out_f, bsz, L.in_f, bias=bias, bias_per_row=True,
+                            out_f32_t=act["logits"], ld_f32_t=act["ld_logits"])  # fmt: skip
+            else:
+                ops.gemm_tn(A, L.in_f, Bm, ldb, L.out_f, bsz, L.in_f, bias=bias, bias_per_row=True, relu=True,
+                            out_bf16=act["HT"][li] if train else None, ld_bf16=act["ldB"],
+                            out_bf16_t=act["H"][li], ld_bf16_t=_pad8(L.out_f))  # fmt: skip
+
+    def _alloc_act(self, B: int, train: bool) -> Dict[str, Any]:
+        dev = self.device
+        Ls = self._layers
+        ldB = _pad8(B)
+        C = Ls[-1].out_f
+        act: Dict[str, Any] = {"ldB": ldB, "ld_logits": _pad8(C)}
+        act["H"] = [torch.zeros(B, _pad8(L.out_f), dtype=torch.bfloat16, device=dev) for L in Ls[:-1]]
+        act["logits"] = torch.zeros(B, _pad8(C), dtype=torch.float32, device=dev)
+        if train:
+            act["HT"] = [torch.zeros(L.out_f, ldB, dtype=torch.bfloat16, device=dev) for L in Ls[:-1]]
+            act["dZT"] = [torch.zeros(L.out_f, ldB, dtype=torch.bfloat16, device=dev) for L in Ls]
+            act["dZ"] = [torch.zeros(B, _pad8(L.out_f), dtype=torch.bfloat16, device=dev) for L in Ls]
+        return act
+
+    def _train_step(self, x16, xT16, y, bsz: int, act, loss_slot, step_offset: int, lr: float) -> None:
+        Ls = self._layers
+        nL = len(Ls)
+        feat = Ls[0].in_f
+        ldB = act["ldB"]
+        C = Ls[-1].out_f
+        self.grads.zero_()
+        self._forward(x16, feat, bsz, act, train=True)
+        ops.softmax_xent(act["logits"], act["ld_logits"], y, bsz, C, act["dZ"][-1], _pad8(C), act["dZT"][-1], ldB,
+                         self.grads[Ls[-1].b_off :], loss_slot)  # fmt: skip
+        for li in range(nL - 1, -1, -1):
+            L = Ls[li]
+            # wgrad: dW[out, in] = dZ^T[out, bsz] . (X^T[in, bsz])^T   (K = batch)
+            Bm = xT16 if li == 0 else act["HT"][li - 1]
+            ops.gemm_tn(act["dZT"][li], ldB, Bm, ldB, L.out_f, L.in_f, bsz,
+                        out_f32=self.grads[L.w_off :], ld_f32=L.in_f)  # fmt: skip
+            if li > 0:
+                # dgrad: dH^T[in, bsz] = W^T[in, out] . dZ[bsz, out]^T, masked by ReLU, bias grad = row sums
+                P = Ls[li - 1]
+                ops.gemm_tn(self.wT16[L.wt_off :], _pad8(L.out_f), act["dZ"][li], _pad8(L.out_f), L.in_f, bsz, L.out_f,
+                            mask=act["HT"][li - 1], ld_mask=ldB,
+                            out_bf16=act["dZT"][li - 1], ld_bf16=ldB,
+                            out_bf16_t=act["dZ"][li - 1] if li - 1 > 0 else None, ld_bf16_t=_pad8(P.out_f),
+                            rowsum=self.grads[P.b_off :])  # fmt: skip
+        ops.adam_step(self.flat, self.grads, self.adam_m, self.adam_v, self.w16, lr, self.adam_step, step_offset)
+        if self._tdescs:
+            ops.transpose_cast(self.flat, self.wT16, self._tdescs)
+
+    def debug_single_step(self, x: torch.Tensor, y: torch.Tensor) -> float:
+        """One eager (un-graphed) fused step on the given batch; returns the mean loss.
+        Test hook: leaves the gradients in ``self.grads``."""
+        B = x.shape[0]
+        feat = self._layers[0].in_f
+        with torch.cuda.stream(self._s()):
+            xf = x.reshape(B, -1).to(self.device, torch.float32).contiguous()
+            yi = y.to(self.device).to(torch.int32)
+            xs = torch.zeros(B, feat, dtype=torch.bfloat16, device=self.device)
+            xsT = torch.zeros(1, feat, _pad8(B), dtype=torch.bfloat16, device=self.device)
+            ys = torch.zeros(B, dtype=torch.int32, device=self.device)
+            ops.gather_rows(xf, None, B, feat, _pad8(B), xs, xsT, yi, ys)
+            act = self._alloc_act(B, train=True)
+            loss = torch.zeros(1, dtype=torch.float32, device=self.device)
+            self._train_step(xs, xsT[0], ys, B, act, loss, 1, float(getattr(self.model, "lr", 1e-3)))
+            ops.add_i32(self.adam_step, 1)
+        self._s().synchronize()
+        return float(loss) / B
+
+    # ------------------------------------------------------------ epoch graph
+    def _build_epoch(self, n: int, B: int) -> Dict[str, Any]:
+        """Capture one whole epoch (gather + every step) as a single CUDA graph."""
+        dev = self.device
+        feat = self._layers[0].in_f
+        nb = (n + B - 1) // B
+        x, y = self._train_dev
+        ep: Dict[str, Any] = {"n": n, "B": B, "nb": nb}
+        ep["perm"] = torch.arange(n, dtype=torch.int32, device=dev)
+        ep["xs"] = torch.zeros(nb * B, feat, dtype=torch.bfloat16, device=dev)
+        ep["xsT"] = torch.zeros(nb, feat, _pad8(B), dtype=torch.bfloat16, device=dev)
+        ep["ys"] = torch.zeros(nb * B, dtype=torch.int32, device=dev)
+        ep["loss"] = torch.zeros(nb, dtype=torch.float32, device=dev)
+        ep["act"] = self._alloc_act(B, train=True)
+        lr = float(getattr(self.model, "lr", 1e-3))
+
+        def body() -> None:
+            ep["loss"].zero_()
+            ops.gather_rows(x, ep["perm"], n, feat, _pad8(B), ep["xs"], ep["xsT"], y, ep["ys"])
+            for i in range(nb):
+                bsz = min(B, n - i * B)
+                self._train_step(ep["xs"][i * B :], ep["xsT"][i], ep["ys"][i * B :], bsz, ep["act"],
+                                 ep["loss"][i:], i + 1, lr)  # fmt: skip
+            ops.add_i32(self.adam_step, nb)
+
+        # warm-up outside capture (first-use attribute calls, lazy driver entry points)
+        before = ops.launch_count()
+        saved = [t.clone() for t in (self.flat, self.adam_m, self.adam_v, self.adam_step, self.w16, self.wT16)]
+        body()
+        for t, s in zip((self.flat, self.adam_m, self.adam_v, self.adam_step, self.w16, self.wT16), saved):
+            t.copy_(s)
+        ep["launches"] = ops.launch_count() - before
+        self._s().synchronize()
+        g = torch.cuda.CUDAGraph()
+        with _capture_lock:
+            with torch.cuda.graph(g, stream=self._s(), capture_error_mode="thread_local"):
+                body()
+        ep["graph"] = g
+        return ep
+
+    def fit(self) -> None:
+        if self.epochs <= 0 or self.model is None:
+            return
+        if not self.fused:
+            with torch.cuda.stream(self._s()):
+                super().fit()
+                self._params_written()
+            self._s().synchronize()
+            return
+        self._interrupt.clear()
+        B = int(getattr(self.data, "batch_size", 32))
+        with torch.cuda.stream(self._s()):
+            x, _ = self._train_data()
+            n = x.shape[0]
+            key = ("epoch", n * 100003 + B)
+            if key not in self._graphs:
+                self._graphs[key] = self._build_epoch(n, B)
+            ep = self._graphs[key]
+            if Settings.RESET_OPTIMIZER_EACH_ROUND:
+                # the reference builds a fresh Trainer (=> fresh Adam) per round (Q16)
+                self.adam_m.zero_()
+                self.adam_v.zero_()
+                self.adam_step.zero_()
+            for e in range(self.epochs):
+                if self._interrupt.is_set():
+                    logger.info(self.addr, "fit interrupted")
+                    break
+                ep["perm"].copy_(torch.randperm(n, device=self.device).to(torch.int32))
+                ep["graph"].replay()
+                ops.add_launches(ep["launches"])
+                self.kernel_launches_per_epoch = ep["launches"]
+                # per-epoch validation, as Lightning does for the reference (mlp.py:82-91)
+                val = self._eval_split("val")
+                if val is not None:
+                    logger.log_metric(self.addr, "val_loss", val[0], step=(e + 1) * ep["nb"])
+                    logger.log_metric(self.addr, "val_metric", val[1], step=(e + 1) * ep["nb"])
+            losses = ep["loss"].cpu()  # one D2H per fit
+            self.d2h_bytes += losses.numel() * 4
+        sizes = [min(B, n - i * B) for i in range(ep["nb"])]
+        for i in range(0, ep["nb"], self.LOG_EVERY):
+            logger.log_metric(self.addr, "train_loss", float(losses[i]) / sizes[i], step=i)
+        self._round_steps = ep["nb"] * self.epochs
+
+    # -------------------------------------------------------------- evaluate
+    def _build_eval(self, split: str, n: int) -> Dict[str, Any]:
+        dev = self.device
+        feat = self._layers[0].in_f
+        C = self._layers[-1].out_f
+        x, y = self._eval_dev[split]
+        ev: Dict[str, Any] = {"n": n}
+        ev["x16"] = torch.zeros(n, feat, dtype=torch.bfloat16, device=dev)
+        ev["act"] = self._alloc_act(n, train=False)
+        ev["loss"] = torch.zeros(1, dtype=torch.float32, device=dev)
+        ev["correct"] = torch.zeros(1, dtype=torch.int32, device=dev)
+        ev["out"] = torch.zeros(2, dtype=torch.float32, device=dev)
+
+        def body() -> None:
+            ev["loss"].zero_()
+            ev["correct"].zero_()
+            ops.gather_rows(x, None, n, feat, 8, ev["x16"])
+            self._forward(ev["x16"], feat, n, ev["act"], train=False)
+            ops.eval_reduce(ev["act"]["logits"], ev["act"]["ld_logits"], y, n, C, ev["loss"], ev["correct"])
+            ev["out"][0].copy_(ev["loss"][0])
+            ev["out"][1].copy_(ev["correct"][0])
+
+        before = ops.launch_count()
+        body()
+        ev["launches"] = ops.launch_count() - before
+        self._s().synchronize()
+        g = torch.cuda.CUDAGraph()
+        with _capture_lock:
+            with torch.cuda.graph(g, stream=self._s(), capture_error_mode="thread_local"):
+                body()
+        ev["graph"] = g
+        return ev
+
+    def _eval_split(self, split: str) -> Optional[Tuple[float, float]]:
+        """(mean loss, accuracy) of the live model on a split: one graph launch, one 8-byte D2H."""
+        x, _ = self._eval_data(split)
+        n = x.shape[0]
+        if n == 0:
+            return None
+        key = ("eval:" + split, n)
+        if key not in self._graphs:
+            self._graphs[key] = self._build_eval(split, n)
+        ev = self._graphs[key]
+        ev["graph"].replay()
+        ops.add_launches(ev["launches"])
+        res = ev["out"].cpu()
+        self.d2h_bytes += 8
+        return float(res[0]) / n, float(res[1]) / n
+
+    def evaluate(self) -> Dict[str, float]:
+        if self.epochs <= 0 or self.model is None:
+            return {}
+        if not self.fused:
+            with torch.cuda.stream(self._s()):
+                return super().evaluate()
+        with torch.cuda.stream(self._s()):
+            res = self._eval_split("test")
+        if res is None:
+            return {}
+        out = {"test_loss": res[0], "test_metric": res[1]}
+        for k, v in out.items():
+            logger.log_metric(self.addr, k, v)
+        return out

@@ -69,7 +69,7 @@ class TorchLearner(NodeLearner):
         self.model = model.to(self.device)
         sd = self.model.state_dict()
         self.layout = ParamLayout.from_state_dict(sd)
-        self.flat = torch.zeros(self.layout.total, dtype=torch.float32, device=self.device)
+        self.flat = self._alloc_flat(self.layout.total)
         views = self.layout.views(self.flat)
         with torch.no_grad():
             for name, t in sd.items():
@@ -85,6 +85,13 @@ class TorchLearner(NodeLearner):
             if name in views and b.dtype == torch.float32:
                 b.data = views[name]
         self._optimizer = None
+
+    def _alloc_flat(self, total: int) -> torch.Tensor:
+        """Storage of the flat parameter vector (subclasses place it in a device arena)."""
+        return torch.zeros(total, dtype=torch.float32, device=self.device)
+
+    def _params_written(self) -> None:
+        """Hook: the flat vector was overwritten from outside (set_parameters / aggregation)."""
 
     def set_data(self, data: Any) -> None:
         self.data = data
@@ -190,6 +197,7 @@ class TorchLearner(NodeLearner):
                 sd = self.model.state_dict()
                 for k, v in extra.items():
                     sd[k].copy_(v.to(sd[k].device))
+        self._params_written()
 
     # -------------------------------------------------------------- training
     def _make_optimizer(self) -> torch.optim.Optimizer:
@@ -229,20 +237,25 @@ class TorchLearner(NodeLearner):
                 if step % self.LOG_EVERY == 0:
                     logger.log_metric(self.addr, "train_loss", float(loss.detach()), step=step)
                 step += 1
+            # per-epoch validation, as Lightning does for the reference (mlp.py:82-91)
+            val = self._score(self.data.val_dataloader()) if hasattr(self.data, "val_dataloader") else None
+            if val is not None:
+                logger.log_metric(self.addr, "val_loss", val[0], step=step)
+                logger.log_metric(self.addr, "val_metric", val[1], step=step)
+            self.model.train()
         self._round_steps = step
 
     def interrupt_fit(self) -> None:
         self._interrupt.set()
 
     @torch.no_grad()
-    def evaluate(self) -> Dict[str, float]:
-        if self.epochs <= 0 or self.model is None:
-            return {}
+    def _score(self, loader: Any) -> Optional[Tuple[float, float]]:
+        """(mean loss, accuracy) over a loader; None when it is empty."""
         self.model.eval()
         loss_sum = torch.zeros((), device=self.device)
         correct = torch.zeros((), device=self.device)
         count = 0
-        for x, y in self.data.test_dataloader():
+        for x, y in loader:
             x = x.to(self.device, non_blocking=True)
             y = y.to(self.device, non_blocking=True)
             logits = self.model(x)
@@ -252,8 +265,16 @@ class TorchLearner(NodeLearner):
             correct += (logits.argmax(dim=1) == y).sum()
             count += y.numel()
         if count == 0:
+            return None
+        return float(loss_sum) / count, float(correct) / count
+
+    def evaluate(self) -> Dict[str, float]:
+        if self.epochs <= 0 or self.model is None:
             return {}
-        out = {"test_loss": float(loss_sum) / count, "test_metric": float(correct) / count}
+        res = self._score(self.data.test_dataloader())
+        if res is None:
+            return {}
+        out = {"test_loss": res[0], "test_metric": res[1]}
         for k, v in out.items():
             logger.log_metric(self.addr, k, v)
         return out

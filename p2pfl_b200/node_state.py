@@ -41,6 +41,9 @@ class NodeState:
         self.pending_init: Optional[Callable[[], None]] = None
         self.pending_models: List[Any] = []
 
+        # observers of round boundaries: fn(rounds_completed), called on the learning thread
+        self.round_listeners: List[Callable[[int], None]] = []
+
         # one condition for "something changed" - all waits are predicate waits
         self.changed = threading.Condition()
         self.start_thread_lock = threading.Lock()
@@ -85,6 +88,8 @@ class NodeState:
         for r in [r for r in self.train_set_votes if r < self.round]:
             del self.train_set_votes[r]
         self.notify()
+        for fn in list(self.round_listeners):
+            fn(self.round)
 
     def clear(self) -> None:
         """Back to idle (reference: node_state.py:110-115, plus Q19 full reset)."""

@@ -1,0 +1,408 @@
+"""Python bindings of the sm_100a kernel library (``lib/libp2pfl_b200.so``).
+
+The library exposes a plain C ABI (``include/p2pfl_b200.h``) and is loaded with
+``ctypes``; tensors are passed as raw device pointers and the launch goes on
+the *current torch stream*, so kernels compose with torch ops, CUDA events and
+CUDA-graph capture.  There is no fallback: on a machine with a GPU a missing
+library is an error, never a silent eager path.
+
+``launch_count()`` reports how many of this library's kernels were launched
+from Python (graph replays add their node count) - bench.py's ``gpu_launches``.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+from typing import List, Optional, Sequence
+
+import torch
+
+from p2pfl_b200.exceptions import ExtensionMissingError
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lib", "libp2pfl_b200.so")
+_lib: Optional[C.CDLL] = None
+_lock = threading.Lock()
+_launches = 0
+
+MAX_PEERS = 16
+MAX_MODELS = 16
+
+
+# --------------------------------------------------------------------- structs
+class GemmArgs(C.Structure):
+    _fields_ = [
+        ("A", C.c_void_p), ("lda", C.c_int32),
+        ("B", C.c_void_p), ("ldb", C.c_int32),
+        ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32),
+        ("bias", C.c_void_p), ("bias_per_row", C.c_int32),
+        ("relu", C.c_int32),
+        ("mask", C.c_void_p), ("ld_mask", C.c_int32),
+        ("out_f32", C.c_void_p), ("ld_f32", C.c_int32),
+        ("out_bf16", C.c_void_p), ("ld_bf16", C.c_int32),
+        ("out_f32_t", C.c_void_p), ("ld_f32_t", C.c_int32),
+        ("out_bf16_t", C.c_void_p), ("ld_bf16_t", C.c_int32),
+        ("rowsum", C.c_void_p),
+        ("alpha", C.c_float),
+    ]  # fmt: skip
+
+
+class PushTable(C.Structure):
+    _fields_ = [
+        ("inbox", C.c_void_p * MAX_PEERS),
+        ("flags", C.c_void_p * MAX_PEERS),
+        ("n_peers", C.c_int32),
+        ("wire_bf16", C.c_int32),
+    ]
+
+
+class ReduceTable(C.Structure):
+    _fields_ = [
+        ("slot", C.c_void_p * MAX_PEERS),
+        ("flags", C.c_void_p * MAX_PEERS),
+        ("weight", C.c_float * MAX_PEERS),
+        ("n_slots", C.c_int32),
+        ("self_pos", C.c_int32),
+        ("self_weight", C.c_float),
+        ("wire_bf16", C.c_int32),
+        ("round_self", C.c_int32),
+        ("pad_", C.c_int32),
+    ]
+
+
+class TransposeDesc(C.Structure):
+    _fields_ = [
+        ("src_off", C.c_uint64),
+        ("dst_off", C.c_uint64),
+        ("rows", C.c_int32),
+        ("cols", C.c_int32),
+        ("ld_t", C.c_int32),
+        ("pad_", C.c_int32),
+    ]
+
+
+# ---------------------------------------------------------------------- loader
+def library_path() -> str:
+    return _LIB_PATH
+
+
+def available() -> bool:
+    return os.path.exists(_LIB_PATH)
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(_LIB_PATH):
+                    raise ExtensionMissingError(
+                        f"{_LIB_PATH} is missing - build it with `python build.py` (see __graft_entry__.build)"
+                    )
+                l = C.CDLL(_LIB_PATH)
+                l.p2pfl_last_error.restype = C.c_char_p
+                _lib = l
+    return _lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        msg = lib().p2pfl_last_error().decode(errors="replace")
+        raise RuntimeError(f"p2pfl_b200 kernel library error {rc}: {msg}")
+
+
+def _stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _dev(t: torch.Tensor) -> int:
+    return t.device.index if t.device.index is not None else torch.cuda.current_device()
+
+
+def _p(t: Optional[torch.Tensor]) -> C.c_void_p:
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _count(n: int = 1) -> None:
+    global _launches
+    _launches += n
+
+
+def launch_count() -> int:
+    return _launches
+
+
+def add_launches(n: int) -> None:
+    """Account for kernels replayed from a CUDA graph."""
+    _count(n)
+
+
+# ------------------------------------------------------------------ optimizers
+def adam_step(
+    p: torch.Tensor,
+    g: torch.Tensor,
+    m: torch.Tensor,
+    v: torch.Tensor,
+    p_bf16: Optional[torch.Tensor],
+    lr: float,
+    step_ptr: Optional[torch.Tensor],
+    step_offset: int,
+    beta1: float = 0.9,
+    beta2: float = 0.999,
+    eps: float = 1e-8,
+    weight_decay: float = 0.0,
+) -> None:
+    _check(
+        lib().p2pfl_adam_step(
+            _dev(p), _stream(), _p(p), _p(g), _p(m), _p(v), _p(p_bf16), C.c_uint64(p.numel()),
+            C.c_float(lr), C.c_float(beta1), C.c_float(beta2), C.c_float(eps), C.c_float(weight_decay),
+            _p(step_ptr), C.c_int32(step_offset),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def sgd_step(p, g, mom, p_bf16, lr: float, momentum: float = 0.0) -> None:
+    _check(
+        lib().p2pfl_sgd_step(
+            _dev(p), _stream(), _p(p), _p(g), _p(mom), _p(p_bf16), C.c_uint64(p.numel()), C.c_float(lr), C.c_float(momentum)
+        )
+    )
+    _count()
+
+
+def add_i32(t: torch.Tensor, delta: int) -> None:
+    _check(lib().p2pfl_add_i32(_dev(t), _stream(), _p(t), C.c_int32(delta)))
+    _count()
+
+
+def cast_f32_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
+    _check(lib().p2pfl_cast_f32_bf16(_dev(src), _stream(), _p(src), _p(dst), C.c_uint64(src.numel())))
+    _count()
+
+
+def transpose_cast(src: torch.Tensor, dst: torch.Tensor, descs: Sequence[tuple]) -> None:
+    """descs: (src_off, dst_off, rows, cols, ld_t) per matrix, at most 16 per call."""
+    for i in range(0, len(descs), 16):
+        chunk = descs[i : i + 16]
+        arr = (TransposeDesc * len(chunk))()
+        for j, (so, do, r, c, ld) in enumerate(chunk):
+            arr[j] = TransposeDesc(so, do, r, c, ld, 0)
+        _check(lib().p2pfl_transpose_cast(_dev(src), _stream(), _p(src), _p(dst), arr, C.c_int(len(chunk))))
+        _count()
+
+
+# ---------------------------------------------------------------------- losses
+def softmax_xent(
+    logits: torch.Tensor,
+    ld_logits: int,
+    labels: torch.Tensor,
+    B: int,
+    Cn: int,
+    dlogits: Optional[torch.Tensor],
+    ld_d: int,
+    dlogits_t: Optional[torch.Tensor],
+    ld_dt: int,
+    dbias: Optional[torch.Tensor],
+    loss_sum: Optional[torch.Tensor],
+) -> None:
+    _check(
+        lib().p2pfl_softmax_xent(
+            _dev(logits), _stream(), _p(logits), C.c_int(ld_logits), _p(labels), C.c_int(B), C.c_int(Cn),
+            _p(dlogits), C.c_int(ld_d), _p(dlogits_t), C.c_int(ld_dt), _p(dbias), _p(loss_sum),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def eval_reduce(logits: torch.Tensor, ld_logits: int, labels: torch.Tensor, B: int, Cn: int, loss_sum, correct) -> None:
+    _check(
+        lib().p2pfl_eval_reduce(
+            _dev(logits), _stream(), _p(logits), C.c_int(ld_logits), _p(labels), C.c_int(B), C.c_int(Cn), _p(loss_sum), _p(correct)
+        )
+    )
+    _count()
+
+
+# ---------------------------------------------------------------------- FedAvg
+def fedavg_into(
+    models: List[torch.Tensor], weights: List[float], out_f32: Optional[torch.Tensor], out_bf16: Optional[torch.Tensor]
+) -> None:
+    """out = sum_i weights[i] * models[i]; at most 16 models per launch (longer
+    lists are folded: the partial result re-enters with weight 1)."""
+    n = models[0].numel()
+    dev = _dev(models[0])
+    models, weights = list(models), list(weights)
+    while models:
+        k = min(len(models), MAX_MODELS)
+        last = k == len(models)
+        ptrs = (C.c_void_p * k)(*[m.data_ptr() for m in models[:k]])
+        ws = (C.c_float * k)(*weights[:k])
+        isb = (C.c_int32 * k)(*[1 if m.dtype == torch.bfloat16 else 0 for m in models[:k]])
+        tmp = out_f32 if (out_f32 is not None) else torch.empty(n, dtype=torch.float32, device=models[0].device)
+        _check(
+            lib().p2pfl_fedavg(dev, _stream(), C.c_int(k), ptrs, ws, isb, _p(tmp), _p(out_bf16 if last else None), C.c_uint64(n))
+        )
+        _count()
+        if last:
+            break
+        models = [tmp] + models[k:]
+        weights = [1.0] + weights[k:]
+
+
+def fedavg_flat(models: List[torch.Tensor], weights: List[float], out_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    out = torch.empty(models[0].numel(), dtype=torch.float32, device=models[0].device)
+    fedavg_into(models, weights, out, None)
+    return out if out_dtype == torch.float32 else out.to(out_dtype)
+
+
+# ------------------------------------------------------------------------ GEMM
+def gemm_tn(
+    A: torch.Tensor, lda: int, B: torch.Tensor, ldb: int, M: int, N: int, K: int,
+    bias: Optional[torch.Tensor] = None, bias_per_row: bool = True, relu: bool = False,
+    mask: Optional[torch.Tensor] = None, ld_mask: int = 0,
+    out_f32: Optional[torch.Tensor] = None, ld_f32: int = 0,
+    out_bf16: Optional[torch.Tensor] = None, ld_bf16: int = 0,
+    out_f32_t: Optional[torch.Tensor] = None, ld_f32_t: int = 0,
+    out_bf16_t: Optional[torch.Tensor] = None, ld_bf16_t: int = 0,
+    rowsum: Optional[torch.Tensor] = None, alpha: float = 1.0,
+) -> None:  # fmt: skip
+    """D[M,N] = alpha * A[M,K] @ B[N,K]^T with the fused epilogue (tcgen05 kernel)."""
+    a = GemmArgs(
+        A.data_ptr(), lda, B.data_ptr(), ldb, M, N, K,
+        0 if bias is None else bias.data_ptr(), int(bias_per_row), int(relu),
+        0 if mask is None else mask.data_ptr(), ld_mask,
+        0 if out_f32 is None else out_f32.data_ptr(), ld_f32,
+        0 if out_bf16 is None else out_bf16.data_ptr(), ld_bf16,
+        0 if out_f32_t is None else out_f32_t.data_ptr(), ld_f32_t,
+        0 if out_bf16_t is None else out_bf16_t.data_ptr(), ld_bf16_t,
+        0 if rowsum is None else rowsum.data_ptr(), alpha,
+    )  # fmt: skip
+    _check(lib().p2pfl_gemm_tn(_dev(A), _stream(), C.byref(a)))
+    _count()
+
+
+# ---------------------------------------------------------------- data movement
+def gather_rows(src, perm, n_rows: int, feat: int, batch: int, dst, dst_t=None, labels_src=None, labels_dst=None) -> None:
+    _check(
+        lib().p2pfl_gather_rows(
+            _dev(src), _stream(), _p(src), _p(perm), C.c_int(n_rows), C.c_int(feat), C.c_int(batch),
+            _p(dst), _p(dst_t), _p(labels_src), _p(labels_dst),
+        )
+    )  # fmt: skip
+    _count()
+
+
+# ---------------------------------------------------------------------- gossip
+def make_push_table(inbox_ptrs: Sequence[int], flag_ptrs: Sequence[int], wire_bf16: bool) -> PushTable:
+    if len(inbox_ptrs) > MAX_PEERS:
+        raise ValueError(f"at most {MAX_PEERS} peers per push")
+    t = PushTable()
+    for i, (a, f) in enumerate(zip(inbox_ptrs, flag_ptrs)):
+        t.inbox[i] = a
+        t.flags[i] = f
+    t.n_peers = len(inbox_ptrs)
+    t.wire_bf16 = int(wire_bf16)
+    return t
+
+
+def make_reduce_table(
+    slot_ptrs: Sequence[int], flag_ptrs: Sequence[int], weights: Sequence[float], self_pos: int, self_weight: float,
+    wire_bf16: bool, round_self: bool = True,
+) -> ReduceTable:  # fmt: skip
+    if len(slot_ptrs) > MAX_PEERS:
+        raise ValueError(f"at most {MAX_PEERS} contributors per reduce")
+    t = ReduceTable()
+    for i, (a, f, w) in enumerate(zip(slot_ptrs, flag_ptrs, weights)):
+        t.slot[i] = a
+        t.flags[i] = f
+        t.weight[i] = w
+    t.n_slots = len(slot_ptrs)
+    t.self_pos = self_pos
+    t.self_weight = self_weight
+    t.wire_bf16 = int(wire_bf16)
+    t.round_self = int(round_self)
+    return t
+
+
+def gossip_push(src: torch.Tensor, tile: int, seq: int, table: PushTable) -> None:
+    _check(lib().p2pfl_gossip_push(_dev(src), _stream(), _p(src), C.c_uint64(src.numel()), C.c_uint32(tile), C.c_uint32(seq), C.byref(table)))
+    _count()
+
+
+def gossip_reduce(params, params_bf16, tile: int, seq: int, table: ReduceTable, abort_flag=None, timeout_cycles: int = 0, status=None) -> None:
+    _check(
+        lib().p2pfl_gossip_reduce(
+            _dev(params), _stream(), _p(params), _p(params_bf16), C.c_uint64(params.numel()), C.c_uint32(tile), C.c_uint32(seq),
+            C.byref(table), _p(abort_flag), C.c_uint64(timeout_cycles), _p(status),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def gossip_fused(params, params_bf16, tile: int, seq: int, push: PushTable, reduce: ReduceTable, abort_flag=None, timeout_cycles: int = 0, status=None) -> None:
+    _check(
+        lib().p2pfl_gossip_fused(
+            _dev(params), _stream(), _p(params), _p(params_bf16), C.c_uint64(params.numel()), C.c_uint32(tile), C.c_uint32(seq),
+            C.byref(push), C.byref(reduce), _p(abort_flag), C.c_uint64(timeout_cycles), _p(status),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def gossip_fused_emulated(params: List[torch.Tensor], tile: int, seq: int, push_dev: torch.Tensor, reduce_dev: torch.Tensor, timeout_cycles: int, status: torch.Tensor) -> None:
+    """Single-GPU emulation of ``len(params)`` ranks; ``push_dev`` / ``reduce_dev`` are
+    uint8 device tensors holding the packed tables of all ranks."""
+    r = len(params)
+    ptrs = (C.c_void_p * r)(*[p.data_ptr() for p in params])
+    _check(
+        lib().p2pfl_gossip_fused_emulated(
+            _dev(params[0]), _stream(), C.c_int(r), ptrs, C.c_uint64(params[0].numel()), C.c_uint32(tile), C.c_uint32(seq),
+            _p(push_dev), _p(reduce_dev), C.c_uint64(timeout_cycles), _p(status),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def tables_to_device(tables: Sequence[C.Structure], device: torch.device) -> torch.Tensor:
+    raw = b"".join(bytes(t) for t in tables)
+    return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(device)
+
+
+# --------------------------------------------------------------------- runtime
+def rt_alloc(device: int, nbytes: int) -> int:
+    out = C.c_void_p()
+    _check(lib().p2pfl_rt_alloc(C.c_int(device), C.c_uint64(nbytes), C.byref(out)))
+    return int(out.value)
+
+
+def rt_free(device: int, ptr: int) -> None:
+    _check(lib().p2pfl_rt_free(C.c_int(device), C.c_void_p(ptr)))
+
+
+def rt_ipc_export(device: int, ptr: int) -> bytes:
+    buf = (C.c_uint8 * 64)()
+    _check(lib().p2pfl_rt_ipc_export(C.c_int(device), C.c_void_p(ptr), buf))
+    return bytes(buf)
+
+
+def rt_ipc_open(device: int, handle: bytes) -> int:
+    out = C.c_void_p()
+    buf = (C.c_uint8 * 64)(*handle)
+    _check(lib().p2pfl_rt_ipc_open(C.c_int(device), buf, C.byref(out)))
+    return int(out.value)
+
+
+def rt_ipc_close(device: int, ptr: int) -> None:
+    _check(lib().p2pfl_rt_ipc_close(C.c_int(device), C.c_void_p(ptr)))
+
+
+def rt_enable_peer(device: int, peer: int) -> None:
+    _check(lib().p2pfl_rt_enable_peer(C.c_int(device), C.c_int(peer)))
+
+
+def rt_can_access_peer(device: int, peer: int) -> bool:
+    out = C.c_int()
+    _check(lib().p2pfl_rt_can_access_peer(C.c_int(device), C.c_int(peer), C.byref(out)))
+    return bool(out.value)

@@ -67,6 +67,8 @@ class Settings:
     """Wire dtype of the device data plane: 'bf16' (inbox mode B) or 'fp32'."""
     DEVICE_TILE_ELEMS: int = 16384
     """Elements per data-plane tile (one arrival flag per tile)."""
+    DEVICE_INBOX_SLOTS: int = 8
+    """Inbox slots per arena = the largest train set the data plane can serve."""
     TRAINER_DIFFUSION_GRACE: float = 0.5
     """Seconds a finished node waits before spending a full-model transfer on a
     train-set peer that has not yet announced ``models_ready``."""

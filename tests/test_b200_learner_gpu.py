@@ -1,0 +1,138 @@
+"""The fused sm_100a learner against eager fp32 PyTorch."""
+
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _dm(n_train=640, n_test=128, **kw):
+    from p2pfl_b200.learning.data import MnistFederatedDM
+
+    return MnistFederatedDM(0, 1, n_train=n_train, n_test=n_test, **kw)
+
+
+def test_single_step_gradients_match_autograd():
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.models import MLP
+
+    torch.manual_seed(0)
+    model = MLP(seed=0)
+    ref = copy.deepcopy(model).to(DEV)
+    learner = B200Learner(model, _dm(), "t", epochs=1, device=DEV)
+    assert learner.fused
+    x, y = _dm().tensors("train")
+    x, y = x[:32], y[:32]
+    before = learner.flat.clone()
+    loss = learner.debug_single_step(x, y)
+    # reference: fp32 autograd on the same bf16-rounded weights and inputs
+    with torch.no_grad():
+        for p in ref.parameters():
+            p.copy_(p.to(torch.bfloat16).float()) if p.dim() == 2 else None
+    xr = x.reshape(32, -1).to(DEV).to(torch.bfloat16).float()
+    out = ref(xr)
+    ref_loss = F.cross_entropy(out, y.to(DEV))
+    ref_loss.backward()
+    assert abs(loss - float(ref_loss)) < 2e-2 * max(1.0, float(ref_loss))
+    views = learner.layout.views(learner.grads)
+    for name, p in ref.named_parameters():
+        g, gr = views[name], p.grad
+        rel = (g - gr).norm() / (gr.norm() + 1e-12)
+        assert rel < 3e-2, f"{name}: relative gradient error {float(rel):.4f}"
+    # Adam moved the parameters, the bf16 copies follow the master
+    assert not torch.equal(before, learner.flat)
+    assert torch.equal(learner.w16, learner.flat.to(torch.bfloat16))
+    L2 = learner._layers[1]
+    w2 = learner.layout.views(learner.flat)["l2.weight"]
+    wt = learner.wT16[L2.wt_off : L2.wt_off + L2.in_f * 128].view(L2.in_f, 128)
+    assert torch.equal(wt, w2.t().to(torch.bfloat16))
+    learner.close()
+
+
+def test_fit_and_evaluate_graphs():
+    from p2pfl_b200 import ops
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.learning.torch_learner import TorchLearner
+    from p2pfl_b200.models import MLP
+
+    dm = _dm(n_train=1000, n_test=250, noise=6.0)  # 900 train samples: last batch is partial (4)
+    learner = B200Learner(MLP(seed=1), dm, "t", epochs=2, device=DEV)
+    oracle = TorchLearner(MLP(seed=1), dm, "o", epochs=2, device=DEV)
+    r0, o0 = learner.evaluate(), oracle.evaluate()
+    assert abs(r0["test_loss"] - o0["test_loss"]) < 3e-2
+    assert abs(r0["test_metric"] - o0["test_metric"]) < 0.05
+    n0 = ops.launch_count()
+    learner.fit()
+    oracle.fit()
+    assert ops.launch_count() - n0 >= 2 * learner.kernel_launches_per_epoch > 0
+    r1, o1 = learner.evaluate(), oracle.evaluate()
+    assert r1["test_loss"] < r0["test_loss"]
+    assert abs(r1["test_loss"] - o1["test_loss"]) < 0.15 * max(o1["test_loss"], 0.1)
+    # second round reuses the captured graphs
+    learner.fit()
+    r2 = learner.evaluate()
+    assert r2["test_loss"] <= r1["test_loss"] * 1.5
+    learner.close()
+
+
+def test_wire_roundtrip_and_set_parameters():
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.models import MLP
+
+    a = B200Learner(MLP(seed=1), _dm(), "a", epochs=1, device=DEV)
+    b = B200Learner(MLP(seed=2), _dm(), "b", epochs=1, device=DEV)
+    enc = a.encode_parameters()
+    b.set_parameters(b.decode_parameters(enc))
+    assert b.encode_parameters() == enc
+    assert torch.equal(b.w16, a.w16)
+    assert torch.equal(b.wT16, a.wT16)
+    # evaluation after a parameter swap uses the new weights
+    assert a.evaluate() == b.evaluate()
+    a.close()
+    b.close()
+
+
+def test_non_fused_model_falls_back_to_autograd():
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.models import CNN
+
+    dm = _dm(n_train=320, n_test=64)
+    learner = B200Learner(CNN(seed=0), dm, "c", epochs=1, device=DEV)
+    assert not learner.fused
+    r0 = learner.evaluate()
+    learner.fit()
+    r1 = learner.evaluate()
+    assert r1["test_loss"] < r0["test_loss"]
+    assert torch.equal(learner.w16, learner.flat.to(torch.bfloat16))
+    learner.close()
+
+
+def test_federation_on_gpu_in_memory():
+    """Two nodes with the fused learner on one GPU, in-memory control plane, host wire."""
+    from p2pfl_b200.communication.memory import InMemoryCommunicationProtocol
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.learning.data import MnistFederatedDM
+    from p2pfl_b200.models import MLP
+    from p2pfl_b200.node import Node
+    from p2pfl_b200.utils import check_equal_models, wait_4_results, wait_convergence
+
+    nodes = [
+        Node(MLP(), MnistFederatedDM(i, 2, n_train=1280, n_test=256), protocol=InMemoryCommunicationProtocol,
+             learner=B200Learner, device=DEV)
+        for i in range(2)
+    ]  # fmt: skip
+    for n in nodes:
+        n.start()
+    try:
+        nodes[1].connect(nodes[0].addr)
+        wait_convergence(nodes, 1, only_direct=True)
+        nodes[0].set_start_learning(rounds=2, epochs=1)
+        wait_4_results(nodes, 120)
+        check_equal_models(nodes, atol=1e-6)
+    finally:
+        for n in nodes:
+            n.stop()
