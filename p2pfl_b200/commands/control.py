@@ -32,7 +32,7 @@ class HeartbeatCommand(Command):
 class StartLearningCommand(Command):
     """``start_learning [rounds, epochs]`` (reference: commands/start_learning_command.py:39-60)."""
 
-    def __init__(self, start_learning_fn: Callable[[int, int], None]) -> None:
+    def __init__(self, start_learning_fn: Callable[..., None]) -> None:
         self._start = start_learning_fn
 
     @staticmethod
@@ -40,7 +40,8 @@ class StartLearningCommand(Command):
         return "start_learning"
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
-        self._start(int(args[0]), int(args[1]))
+        # optional third argument: the experiment's data-plane sequence base (ignored by reference nodes)
+        self._start(int(args[0]), int(args[1]), int(args[2]) if len(args) > 2 else 0)
 
 
 class StopLearningCommand(Command):

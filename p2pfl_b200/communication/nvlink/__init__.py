@@ -1,0 +1,3 @@
+from p2pfl_b200.communication.nvlink.nvlink_protocol import NvlinkCommunicationProtocol, NvlinkMemoryProtocol
+
+__all__ = ["NvlinkCommunicationProtocol", "NvlinkMemoryProtocol"]

@@ -159,7 +159,8 @@ class Aggregator:
             logger.info(self.node_name, f"aggregation timeout; missing models: {sorted(missing)}")
         if not models:
             raise NoModelsToAggregateError(f"({self.node_name}) no models to aggregate")
-        if waiting:
+        if waiting or len(models) == 1:
+            # a single entry is already the normalised mean of its contributors
             return next(iter(models.values()))[0]
         return self.aggregate(models)
 

@@ -30,7 +30,7 @@ from p2pfl_b200 import ops
 from p2pfl_b200.learning.params import FlatParams
 from p2pfl_b200.learning.torch_learner import TorchLearner
 from p2pfl_b200.management.logger import logger
-from p2pfl_b200.parallel.arena import DeviceArena
+from p2pfl_b200.parallel.arena import ArenaPool, DeviceArena
 from p2pfl_b200.settings import Settings
 
 _capture_lock = threading.Lock()
@@ -79,8 +79,9 @@ class B200Learner(TorchLearner):
     # --------------------------------------------------------------- storage
     def _alloc_flat(self, total: int) -> torch.Tensor:
         if self.arena is not None:
-            self.arena.close()
-        self.arena = DeviceArena(
+            ArenaPool.release(self.arena)
+        self.arena = ArenaPool.acquire(
+            self.addr,
             total,
             slots=self.inbox_slots,
             tile=Settings.DEVICE_TILE_ELEMS,
@@ -144,6 +145,12 @@ class B200Learner(TorchLearner):
             if self.fused and self._tdescs:
                 ops.transpose_cast(self.flat, self.wT16, self._tdescs)
 
+    def _params_written_by_plane(self) -> None:
+        """The data plane wrote fp32 params AND the bf16 copy; only the transposes are stale."""
+        if self.fused and self._tdescs:
+            with torch.cuda.stream(self._s()):
+                ops.transpose_cast(self.flat, self.wT16, self._tdescs)
+
     def _s(self) -> torch.cuda.Stream:
         return getattr(self, "stream", None) or torch.cuda.current_stream(self.device)
 
@@ -153,7 +160,7 @@ class B200Learner(TorchLearner):
             torch.cuda.synchronize(self.device)
             # views into the arena must not outlive it
             self.flat = None
-            self.arena.close()
+            ArenaPool.release(self.arena)
             self.arena = None
 
     # ------------------------------------------------------------ parameters
@@ -163,7 +170,26 @@ class B200Learner(TorchLearner):
         self._s().synchronize()
         return out
 
+    def export_payload(self, params: Any = None) -> Any:
+        """Device payload for data planes that move device memory themselves: the
+        model stays on the GPU; what travels on the control plane is a reference."""
+        from p2pfl_b200.parallel.payload import DevicePayload
+
+        if params is None:
+            params = self.export_model()
+        if not isinstance(params, FlatParams):
+            raise TypeError("export_payload needs a FlatParams")
+        return DevicePayload(params, self)
+
+    def live_params(self) -> FlatParams:
+        """The live model WITHOUT a copy (valid until the next update)."""
+        return FlatParams(self.flat, self.layout, self._extra())
+
     def set_parameters(self, params: Any) -> None:
+        if isinstance(params, FlatParams) and params.flat.data_ptr() == self.flat.data_ptr():
+            self._params_written()  # already in place (device data plane wrote it)
+            self._s().synchronize()
+            return
         with torch.cuda.stream(self._s()):
             if isinstance(params, FlatParams) and params.flat.is_cuda:
                 # the producer may have written it on another stream
@@ -289,6 +315,7 @@ class B200Learner(TorchLearner):
         x, y = self._train_dev
         ep: Dict[str, Any] = {"n": n, "B": B, "nb": nb}
         ep["perm"] = torch.arange(n, dtype=torch.int32, device=dev)
+        ep["perm_host"] = torch.empty(n, dtype=torch.int32).pin_memory()
         ep["xs"] = torch.zeros(nb * B, feat, dtype=torch.bfloat16, device=dev)
         ep["xsT"] = torch.zeros(nb, feat, _pad8(B), dtype=torch.bfloat16, device=dev)
         ep["ys"] = torch.zeros(nb * B, dtype=torch.int32, device=dev)
@@ -347,7 +374,11 @@ class B200Learner(TorchLearner):
                 if self._interrupt.is_set():
                     logger.info(self.addr, "fit interrupted")
                     break
-                ep["perm"].copy_(torch.randperm(n, device=self.device).to(torch.int32))
+                # host RNG: the CUDA generator cannot be used while another node's
+                # thread captures a graph on this device
+                ep["perm_host"].copy_(torch.randperm(n, dtype=torch.int32))
+                ep["perm"].copy_(ep["perm_host"], non_blocking=True)
+                self.h2d_bytes += n * 4
                 ep["graph"].replay()
                 ops.add_launches(ep["launches"])
                 self.kernel_launches_per_epoch = ep["launches"]

@@ -11,6 +11,7 @@ A fresh ``LearningWorkflow`` is built per experiment (Q2).
 from __future__ import annotations
 
 import threading
+import time
 from typing import Any, Dict, Optional, Type
 
 from p2pfl_b200.commands import (
@@ -169,10 +170,13 @@ class Node:
             raise LearnerNotSetException("learner not set")
         logger.info(self.addr, f"starting learning: {rounds} rounds x {epochs} epochs")
         proto = self._communication_protocol
-        proto.broadcast(proto.build_msg("start_learning", [str(rounds), str(epochs)]))
+        # data-plane sequence numbers must grow from one experiment to the next (arenas and
+        # their arrival flags are reused): derive the base from the wall clock
+        seq_base = (int(time.time()) % (1 << 18)) * 4096
+        proto.broadcast(proto.build_msg("start_learning", [str(rounds), str(epochs), str(seq_base)]))
         self.state.model_initialized.set()
         proto.broadcast(proto.build_msg("model_initialized"))
-        self.__start_learning_thread(rounds, epochs)
+        self.__start_learning_thread(rounds, epochs, seq_base)
 
     def set_stop_learning(self) -> None:
         if self.state.round is not None:
@@ -191,11 +195,12 @@ class Node:
         return ok
 
     # ---------------------------------------------------------- internals
-    def __start_learning_thread(self, rounds: int, epochs: int) -> None:
+    def __start_learning_thread(self, rounds: int, epochs: int, seq_base: int = 0) -> None:
         with self.state.start_thread_lock:
             if self.state.round is not None or not self.state.finished.is_set():
                 return
             self.state.finished.clear()
+            self.state.seq_base = seq_base
         t = threading.Thread(
             target=self.__start_learning, args=(rounds, epochs), name=f"learning_thread-{self.addr}", daemon=True
         )

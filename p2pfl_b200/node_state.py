@@ -25,6 +25,8 @@ class NodeState:
         self.round: Optional[int] = None
         self.total_rounds: Optional[int] = None
         self.learner: Any = None
+        # base of the data-plane sequence numbers of this experiment (agreed through start_learning)
+        self.seq_base: int = 0
 
         # who aggregated what this round: node -> list of contributors
         self.models_aggregated: Dict[str, List[str]] = {}

@@ -5,6 +5,7 @@ by the C++ runtime with ``cudaMalloc`` so it can be exported over CUDA IPC and
 mapped into peer GPUs / peer processes.  Layout (every region 256-byte aligned):
 
     params   fp32[n]                       the live model (the learner's tensors are views)
+    outbox   fp32[n]                       staging for models peers pull (partial aggregates)
     inbox    wire[2 banks][slots][n]       one slot per possible contributor
     flags    u32 [2 banks][slots][tiles]   arrival flag per (slot, tile), holds the exchange seq
     status   i32 [4]                       written by the reduce kernels
@@ -20,8 +21,9 @@ No counterpart in the reference (models live in host ``state_dict``s there).
 
 from __future__ import annotations
 
+import threading
 from dataclasses import dataclass
-from typing import List, Optional, Sequence, Tuple
+from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
 
@@ -76,8 +78,12 @@ class ArenaGeometry:
         return 0
 
     @property
-    def off_inbox(self) -> int:
+    def off_outbox(self) -> int:
         return _align(self.n * 4)
+
+    @property
+    def off_inbox(self) -> int:
+        return 2 * _align(self.n * 4)
 
     @property
     def slot_bytes(self) -> int:
@@ -128,6 +134,7 @@ class DeviceArena:
         self.device = device
         self.base = ops.rt_alloc(device, self.geo.total_bytes)
         self.params = tensor_from_ptr(self.base + self.geo.off_params, n, torch.float32, device)
+        self.outbox = tensor_from_ptr(self.base + self.geo.off_outbox, n, torch.float32, device)
         self.status = tensor_from_ptr(self.base + self.geo.off_status, 4, torch.int32, device)
         self.abort = tensor_from_ptr(self.base + self.geo.off_abort, 1, torch.int32, device)
         self._closed = False
@@ -161,7 +168,7 @@ class DeviceArena:
         if not self._closed:
             self._closed = True
             torch.cuda.synchronize(self.device)
-            self.params = self.status = self.abort = None  # type: ignore[assignment]
+            self.params = self.outbox = self.status = self.abort = None  # type: ignore[assignment]
             ops.rt_free(self.device, self.base)
 
     def __del__(self) -> None:  # best effort
@@ -169,6 +176,43 @@ class DeviceArena:
             self.close()
         except Exception:
             pass
+
+
+class ArenaPool:
+    """Process-wide pool so that a node's arena (and with it the IPC handle its peers
+    hold) survives from one experiment to the next instead of being re-allocated."""
+
+    _lock = threading.Lock()
+    _free: Dict[Tuple[str, int, str], DeviceArena] = {}
+
+    @classmethod
+    def acquire(cls, owner: str, n: int, slots: int, tile: int, wire_bf16: bool, device: int) -> DeviceArena:
+        key = (owner, device, ArenaGeometry(n, slots, tile, wire_bf16).key())
+        with cls._lock:
+            arena = cls._free.pop(key, None)
+        if arena is None:
+            arena = DeviceArena(n, slots, tile, wire_bf16, device)
+        arena.pool_key = key  # type: ignore[attr-defined]
+        return arena
+
+    @classmethod
+    def release(cls, arena: DeviceArena) -> None:
+        key = getattr(arena, "pool_key", None)
+        if key is None or arena._closed:
+            arena.close()
+            return
+        with cls._lock:
+            old = cls._free.pop(key, None)
+            cls._free[key] = arena
+        if old is not None and old is not arena:
+            old.close()
+
+    @classmethod
+    def drain(cls) -> None:
+        with cls._lock:
+            arenas, cls._free = list(cls._free.values()), {}
+        for a in arenas:
+            a.close()
 
 
 class PeerArena:
@@ -186,6 +230,9 @@ class PeerArena:
 
     def params_ptr(self) -> int:
         return self.base + self.geo.off_params
+
+    def region_ptr(self, region: str) -> int:
+        return self.base + (self.geo.off_outbox if region == "outbox" else self.geo.off_params)
 
     def close(self) -> None:
         if self._ipc_dev is not None:

@@ -67,6 +67,9 @@ class Settings:
     """Wire dtype of the device data plane: 'bf16' (inbox mode B) or 'fp32'."""
     DEVICE_TILE_ELEMS: int = 16384
     """Elements per data-plane tile (one arrival flag per tile)."""
+    FUSED_EXCHANGE: bool = True
+    """Use the single-kernel push+FedAvg exchange whenever the whole train set has
+    device arenas on distinct GPUs; otherwise models are pulled one by one."""
     DEVICE_INBOX_SLOTS: int = 8
     """Inbox slots per arena = the largest train set the data plane can serve."""
     TRAINER_DIFFUSION_GRACE: float = 0.5

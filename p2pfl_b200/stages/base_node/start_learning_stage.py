@@ -38,7 +38,16 @@ class StartLearningStage(Stage):
                 logger.debug(st.addr, "learning already started; duplicate start ignored")
                 return None
             st.set_experiment("experiment", ctx.rounds)
+            old = st.learner
+            if old is not None:
+                try:
+                    old.close()  # hands its device arena back to the pool for the new learner
+                except Exception:
+                    pass
             st.learner = build_learner(ctx)
+        publish = getattr(ctx.communication_protocol, "publish_arena", None)
+        if publish is not None:
+            publish(st.learner)
         logger.experiment_started(st.addr)
 
         # initial weights: the initiator set the event itself; everybody else

@@ -46,9 +46,20 @@ class TrainStage(Stage):
 
         if ctx.early_stopping_fn():
             return None
-        held = agg.add_model(st.learner.export_model(), [st.addr], st.learner.get_num_samples()[0])
-        proto.broadcast(proto.build_msg("models_aggregated", held, round=st.round))
-        TrainStage._gossip_partial_aggregates(ctx)
+        fused = None
+        plan = getattr(proto, "plan_fused_exchange", None)
+        if plan is not None and getattr(st.learner, "arena", None) is not None:
+            fused = plan(st, st.learner)
+        if fused is not None:
+            # device data plane: ONE kernel pushes this model to every trainer and
+            # FedAvg-accumulates theirs into the live parameters as the tiles land
+            contributors, total_w = fused.run(st.seq_base + st.round + 1)
+            held = agg.add_model(st.learner.live_params(), contributors, total_w)
+            proto.broadcast(proto.build_msg("models_aggregated", held, round=st.round))
+        else:
+            held = agg.add_model(st.learner.export_model(), [st.addr], st.learner.get_num_samples()[0])
+            proto.broadcast(proto.build_msg("models_aggregated", held, round=st.round))
+            TrainStage._gossip_partial_aggregates(ctx)
         t3 = time.time()
         for k, dt in (("evaluate", t1 - t0), ("fit", t2 - t1), ("exchange", t3 - t2)):
             ctx.timings[k] = ctx.timings.get(k, 0.0) + dt
