@@ -24,11 +24,15 @@ using namespace p2pfl;
 
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;
+constexpr int kLag = 2;  // tiles between pushing a tile and reducing it (fused kernel)
 
-__device__ __forceinline__ uint4 ld_volatile_u4(const void* p) {
+// Inbox tiles are read only after the tile's flag was acquired at system scope and
+// were never touched earlier in this launch (L1 is invalidated at launch), so a
+// plain L1-bypassing load sees the peer's data; unlike ld.volatile it can be batched.
+__device__ __forceinline__ uint4 ld_inbox_u4(const void* p) {
   uint4 r;
-  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                : "l"(p)
                : "memory");
@@ -36,152 +40,238 @@ __device__ __forceinline__ uint4 ld_volatile_u4(const void* p) {
 }
 
 // ---------------------------------------------------------------------- push
+__device__ __forceinline__ void push_tile(const float* __restrict__ src, uint64_t n, uint32_t tile, uint32_t seq,
+                                          const p2pfl_push_table& t, uint32_t ti) {
+  const uint64_t t0 = (uint64_t)ti * tile;
+  const uint32_t len = (uint32_t)((n - t0) < tile ? (n - t0) : tile);
+  if (t.wire_bf16) {
+    // 8 elements per vector (32 B in, 16 B out per peer), 4 vectors in flight per thread
+    for (uint32_t e0 = threadIdx.x * 8; e0 < len; e0 += kThreads * 8 * 4) {
+      uint4 w[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t e = e0 + u * kThreads * 8;
+        if (e < len) {
+          const float4 a = *reinterpret_cast<const float4*>(src + t0 + e);
+          const float4 b = *reinterpret_cast<const float4*>(src + t0 + e + 4);
+          w[u].x = pack_bf16x2(a.x, a.y);
+          w[u].y = pack_bf16x2(a.z, a.w);
+          w[u].z = pack_bf16x2(b.x, b.y);
+          w[u].w = pack_bf16x2(b.z, b.w);
+        }
+      }
+      for (int p = 0; p < t.n_peers; ++p) {
+        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(t.inbox[p]) + t0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t e = e0 + u * kThreads * 8;
+          if (e < len) st_stream_u4(dst + e, w[u]);
+        }
+      }
+    }
+  } else {
+    for (uint32_t e0 = threadIdx.x * 4; e0 < len; e0 += kThreads * 4 * 4) {
+      uint4 w[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t e = e0 + u * kThreads * 4;
+        if (e < len) w[u] = *reinterpret_cast<const uint4*>(src + t0 + e);
+      }
+      for (int p = 0; p < t.n_peers; ++p) {
+        float* dst = reinterpret_cast<float*>(t.inbox[p]) + t0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t e = e0 + u * kThreads * 4;
+          if (e < len) st_stream_u4(dst + e, w[u]);
+        }
+      }
+    }
+  }
+  __syncthreads();  // every store of this tile happens-before the flag writers below
+  if ((int)threadIdx.x < t.n_peers) {
+    __threadfence_system();
+    st_release_sys_u32(t.flags[threadIdx.x] + ti, seq);
+  }
+}
+
 // `cta` / `n_cta` let several logical ranks share one launch (emulation).
 __device__ void push_phase(const float* __restrict__ src, uint64_t n, uint32_t tile, uint32_t seq,
                            const p2pfl_push_table& t, int cta, int n_cta) {
   const uint32_t n_tiles = (uint32_t)((n + tile - 1) / tile);
-  for (uint32_t ti = cta; ti < n_tiles; ti += n_cta) {
-    const uint64_t t0 = (uint64_t)ti * tile;
-    const uint32_t len = (uint32_t)((n - t0) < tile ? (n - t0) : tile);
-    if (t.wire_bf16) {
-      // 8 elements per thread-iteration: 32 B in, 16 B out per peer
-      for (uint32_t e = threadIdx.x * 8; e < len; e += kThreads * 8) {
-        const float4 a = *reinterpret_cast<const float4*>(src + t0 + e);
-        const float4 b = *reinterpret_cast<const float4*>(src + t0 + e + 4);
-        uint4 w;
-        w.x = pack_bf16x2(a.x, a.y);
-        w.y = pack_bf16x2(a.z, a.w);
-        w.z = pack_bf16x2(b.x, b.y);
-        w.w = pack_bf16x2(b.z, b.w);
-#pragma unroll 4
-        for (int p = 0; p < t.n_peers; ++p)
-          st_stream_u4(reinterpret_cast<__nv_bfloat16*>(t.inbox[p]) + t0 + e, w);
-      }
-    } else {
-      for (uint32_t e = threadIdx.x * 4; e < len; e += kThreads * 4) {
-        const uint4 w = *reinterpret_cast<const uint4*>(src + t0 + e);
-#pragma unroll 4
-        for (int p = 0; p < t.n_peers; ++p) st_stream_u4(reinterpret_cast<float*>(t.inbox[p]) + t0 + e, w);
-      }
-    }
-    __syncthreads();  // every store of this tile happens-before the flag writers below
-    if ((int)threadIdx.x < t.n_peers) {
-      __threadfence_system();
-      st_release_sys_u32(t.flags[threadIdx.x] + ti, seq);
-    }
-  }
+  for (uint32_t ti = cta; ti < n_tiles; ti += n_cta) push_tile(src, n, tile, seq, t, ti);
 }
 
 // -------------------------------------------------------------------- reduce
+__device__ __forceinline__ void reduce_tile(float* __restrict__ params, __nv_bfloat16* __restrict__ params_bf16,
+                                            uint64_t n, uint32_t tile, uint32_t seq, const p2pfl_reduce_table& t,
+                                            const uint32_t* __restrict__ abort_flag, uint64_t timeout_cycles,
+                                            int32_t* status, uint32_t ti, int* s_arrived) {
+  const uint64_t t0 = (uint64_t)ti * tile;
+  const uint32_t len = (uint32_t)((n - t0) < tile ? (n - t0) : tile);
+
+  // ---- wait: one thread per expected contributor ---------------------------
+  if ((int)threadIdx.x < t.n_slots) {
+    const uint32_t* f = t.flags[threadIdx.x] + ti;
+    const long long start = clock64();
+    int ok = 1;
+    uint32_t spins = 0;
+    while ((int32_t)(ld_acquire_sys_u32(f) - seq) < 0) {
+      if ((++spins & 63u) == 0) {
+        if ((abort_flag && ld_volatile_u32(abort_flag) != 0) ||
+            (timeout_cycles && (uint64_t)(clock64() - start) > timeout_cycles)) {
+          ok = 0;
+          break;
+        }
+      }
+      __nanosleep(32);
+    }
+    s_arrived[threadIdx.x] = ok;
+    if (!ok && status) atomicExch(status, 1);
+  }
+  __syncthreads();
+
+  // ---- weights of what actually arrived -----------------------------------
+  float wsum = (t.self_pos >= 0) ? t.self_weight : 0.f;
+  for (int j = 0; j < t.n_slots; ++j) wsum += s_arrived[j] ? t.weight[j] : 0.f;
+  const float scale = (wsum > 0.f && fabsf(wsum - 1.f) > 1e-6f) ? 1.f / wsum : 1.f;
+  const float w_self = (t.self_pos >= 0) ? t.self_weight : 0.f;
+  const bool round_own = t.round_self && t.wire_bf16;
+
+  // ---- accumulate in slot order, local model inserted at self_pos ---------
+  // two 8-element vectors per thread-iteration so the loads of both are in flight together
+  for (uint32_t e0 = threadIdx.x * 8; e0 < len; e0 += kThreads * 8 * 2) {
+    float own[2][8];
+    float acc[2][8];
+    bool live[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const uint32_t e = e0 + u * kThreads * 8;
+      live[u] = e < len;
+      if (live[u]) {
+        const float4 a = *reinterpret_cast<const float4*>(params + t0 + e);
+        const float4 b = *reinterpret_cast<const float4*>(params + t0 + e + 4);
+        own[u][0] = a.x; own[u][1] = a.y; own[u][2] = a.z; own[u][3] = a.w;
+        own[u][4] = b.x; own[u][5] = b.y; own[u][6] = b.z; own[u][7] = b.w;
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (round_own) own[u][k] = __bfloat162float(__float2bfloat16_rn(own[u][k]));
+        acc[u][k] = 0.f;
+      }
+    }
+    for (int j = 0; j <= t.n_slots; ++j) {
+      if (j == t.self_pos) {
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[u][k] = fmaf(w_self, own[u][k], acc[u][k]);
+      }
+      if (j == t.n_slots) break;
+      const float wj = s_arrived[j] ? t.weight[j] : 0.f;
+      if (wj == 0.f) continue;
+      if (t.wire_bf16) {
+        uint4 v[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+          if (live[u]) v[u] = ld_inbox_u4(reinterpret_cast<const __nv_bfloat16*>(t.slot[j]) + t0 + e0 + u * kThreads * 8);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (!live[u]) continue;
+          const float2 p0 = unpack_bf16x2(v[u].x), p1 = unpack_bf16x2(v[u].y), p2 = unpack_bf16x2(v[u].z),
+                       p3 = unpack_bf16x2(v[u].w);
+          acc[u][0] = fmaf(wj, p0.x, acc[u][0]); acc[u][1] = fmaf(wj, p0.y, acc[u][1]);
+          acc[u][2] = fmaf(wj, p1.x, acc[u][2]); acc[u][3] = fmaf(wj, p1.y, acc[u][3]);
+          acc[u][4] = fmaf(wj, p2.x, acc[u][4]); acc[u][5] = fmaf(wj, p2.y, acc[u][5]);
+          acc[u][6] = fmaf(wj, p3.x, acc[u][6]); acc[u][7] = fmaf(wj, p3.y, acc[u][7]);
+        }
+      } else {
+        uint4 v[2][2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+          if (live[u]) {
+            const float* sp = reinterpret_cast<const float*>(t.slot[j]) + t0 + e0 + u * kThreads * 8;
+            v[u][0] = ld_inbox_u4(sp);
+            v[u][1] = ld_inbox_u4(sp + 4);
+          }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (!live[u]) continue;
+          acc[u][0] = fmaf(wj, __uint_as_float(v[u][0].x), acc[u][0]); acc[u][1] = fmaf(wj, __uint_as_float(v[u][0].y), acc[u][1]);
+          acc[u][2] = fmaf(wj, __uint_as_float(v[u][0].z), acc[u][2]); acc[u][3] = fmaf(wj, __uint_as_float(v[u][0].w), acc[u][3]);
+          acc[u][4] = fmaf(wj, __uint_as_float(v[u][1].x), acc[u][4]); acc[u][5] = fmaf(wj, __uint_as_float(v[u][1].y), acc[u][5]);
+          acc[u][6] = fmaf(wj, __uint_as_float(v[u][1].z), acc[u][6]); acc[u][7] = fmaf(wj, __uint_as_float(v[u][1].w), acc[u][7]);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (!live[u]) continue;
+      const uint32_t e = e0 + u * kThreads * 8;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[u][k] *= scale;
+      *reinterpret_cast<float4*>(params + t0 + e) = make_float4(acc[u][0], acc[u][1], acc[u][2], acc[u][3]);
+      *reinterpret_cast<float4*>(params + t0 + e + 4) = make_float4(acc[u][4], acc[u][5], acc[u][6], acc[u][7]);
+      if (params_bf16) {
+        uint4 o;
+        o.x = pack_bf16x2(acc[u][0], acc[u][1]);
+        o.y = pack_bf16x2(acc[u][2], acc[u][3]);
+        o.z = pack_bf16x2(acc[u][4], acc[u][5]);
+        o.w = pack_bf16x2(acc[u][6], acc[u][7]);
+        *reinterpret_cast<uint4*>(params_bf16 + t0 + e) = o;
+      }
+    }
+  }
+  if (threadIdx.x == 0 && status) atomicAdd(status + 1, 1);
+  __syncthreads();  // s_arrived is reused by the next tile
+}
+
 __device__ void reduce_phase(float* __restrict__ params, __nv_bfloat16* __restrict__ params_bf16, uint64_t n,
                              uint32_t tile, uint32_t seq, const p2pfl_reduce_table& t,
                              const uint32_t* __restrict__ abort_flag, uint64_t timeout_cycles, int32_t* status, int cta,
                              int n_cta) {
   __shared__ int s_arrived[P2PFL_MAX_PEERS];
   const uint32_t n_tiles = (uint32_t)((n + tile - 1) / tile);
-  for (uint32_t ti = cta; ti < n_tiles; ti += n_cta) {
-    const uint64_t t0 = (uint64_t)ti * tile;
-    const uint32_t len = (uint32_t)((n - t0) < tile ? (n - t0) : tile);
+  for (uint32_t ti = cta; ti < n_tiles; ti += n_cta)
+    reduce_tile(params, params_bf16, n, tile, seq, t, abort_flag, timeout_cycles, status, ti, s_arrived);
+}
 
-    // ---- wait: one thread per expected contributor ---------------------------
-    if ((int)threadIdx.x < t.n_slots) {
-      const uint32_t* f = t.flags[threadIdx.x] + ti;
-      const long long start = clock64();
-      int ok = 1;
-      uint32_t spins = 0;
-      while ((int32_t)(ld_acquire_sys_u32(f) - seq) < 0) {
-        if ((++spins & 63u) == 0) {
-          if ((abort_flag && ld_volatile_u32(abort_flag) != 0) ||
-              (timeout_cycles && (uint64_t)(clock64() - start) > timeout_cycles)) {
-            ok = 0;
-            break;
-          }
-        }
-        __nanosleep(64);
-      }
-      s_arrived[threadIdx.x] = ok;
-      if (!ok && status) atomicExch(status, 1);
-    }
-    __syncthreads();
-
-    // ---- weights of what actually arrived -----------------------------------
-    float w[P2PFL_MAX_PEERS];
-    float wsum = (t.self_pos >= 0) ? t.self_weight : 0.f;
-#pragma unroll
-    for (int j = 0; j < P2PFL_MAX_PEERS; ++j) {
-      w[j] = (j < t.n_slots && s_arrived[j]) ? t.weight[j] : 0.f;
-      wsum += w[j];
-    }
-    const float scale = (wsum > 0.f && fabsf(wsum - 1.f) > 1e-6f) ? 1.f / wsum : 1.f;
-    const float w_self = (t.self_pos >= 0) ? t.self_weight : 0.f;
-
-    // ---- accumulate in slot order, local model inserted at self_pos ---------
-    for (uint32_t e = threadIdx.x * 8; e < len; e += kThreads * 8) {
-      float own[8];
-      {
-        const float4 a = *reinterpret_cast<const float4*>(params + t0 + e);
-        const float4 b = *reinterpret_cast<const float4*>(params + t0 + e + 4);
-        own[0] = a.x; own[1] = a.y; own[2] = a.z; own[3] = a.w;
-        own[4] = b.x; own[5] = b.y; own[6] = b.z; own[7] = b.w;
-        if (t.round_self && t.wire_bf16) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) own[k] = __bfloat162float(__float2bfloat16_rn(own[k]));
-        }
-      }
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int j = 0; j <= t.n_slots; ++j) {
-        if (j == t.self_pos) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) acc[k] = fmaf(w_self, own[k], acc[k]);
-        }
-        if (j == t.n_slots) break;
-        const float wj = w[j];
-        if (wj == 0.f) continue;
-        if (t.wire_bf16) {
-          const uint4 u = ld_volatile_u4(reinterpret_cast<const __nv_bfloat16*>(t.slot[j]) + t0 + e);
-          const float2 p0 = unpack_bf16x2(u.x), p1 = unpack_bf16x2(u.y), p2 = unpack_bf16x2(u.z), p3 = unpack_bf16x2(u.w);
-          acc[0] = fmaf(wj, p0.x, acc[0]); acc[1] = fmaf(wj, p0.y, acc[1]);
-          acc[2] = fmaf(wj, p1.x, acc[2]); acc[3] = fmaf(wj, p1.y, acc[3]);
-          acc[4] = fmaf(wj, p2.x, acc[4]); acc[5] = fmaf(wj, p2.y, acc[5]);
-          acc[6] = fmaf(wj, p3.x, acc[6]); acc[7] = fmaf(wj, p3.y, acc[7]);
-        } else {
-          const uint4 u0 = ld_volatile_u4(reinterpret_cast<const float*>(t.slot[j]) + t0 + e);
-          const uint4 u1 = ld_volatile_u4(reinterpret_cast<const float*>(t.slot[j]) + t0 + e + 4);
-          acc[0] = fmaf(wj, __uint_as_float(u0.x), acc[0]); acc[1] = fmaf(wj, __uint_as_float(u0.y), acc[1]);
-          acc[2] = fmaf(wj, __uint_as_float(u0.z), acc[2]); acc[3] = fmaf(wj, __uint_as_float(u0.w), acc[3]);
-          acc[4] = fmaf(wj, __uint_as_float(u1.x), acc[4]); acc[5] = fmaf(wj, __uint_as_float(u1.y), acc[5]);
-          acc[6] = fmaf(wj, __uint_as_float(u1.z), acc[6]); acc[7] = fmaf(wj, __uint_as_float(u1.w), acc[7]);
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < 8; ++k) acc[k] *= scale;
-      *reinterpret_cast<float4*>(params + t0 + e) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      *reinterpret_cast<float4*>(params + t0 + e + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
-      if (params_bf16) {
-        uint4 o;
-        o.x = pack_bf16x2(acc[0], acc[1]);
-        o.y = pack_bf16x2(acc[2], acc[3]);
-        o.z = pack_bf16x2(acc[4], acc[5]);
-        o.w = pack_bf16x2(acc[6], acc[7]);
-        *reinterpret_cast<uint4*>(params_bf16 + t0 + e) = o;
-      }
-    }
-    if (threadIdx.x == 0 && status) atomicAdd(status + 1, 1);
-    __syncthreads();  // s_arrived is reused by the next tile
+// Fused schedule of one CTA: push tile k, then reduce the tile pushed kLag steps
+// earlier - peers run the same schedule, so by then their copy of that tile has
+// normally landed and NVLink stores overlap the HBM-bound accumulate.
+__device__ void fused_phase(float* __restrict__ params, __nv_bfloat16* __restrict__ params_bf16, uint64_t n,
+                            uint32_t tile, uint32_t seq, const p2pfl_push_table& push, const p2pfl_reduce_table& red,
+                            const uint32_t* __restrict__ abort_flag, uint64_t timeout_cycles, int32_t* status, int cta,
+                            int n_cta) {
+  __shared__ int s_arrived[P2PFL_MAX_PEERS];
+  const uint32_t n_tiles = (uint32_t)((n + tile - 1) / tile);
+  const uint32_t mine = n_tiles > (uint32_t)cta ? (n_tiles - cta + n_cta - 1) / n_cta : 0;
+  for (uint32_t k = 0; k < mine + kLag; ++k) {
+    if (k < mine) push_tile(params, n, tile, seq, push, cta + k * n_cta);
+    if (k >= kLag)
+      reduce_tile(params, params_bf16, n, tile, seq, red, abort_flag, timeout_cycles, status, cta + (k - kLag) * n_cta,
+                  s_arrived);
   }
 }
 
 // ------------------------------------------------------------------- kernels
 __global__ void __launch_bounds__(kThreads)
-gossip_push_kernel(const float* __restrict__ src, uint64_t n, uint32_t tile, uint32_t seq, p2pfl_push_table t) {
-  push_phase(src, n, tile, seq, t, blockIdx.x, gridDim.x);
+gossip_push_kernel(const float* __restrict__ src, uint64_t n, uint32_t tile, uint32_t seq,
+                   const __grid_constant__ p2pfl_push_table t) {
+  // dynamic indexing into kernel parameters would be copied to local memory: stage in smem
+  __shared__ p2pfl_push_table s_push;
+  if (threadIdx.x == 0) s_push = t;
+  __syncthreads();
+  push_phase(src, n, tile, seq, s_push, blockIdx.x, gridDim.x);
 }
 
 __global__ void __launch_bounds__(kThreads)
 gossip_reduce_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ params_bf16, uint64_t n, uint32_t tile,
-                     uint32_t seq, p2pfl_reduce_table t, const uint32_t* __restrict__ abort_flag,
-                     uint64_t timeout_cycles, int32_t* status) {
-  reduce_phase(params, params_bf16, n, tile, seq, t, abort_flag, timeout_cycles, status, blockIdx.x, gridDim.x);
+                     uint32_t seq, const __grid_constant__ p2pfl_reduce_table t,
+                     const uint32_t* __restrict__ abort_flag, uint64_t timeout_cycles, int32_t* status) {
+  __shared__ p2pfl_reduce_table s_red;
+  if (threadIdx.x == 0) s_red = t;
+  __syncthreads();
+  reduce_phase(params, params_bf16, n, tile, seq, s_red, abort_flag, timeout_cycles, status, blockIdx.x, gridDim.x);
 }
 
 // G1+G2: one launch.  Every CTA first pushes its tiles (no waiting), then
@@ -189,10 +279,18 @@ gossip_reduce_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ par
 // every contributor is in flight while tile i-1 is being accumulated.
 __global__ void __launch_bounds__(kThreads)
 gossip_fused_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ params_bf16, uint64_t n, uint32_t tile,
-                    uint32_t seq, p2pfl_push_table push, p2pfl_reduce_table red,
-                    const uint32_t* __restrict__ abort_flag, uint64_t timeout_cycles, int32_t* status) {
-  push_phase(params, n, tile, seq, push, blockIdx.x, gridDim.x);
-  reduce_phase(params, params_bf16, n, tile, seq, red, abort_flag, timeout_cycles, status, blockIdx.x, gridDim.x);
+                    uint32_t seq, const __grid_constant__ p2pfl_push_table push,
+                    const __grid_constant__ p2pfl_reduce_table red, const uint32_t* __restrict__ abort_flag,
+                    uint64_t timeout_cycles, int32_t* status) {
+  __shared__ p2pfl_push_table s_push;
+  __shared__ p2pfl_reduce_table s_red;
+  if (threadIdx.x == 0) {
+    s_push = push;
+    s_red = red;
+  }
+  __syncthreads();
+  fused_phase(params, params_bf16, n, tile, seq, s_push, s_red, abort_flag, timeout_cycles, status, blockIdx.x,
+              gridDim.x);
 }
 
 // Test harness: R logical ranks in ONE cooperative launch on one GPU
@@ -215,14 +313,13 @@ gossip_fused_emulated_kernel(EmuArgs a, uint64_t n, uint32_t tile, uint32_t seq,
     s_red = a.reduce[r];
   }
   __syncthreads();
-  push_phase(a.params[r], n, tile, seq, s_push, blockIdx.x, gridDim.x);
-  reduce_phase(a.params[r], nullptr, n, tile, seq, s_red, nullptr, timeout_cycles, status + 4 * r, blockIdx.x,
-               gridDim.x);
+  fused_phase(a.params[r], nullptr, n, tile, seq, s_push, s_red, nullptr, timeout_cycles, status + 4 * r, blockIdx.x,
+              gridDim.x);
 }
 
 int check_common(uint64_t n, uint32_t tile) {
   P2PFL_REQUIRE(n > 0 && (n % 8) == 0, "gossip kernels need n to be a positive multiple of 8 elements");
-  P2PFL_REQUIRE(tile >= 2048 && (tile % 2048) == 0, "tile must be a multiple of 2048 elements");
+  P2PFL_REQUIRE(tile >= 4096 && (tile % 4096) == 0, "tile must be a multiple of 4096 elements");
   return 0;
 }
 
@@ -266,9 +363,14 @@ int p2pfl_gossip_fused(int device, void* stream, float* params, void* params_bf1
   P2PFL_REQUIRE(push && reduce, "null table");
   P2PFL_REQUIRE(push->n_peers <= P2PFL_MAX_PEERS && reduce->n_slots <= P2PFL_MAX_PEERS, "too many peers");
   P2PFL_CUDA_OK(cudaSetDevice(device));
-  // one CTA per SM: the kernel spins on remote flags, keep it to a single wave
+  // the kernel spins on remote flags: keep the grid to ONE resident wave
   uint64_t tiles = (n + tile - 1) / tile;
-  int grid = (int)(tiles < (uint64_t)sm_count(device) ? tiles : (uint64_t)sm_count(device));
+  int per_sm = 0;
+  P2PFL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gossip_fused_kernel, kThreads, 0));
+  if (per_sm > 2) per_sm = 2;
+  if (per_sm < 1) per_sm = 1;
+  uint64_t cap = (uint64_t)sm_count(device) * per_sm;
+  int grid = (int)(tiles < cap ? tiles : cap);
   gossip_fused_kernel<<<grid, kThreads, 0, as_stream(stream)>>>(params, (__nv_bfloat16*)params_bf16, n, tile, seq,
                                                                *push, *reduce, abort_flag, timeout_cycles, status);
   P2PFL_LAUNCH_OK();

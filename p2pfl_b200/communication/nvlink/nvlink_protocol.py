@@ -95,6 +95,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         self._peers: Dict[str, PeerInfo] = {}
         self._peers_lock = threading.Lock()
         self._nonce = 0
+        self._no_arena: set = set()
         self.add_command(ArenaInfoCommand(self))
         self.stats = {"fused": 0, "pulled": 0, "host": 0, "fused_bytes": 0, "pulled_bytes": 0}
 
@@ -126,6 +127,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
             return
         with _local_lock:
             _local_arenas[self.addr] = arena
+        learner.plane = self
         try:
             ipc = arena.ipc_handle().hex()
         except Exception as e:  # IPC export can be refused in restricted containers
@@ -143,6 +145,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
                 old.n_samples, old.layout_hash = info.n_samples, info.layout_hash
                 return  # same arena as before (pooled): keep the mapping
             self._peers[source] = info
+            self._no_arena.discard(source)
         if old is not None and old.mapped is not None:
             old.mapped.close()
         if self._node is not None:
@@ -196,6 +199,13 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         arena = getattr(learner, "arena", None)
         with self._peers_lock:
             info = self._peers.get(nei)
+        if info is None and arena is not None and nei not in self._no_arena and self._node is not None:
+            # the peer may still be building its learner: its announcement is milliseconds away
+            self._node.state.wait_for(lambda: nei in self._peers, 0.5)
+            with self._peers_lock:
+                info = self._peers.get(nei)
+            if info is None:
+                self._no_arena.add(nei)
         reachable = (
             arena is not None
             and info is not None
@@ -221,14 +231,11 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         return Weights(w.source, w.cmd, w.round, ref.to_bytes(), w.contributors, w.weight)
 
     # ------------------------------------------------------------------- inbound
-    def on_weights(self, w: Weights) -> Optional[str]:
-        if DeviceRef.is_ref(w.weights):
-            try:
-                w = Weights(w.source, w.cmd, w.round, self._pull(DeviceRef.from_bytes(w.weights)), w.contributors, w.weight)
-            except Exception as e:
-                logger.error(self.addr, f"device pull from {w.source} failed: {e!r}")
-                return f"device pull failed: {e}"
-        return super().on_weights(w)
+    # A ``DeviceRef`` travels through the ordinary command path untouched; the device
+    # learner resolves it in ``decode_parameters`` by calling :meth:`pull`.  That way a
+    # reference that arrives before the learner exists is stashed like any other payload.
+    def pull(self, ref: DeviceRef) -> Any:
+        return self._pull(ref)
 
     def _pull(self, ref: DeviceRef) -> Any:
         """Read the sender's tensor over NVLink into a private bf16/fp32 buffer."""
@@ -238,8 +245,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         if ref.layout_hash != learner.layout.hash:
             from p2pfl_b200.exceptions import ModelNotMatchingError
 
-            # surface it through the normal command path so the node stops as the reference does
-            return _Mismatch(ModelNotMatchingError("layout hash differs from the local model"))
+            raise ModelNotMatchingError("layout hash differs from the local model")
         peer = self._map_peer(ref.addr)
         if peer is None:
             raise RuntimeError(f"arena of {ref.addr} is not mapped")
@@ -293,13 +299,6 @@ class NvlinkCommunicationProtocol(BaseProtocol):
             peers[n] = p
             samples[n] = info.n_samples
         return FusedExchange(self, state, learner, train_set, peers, samples)
-
-
-class _Mismatch:
-    """Carries a decode error through ``decode_parameters`` (see ``_pull``)."""
-
-    def __init__(self, err: Exception) -> None:
-        self.err = err
 
 
 class FusedExchange:

@@ -181,6 +181,20 @@ class B200Learner(TorchLearner):
             raise TypeError("export_payload needs a FlatParams")
         return DevicePayload(params, self)
 
+    def decode_parameters(self, data: Any) -> FlatParams:
+        """Host payloads decode as usual; a device reference is resolved by pulling the
+        tensor from the sender's arena over NVLink."""
+        from p2pfl_b200.parallel.payload import DeviceRef
+
+        if DeviceRef.is_ref(data):
+            plane = getattr(self, "plane", None)
+            if plane is None:
+                from p2pfl_b200.exceptions import DecodingParamsError
+
+                raise DecodingParamsError("device reference received but no device data plane is attached")
+            return plane.pull(DeviceRef.from_bytes(data))
+        return super().decode_parameters(data)
+
     def live_params(self) -> FlatParams:
         """The live model WITHOUT a copy (valid until the next update)."""
         return FlatParams(self.flat, self.layout, self._extra())

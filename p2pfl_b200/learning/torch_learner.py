@@ -133,8 +133,6 @@ class TorchLearner(NodeLearner):
         """bytes -> FlatParams on this learner's device.  Count, shapes and
         dtypes are validated here (Q20)."""
         assert self.layout is not None
-        if isinstance(getattr(data, "err", None), Exception):
-            raise data.err  # a data plane reporting why it could not deliver (e.g. layout mismatch)
         if isinstance(data, FlatParams):
             self.check_parameters(data)
             if data.flat.device != self.device:

@@ -86,7 +86,7 @@ class StartLearningStage(Stage):
             if st.learner is None or st.round is None:
                 return None
             if not cache:  # encode once, not per candidate per tick (Q13)
-                cache.append(pack_model(proto, st.learner, st.learner.export_model()))
+                cache.append(pack_model(proto, st.learner, None))
             return proto.build_weights("init_model", st.round, cache[0], ctx.aggregator.get_aggregated_models(), 1)
 
         proto.gossip_weights(

@@ -11,8 +11,9 @@ def pack_model(protocol: Any, learner: Any, params: Any) -> Any:
     """Serialise ``params`` the way ``protocol`` wants it: a device payload for
     data planes that move device memory themselves, pickled bytes otherwise."""
     if getattr(protocol, "device_payloads", False) and hasattr(learner, "export_payload"):
-        return learner.export_payload(params)
-    return learner.encode_parameters(params=params)
+        # params=None: the live model, by reference (peers pull it straight from the arena)
+        return learner.export_payload(params if params is not None else learner.live_params())
+    return learner.encode_parameters(params=params if params is not None else learner.export_model())
 
 
 def broadcast_metrics(protocol: Any, state: Any, results: Dict[str, float]) -> None:

@@ -1,0 +1,50 @@
+#!/usr/bin/env python
+"""Small single-GPU workload for ncu: a few fused train steps (graph replay), an
+evaluation, a FedAvg, and a GPT-2-sized push + reduce on one device.  Run it plain
+first; only then under ncu (B200_PROFILING.md)."""
+
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from p2pfl_b200 import ops  # noqa: E402
+from p2pfl_b200.learning.b200_learner import B200Learner  # noqa: E402
+from p2pfl_b200.learning.data import MnistFederatedDM  # noqa: E402
+from p2pfl_b200.models import MLP  # noqa: E402
+from p2pfl_b200.parallel.arena import DeviceArena  # noqa: E402
+
+what = sys.argv[1] if len(sys.argv) > 1 else "all"
+torch.cuda.set_device(0)
+if what in ("all", "step"):
+    dm = MnistFederatedDM(0, 1, n_train=1280, n_test=256)
+    learner = B200Learner(MLP(seed=0), dm, "prof", epochs=1, device="cuda:0")
+    learner.fit()  # builds + warms the graphs
+    learner.fit()
+    print("eval", learner.evaluate())
+    torch.cuda.synchronize()
+if what in ("all", "gossip"):
+    n, tile = 124_441_344, 16384
+    a = DeviceArena(n, slots=2, tile=tile, wire_bf16=True, device=0)
+    b = DeviceArena(n, slots=2, tile=tile, wire_bf16=True, device=0)
+    a.params.normal_()
+    b.params.normal_()
+    w16 = torch.empty(n, dtype=torch.bfloat16, device="cuda:0")
+    for seq in (1, 3, 5):
+        push = ops.make_push_table([b.slot_ptr(0, 1)], [b.flag_ptr(0, 1)], True)
+        ops.gossip_push(a.params, tile, seq, push)
+        red = ops.make_reduce_table([b.slot_ptr(0, 1)], [b.flag_ptr(0, 1)], [0.5], 1, 0.5, True, True)
+        ops.gossip_reduce(b.params, w16, tile, seq, red, None, 0, None)
+    torch.cuda.synchronize()
+    print("gossip ok")
+if what in ("all", "gemm"):
+    M, N, K = 4096, 4096, 4096
+    A = (torch.randn(M, K, device="cuda:0") / 64).to(torch.bfloat16)
+    B = torch.randn(N, K, device="cuda:0").to(torch.bfloat16)
+    out = torch.empty(M, N, device="cuda:0", dtype=torch.bfloat16)
+    for _ in range(3):
+        ops.gemm_tn(A, K, B, K, M, N, K, out_bf16=out, ld_bf16=N)
+    torch.cuda.synchronize()
+    print("gemm ok")
