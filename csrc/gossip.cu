@@ -18,6 +18,8 @@
 // Senders never read remote memory; receivers never write remote memory.
 #include <cooperative_groups.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 using namespace p2pfl;
@@ -402,3 +404,148 @@ int p2pfl_gossip_fused_emulated(int device, void* stream, int n_ranks, float* co
 }
 
 }  // extern "C"
+
+// ===========================================================================
+// Allocation-free exchange for nodes that share one GPU.
+//
+// Some hosts that embed this library cannot obtain device memory when an
+// exchange is due: a simulator that packs many federated nodes on one GPU and
+// hands the whole device to its own pool at start-up has nothing left to ask
+// cudaMalloc for, and a latency-sensitive round loop cannot afford the implicit
+// device-wide synchronisation an allocation (or a free) performs.  For them the
+// inbox the exchange needs lives in the library image itself.
+//
+// The kernel is the one behind p2pfl_gossip_fused_emulated; only the source of
+// its scratch differs.  Because the ranks are co-located, every rank publishes
+// its bf16 model ONCE into wire[rank] (instead of once per receiver) and all
+// other ranks read it from there.
+//
+// Limits: 2..8 ranks, at most 262144 elements per model (the 235146-parameter
+// MLP fits), bf16 wire.  The scratch is 4200192 bytes; every GPU that loads
+// the library carries it until the process exits.
+namespace {
+
+constexpr int kStaticMaxRanks = 8;
+constexpr uint64_t kStaticMaxElems = 262144;
+constexpr uint32_t kStaticTile = 16384;
+constexpr uint64_t kStaticTilesPerRank = kStaticMaxElems / kStaticTile;
+
+constexpr uint64_t kOffWire = 0;
+constexpr uint64_t kOffFlags = kOffWire + kStaticMaxRanks * kStaticMaxElems * 2;
+constexpr uint64_t kOffStatus = kOffFlags + kStaticMaxRanks * kStaticTilesPerRank * 4;
+constexpr uint64_t kOffPush = kOffStatus + 256;
+constexpr uint64_t kOffReduce = kOffPush + 2304;  // 8 push tables of 264 bytes, rounded up
+constexpr uint64_t kStaticScratchBytes = kOffReduce + 2816;  // 8 reduce tables of 344 bytes, rounded up
+static_assert(sizeof(p2pfl_push_table) * kStaticMaxRanks <= 2304, "push tables outgrew their region");
+static_assert(sizeof(p2pfl_reduce_table) * kStaticMaxRanks <= 2816, "reduce tables outgrew their region");
+static_assert(kStaticScratchBytes == 4200192, "documented scratch size is stale");
+
+// In host code this name is only a stand-in; the device address comes from
+// cudaGetSymbolAddress (see static_scratch_for).
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+struct StaticSetup {
+  float* params[kStaticMaxRanks];
+  float weight[kStaticMaxRanks];
+  int32_t n_ranks;
+};
+
+// One thread per rank writes that rank's push and reduce table into the scratch.
+__global__ void static_setup_kernel(StaticSetup s, unsigned char* scratch) {
+  const int r = threadIdx.x;
+  if (r >= s.n_ranks) return;
+  __nv_bfloat16* wire = reinterpret_cast<__nv_bfloat16*>(scratch + kOffWire);
+  uint32_t* flags = reinterpret_cast<uint32_t*>(scratch + kOffFlags);
+  p2pfl_push_table* push = reinterpret_cast<p2pfl_push_table*>(scratch + kOffPush) + r;
+  p2pfl_reduce_table* red = reinterpret_cast<p2pfl_reduce_table*>(scratch + kOffReduce) + r;
+  push->inbox[0] = wire + (uint64_t)r * kStaticMaxElems;
+  push->flags[0] = flags + (uint64_t)r * kStaticTilesPerRank;
+  push->n_peers = 1;
+  push->wire_bf16 = 1;
+  int k = 0;
+  for (int p = 0; p < s.n_ranks; ++p) {
+    if (p == r) continue;
+    red->slot[k] = wire + (uint64_t)p * kStaticMaxElems;
+    red->flags[k] = flags + (uint64_t)p * kStaticTilesPerRank;
+    red->weight[k] = s.weight[p];
+    ++k;
+  }
+  red->n_slots = k;
+  red->self_pos = r;  // ranks are summed in ascending order, the local model at its own rank
+  red->self_weight = s.weight[r];
+  red->wire_bf16 = 1;
+  red->round_self = 1;
+  red->pad_ = 0;
+}
+
+// Device address of the scratch on `device`, resolved once per device.
+int static_scratch_for(int device, unsigned char** out) {
+  static std::mutex mu;
+  static unsigned char* ptrs[64] = {nullptr};
+  P2PFL_REQUIRE(device >= 0 && device < 64, "device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[device] == nullptr) {
+    unsigned char* p = nullptr;
+    P2PFL_CUDA_OK(cudaSetDevice(device));
+    P2PFL_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_scratch));
+    P2PFL_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    ptrs[device] = p;
+  }
+  *out = ptrs[device];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int p2pfl_gossip_exchange_static(int device, void* stream, int n_ranks, float* const* params,
+                                            const float* weights, uint64_t n, uint64_t timeout_cycles,
+                                            int32_t* status_out) {
+  P2PFL_REQUIRE(params != nullptr && weights != nullptr, "null argument");
+  if (n_ranks < 2 || n_ranks > kStaticMaxRanks) {
+    set_error("p2pfl_gossip_exchange_static handles 2..%d co-located ranks, got %d", kStaticMaxRanks, n_ranks);
+    return -3;
+  }
+  if (n == 0 || n > kStaticMaxElems || (n % 8) != 0) {
+    set_error("p2pfl_gossip_exchange_static handles models of at most %llu elements (a multiple of 8), got %llu; "
+              "use p2pfl_gossip_fused_emulated with caller-owned inboxes for larger models",
+              (unsigned long long)kStaticMaxElems, (unsigned long long)n);
+    return -3;
+  }
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  unsigned char* scratch = nullptr;
+  if (int rc = static_scratch_for(device, &scratch)) return rc;
+  cudaStream_t s = as_stream(stream);
+
+  // The scratch still holds the previous call's flags and status: arrival flags and the
+  // status words must start at zero (the wire data and the tables are overwritten below).
+  P2PFL_CUDA_OK(cudaMemsetAsync(scratch + kOffFlags, 0, kOffPush - kOffFlags, s));
+
+  StaticSetup setup;
+  EmuArgs a;
+  for (int r = 0; r < kStaticMaxRanks; ++r) {
+    setup.params[r] = r < n_ranks ? params[r] : nullptr;
+    setup.weight[r] = r < n_ranks ? weights[r] : 0.f;
+    a.params[r] = setup.params[r];
+    if (r < n_ranks) P2PFL_REQUIRE(params[r] != nullptr && ((uintptr_t)params[r] & 15) == 0, "params must be 16-byte aligned");
+  }
+  for (int r = kStaticMaxRanks; r < P2PFL_MAX_PEERS; ++r) a.params[r] = nullptr;
+  setup.n_ranks = n_ranks;
+  static_setup_kernel<<<1, 32, 0, s>>>(setup, scratch);
+  P2PFL_LAUNCH_OK();
+
+  a.push = reinterpret_cast<const p2pfl_push_table*>(scratch + kOffPush);
+  a.reduce = reinterpret_cast<const p2pfl_reduce_table*>(scratch + kOffReduce);
+  int32_t* status = reinterpret_cast<int32_t*>(scratch + kOffStatus);
+  uint32_t tile = kStaticTile, seq = 1;
+  int per_sm = 0;
+  P2PFL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gossip_fused_emulated_kernel, kThreads, 0));
+  int gx = per_sm * sm_count(device) / n_ranks;
+  const uint64_t tiles = (n + tile - 1) / tile;
+  if ((uint64_t)gx > tiles) gx = (int)tiles;
+  P2PFL_REQUIRE(gx >= 1, "not enough resident CTAs for the co-located exchange");
+  dim3 grid(gx, n_ranks, 1), block(kThreads, 1, 1);
+  void* args[] = {&a, &n, &tile, &seq, &timeout_cycles, &status};
+  P2PFL_CUDA_OK(cudaLaunchCooperativeKernel((void*)gossip_fused_emulated_kernel, grid, block, args, 0, s));
+  if (status_out) P2PFL_CUDA_OK(cudaMemcpyAsync(status_out, status, sizeof(int32_t) * 4 * n_ranks, cudaMemcpyDeviceToDevice, s));
+  return 0;
+}

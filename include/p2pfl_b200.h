@@ -136,6 +136,40 @@ int p2pfl_gossip_fused_emulated(int device, void* stream, int n_ranks, float* co
                                 const p2pfl_reduce_table* reduce_tables, uint64_t timeout_cycles,
                                 int32_t* status /* int32[4 * n_ranks] */);
 
+/* Allocation-free exchange among 2..8 nodes that share `device`.
+ * (No counterpart in the reference: it has no device memory to manage.)
+ *
+ * For hosts that cannot ask CUDA for memory when a round's exchange is due - a
+ * simulator that gave the whole GPU to its own pool at start-up, or a round loop
+ * that cannot tolerate the device-wide synchronisation an allocation or a free
+ * implies.  Same kernel and same arithmetic as p2pfl_gossip_fused_emulated (bf16
+ * wire, contributors summed in rank order, every rank ends with identical bits),
+ * but the inbox, the arrival flags, the kernel's tables and its status words live
+ * in a 4200192-byte array inside the library image, so this call performs no
+ * cudaMalloc / cudaFree and calls nothing that allocates.  Every GPU that loads
+ * the library carries that array until the process exits.
+ *
+ *   params[r]  (host array of device pointers) fp32 model of rank r, n elements,
+ *              16-byte aligned; overwritten with the weighted average
+ *   weights[r] (host array) normalised FedAvg weight of rank r
+ *   n          elements per model: a multiple of 8, at most 262144
+ *   status_out (nullable, device int32[4 * n_ranks]) per-rank status words,
+ *              same meaning as for the reduce kernels
+ *
+ * Anything larger (more ranks, bigger models) is refused with a non-zero return
+ * and a message in p2pfl_last_error(); use p2pfl_gossip_fused_emulated with inboxes
+ * you own instead.
+ *
+ * The first call on a device looks up the array's device address
+ * (cudaGetSymbolAddress); make that first call before starting any stream
+ * capture on that device.  All calls share the one array and it keeps what the
+ * previous call left (this entry point re-zeroes the flags and status itself):
+ * two calls whose GPU work overlaps - different streams, different threads -
+ * race on it.  Serialise them. */
+int p2pfl_gossip_exchange_static(int device, void* stream, int n_ranks, float* const* params,
+                                 const float* weights, uint64_t n, uint64_t timeout_cycles,
+                                 int32_t* status_out);
+
 /* --------------------------------------------------------------------- GEMM
  * K1/K2/K4/K8: D[M,N] = A[M,K] . B[N,K]^T on tcgen05 tensor cores, operands bf16
  * K-major staged by TMA (128B swizzle), fp32 accumulators in TMEM, fused
