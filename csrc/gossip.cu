@@ -42,8 +42,8 @@ __device__ __forceinline__ uint4 ld_inbox_u4(const void* p) {
 }
 
 // ---------------------------------------------------------------------- push
-__device__ __forceinline__ void push_tile(const float* __restrict__ src, uint64_t n, uint32_t tile, uint32_t seq,
-                                          const p2pfl_push_table& t, uint32_t ti) {
+__device__ __forceinline__ void push_tile_data(const float* __restrict__ src, uint64_t n, uint32_t tile,
+                                               const p2pfl_push_table& t, uint32_t ti) {
   const uint64_t t0 = (uint64_t)ti * tile;
   const uint32_t len = (uint32_t)((n - t0) < tile ? (n - t0) : tile);
   if (t.wire_bf16) {
@@ -89,18 +89,24 @@ __device__ __forceinline__ void push_tile(const float* __restrict__ src, uint64_
       }
     }
   }
-  __syncthreads();  // every store of this tile happens-before the flag writers below
-  if ((int)threadIdx.x < t.n_peers) {
-    __threadfence_system();
-    st_release_sys_u32(t.flags[threadIdx.x] + ti, seq);
-  }
+  __syncthreads();  // every store of this tile happens-before the flag writers
+}
+
+// Publish tile `ti`: st.release.sys orders every store this CTA made before the
+// preceding barrier ahead of the flag (release is cumulative over bar.sync), so no
+// separate __threadfence_system() is needed.
+__device__ __forceinline__ void publish_tile(uint32_t seq, const p2pfl_push_table& t, uint32_t ti) {
+  if ((int)threadIdx.x < t.n_peers) st_release_sys_u32(t.flags[threadIdx.x] + ti, seq);
 }
 
 // `cta` / `n_cta` let several logical ranks share one launch (emulation).
 __device__ void push_phase(const float* __restrict__ src, uint64_t n, uint32_t tile, uint32_t seq,
                            const p2pfl_push_table& t, int cta, int n_cta) {
   const uint32_t n_tiles = (uint32_t)((n + tile - 1) / tile);
-  for (uint32_t ti = cta; ti < n_tiles; ti += n_cta) push_tile(src, n, tile, seq, t, ti);
+  for (uint32_t ti = cta; ti < n_tiles; ti += n_cta) {
+    push_tile_data(src, n, tile, t, ti);
+    publish_tile(seq, t, ti);
+  }
 }
 
 // -------------------------------------------------------------------- reduce
@@ -140,87 +146,54 @@ __device__ __forceinline__ void reduce_tile(float* __restrict__ params, __nv_bfl
   const bool round_own = t.round_self && t.wire_bf16;
 
   // ---- accumulate in slot order, local model inserted at self_pos ---------
-  // two 8-element vectors per thread-iteration so the loads of both are in flight together
-  for (uint32_t e0 = threadIdx.x * 8; e0 < len; e0 += kThreads * 8 * 2) {
-    float own[2][8];
-    float acc[2][8];
-    bool live[2];
+  for (uint32_t e = threadIdx.x * 8; e < len; e += kThreads * 8) {
+    float own[8], acc[8];
+    {
+      const float4 a = *reinterpret_cast<const float4*>(params + t0 + e);
+      const float4 b = *reinterpret_cast<const float4*>(params + t0 + e + 4);
+      own[0] = a.x; own[1] = a.y; own[2] = a.z; own[3] = a.w;
+      own[4] = b.x; own[5] = b.y; own[6] = b.z; own[7] = b.w;
+    }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      const uint32_t e = e0 + u * kThreads * 8;
-      live[u] = e < len;
-      if (live[u]) {
-        const float4 a = *reinterpret_cast<const float4*>(params + t0 + e);
-        const float4 b = *reinterpret_cast<const float4*>(params + t0 + e + 4);
-        own[u][0] = a.x; own[u][1] = a.y; own[u][2] = a.z; own[u][3] = a.w;
-        own[u][4] = b.x; own[u][5] = b.y; own[u][6] = b.z; own[u][7] = b.w;
-      }
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        if (round_own) own[u][k] = __bfloat162float(__float2bfloat16_rn(own[u][k]));
-        acc[u][k] = 0.f;
-      }
+    for (int k = 0; k < 8; ++k) {
+      if (round_own) own[k] = __bfloat162float(__float2bfloat16_rn(own[k]));
+      acc[k] = 0.f;
     }
     for (int j = 0; j <= t.n_slots; ++j) {
       if (j == t.self_pos) {
 #pragma unroll
-        for (int u = 0; u < 2; ++u)
-#pragma unroll
-          for (int k = 0; k < 8; ++k) acc[u][k] = fmaf(w_self, own[u][k], acc[u][k]);
+        for (int k = 0; k < 8; ++k) acc[k] = fmaf(w_self, own[k], acc[k]);
       }
       if (j == t.n_slots) break;
       const float wj = s_arrived[j] ? t.weight[j] : 0.f;
       if (wj == 0.f) continue;
       if (t.wire_bf16) {
-        uint4 v[2];
-#pragma unroll
-        for (int u = 0; u < 2; ++u)
-          if (live[u]) v[u] = ld_inbox_u4(reinterpret_cast<const __nv_bfloat16*>(t.slot[j]) + t0 + e0 + u * kThreads * 8);
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          if (!live[u]) continue;
-          const float2 p0 = unpack_bf16x2(v[u].x), p1 = unpack_bf16x2(v[u].y), p2 = unpack_bf16x2(v[u].z),
-                       p3 = unpack_bf16x2(v[u].w);
-          acc[u][0] = fmaf(wj, p0.x, acc[u][0]); acc[u][1] = fmaf(wj, p0.y, acc[u][1]);
-          acc[u][2] = fmaf(wj, p1.x, acc[u][2]); acc[u][3] = fmaf(wj, p1.y, acc[u][3]);
-          acc[u][4] = fmaf(wj, p2.x, acc[u][4]); acc[u][5] = fmaf(wj, p2.y, acc[u][5]);
-          acc[u][6] = fmaf(wj, p3.x, acc[u][6]); acc[u][7] = fmaf(wj, p3.y, acc[u][7]);
-        }
+        const uint4 v = ld_inbox_u4(reinterpret_cast<const __nv_bfloat16*>(t.slot[j]) + t0 + e);
+        const float2 p0 = unpack_bf16x2(v.x), p1 = unpack_bf16x2(v.y), p2 = unpack_bf16x2(v.z), p3 = unpack_bf16x2(v.w);
+        acc[0] = fmaf(wj, p0.x, acc[0]); acc[1] = fmaf(wj, p0.y, acc[1]);
+        acc[2] = fmaf(wj, p1.x, acc[2]); acc[3] = fmaf(wj, p1.y, acc[3]);
+        acc[4] = fmaf(wj, p2.x, acc[4]); acc[5] = fmaf(wj, p2.y, acc[5]);
+        acc[6] = fmaf(wj, p3.x, acc[6]); acc[7] = fmaf(wj, p3.y, acc[7]);
       } else {
-        uint4 v[2][2];
-#pragma unroll
-        for (int u = 0; u < 2; ++u)
-          if (live[u]) {
-            const float* sp = reinterpret_cast<const float*>(t.slot[j]) + t0 + e0 + u * kThreads * 8;
-            v[u][0] = ld_inbox_u4(sp);
-            v[u][1] = ld_inbox_u4(sp + 4);
-          }
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          if (!live[u]) continue;
-          acc[u][0] = fmaf(wj, __uint_as_float(v[u][0].x), acc[u][0]); acc[u][1] = fmaf(wj, __uint_as_float(v[u][0].y), acc[u][1]);
-          acc[u][2] = fmaf(wj, __uint_as_float(v[u][0].z), acc[u][2]); acc[u][3] = fmaf(wj, __uint_as_float(v[u][0].w), acc[u][3]);
-          acc[u][4] = fmaf(wj, __uint_as_float(v[u][1].x), acc[u][4]); acc[u][5] = fmaf(wj, __uint_as_float(v[u][1].y), acc[u][5]);
-          acc[u][6] = fmaf(wj, __uint_as_float(v[u][1].z), acc[u][6]); acc[u][7] = fmaf(wj, __uint_as_float(v[u][1].w), acc[u][7]);
-        }
+        const float* sp = reinterpret_cast<const float*>(t.slot[j]) + t0 + e;
+        const uint4 v0 = ld_inbox_u4(sp), v1 = ld_inbox_u4(sp + 4);
+        acc[0] = fmaf(wj, __uint_as_float(v0.x), acc[0]); acc[1] = fmaf(wj, __uint_as_float(v0.y), acc[1]);
+        acc[2] = fmaf(wj, __uint_as_float(v0.z), acc[2]); acc[3] = fmaf(wj, __uint_as_float(v0.w), acc[3]);
+        acc[4] = fmaf(wj, __uint_as_float(v1.x), acc[4]); acc[5] = fmaf(wj, __uint_as_float(v1.y), acc[5]);
+        acc[6] = fmaf(wj, __uint_as_float(v1.z), acc[6]); acc[7] = fmaf(wj, __uint_as_float(v1.w), acc[7]);
       }
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      if (!live[u]) continue;
-      const uint32_t e = e0 + u * kThreads * 8;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) acc[u][k] *= scale;
-      *reinterpret_cast<float4*>(params + t0 + e) = make_float4(acc[u][0], acc[u][1], acc[u][2], acc[u][3]);
-      *reinterpret_cast<float4*>(params + t0 + e + 4) = make_float4(acc[u][4], acc[u][5], acc[u][6], acc[u][7]);
-      if (params_bf16) {
-        uint4 o;
-        o.x = pack_bf16x2(acc[u][0], acc[u][1]);
-        o.y = pack_bf16x2(acc[u][2], acc[u][3]);
-        o.z = pack_bf16x2(acc[u][4], acc[u][5]);
-        o.w = pack_bf16x2(acc[u][6], acc[u][7]);
-        *reinterpret_cast<uint4*>(params_bf16 + t0 + e) = o;
-      }
+    for (int k = 0; k < 8; ++k) acc[k] *= scale;
+    *reinterpret_cast<float4*>(params + t0 + e) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(params + t0 + e + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    if (params_bf16) {
+      uint4 o;
+      o.x = pack_bf16x2(acc[0], acc[1]);
+      o.y = pack_bf16x2(acc[2], acc[3]);
+      o.z = pack_bf16x2(acc[4], acc[5]);
+      o.w = pack_bf16x2(acc[6], acc[7]);
+      *reinterpret_cast<uint4*>(params_bf16 + t0 + e) = o;
     }
   }
   if (threadIdx.x == 0 && status) atomicAdd(status + 1, 1);
@@ -248,10 +221,13 @@ __device__ void fused_phase(float* __restrict__ params, __nv_bfloat16* __restric
   const uint32_t n_tiles = (uint32_t)((n + tile - 1) / tile);
   const uint32_t mine = n_tiles > (uint32_t)cta ? (n_tiles - cta + n_cta - 1) / n_cta : 0;
   for (uint32_t k = 0; k < mine + kLag; ++k) {
-    if (k < mine) push_tile(params, n, tile, seq, push, cta + k * n_cta);
+    if (k < mine) push_tile_data(params, n, tile, push, cta + k * n_cta);
     if (k >= kLag)
       reduce_tile(params, params_bf16, n, tile, seq, red, abort_flag, timeout_cycles, status, cta + (k - kLag) * n_cta,
                   s_arrived);
+    // flags go out AFTER the reduce work of this step: the tile's remote stores have had
+    // that long to drain, so the release fence does not stall on an NVLink round trip
+    if (k < mine) publish_tile(seq, push, cta + k * n_cta);
   }
 }
 
@@ -266,7 +242,7 @@ gossip_push_kernel(const float* __restrict__ src, uint64_t n, uint32_t tile, uin
   push_phase(src, n, tile, seq, s_push, blockIdx.x, gridDim.x);
 }
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 gossip_reduce_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ params_bf16, uint64_t n, uint32_t tile,
                      uint32_t seq, const __grid_constant__ p2pfl_reduce_table t,
                      const uint32_t* __restrict__ abort_flag, uint64_t timeout_cycles, int32_t* status) {
@@ -279,7 +255,7 @@ gossip_reduce_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ par
 // G1+G2: one launch.  Every CTA first pushes its tiles (no waiting), then
 // reduces the same tile indices; peers run the same schedule, so tile i of
 // every contributor is in flight while tile i-1 is being accumulated.
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 gossip_fused_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ params_bf16, uint64_t n, uint32_t tile,
                     uint32_t seq, const __grid_constant__ p2pfl_push_table push,
                     const __grid_constant__ p2pfl_reduce_table red, const uint32_t* __restrict__ abort_flag,
@@ -304,7 +280,7 @@ struct EmuArgs {
   const p2pfl_reduce_table* reduce; // device array [R]
 };
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 gossip_fused_emulated_kernel(EmuArgs a, uint64_t n, uint32_t tile, uint32_t seq, uint64_t timeout_cycles,
                              int32_t* status) {
   const int r = blockIdx.y;
