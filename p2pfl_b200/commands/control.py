@@ -18,8 +18,9 @@ from p2pfl_b200.node_state import NodeState
 class HeartbeatCommand(Command):
     """``beat [time]`` (reference: commands/heartbeat_command.py:39-52)."""
 
-    def __init__(self, heartbeater: Any) -> None:
+    def __init__(self, heartbeater: Any, on_neighbors: Any = None) -> None:
         self._hb = heartbeater
+        self._on_neighbors = on_neighbors
 
     @staticmethod
     def get_name() -> str:
@@ -27,6 +28,8 @@ class HeartbeatCommand(Command):
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
         self._hb.beat(source, float(args[0]))
+        if len(args) > 1 and self._on_neighbors is not None:
+            self._on_neighbors(source, [n for n in args[1].split(",") if n])
 
 
 class StartLearningCommand(Command):

@@ -187,6 +187,36 @@ class GrpcTransport(Transport):
         return res.error if res.HasField("error") else None
 
 
+    def _call(self, env: Envelope):
+        pb = to_pb(env)
+        name = "send_message" if isinstance(env, Message) else "send_weights"
+        timeout = Settings.GRPC_TIMEOUT
+        if name == "send_weights":
+            timeout += len(pb.weights) / 50e6
+        return name, pb, timeout
+
+    def deliver_many(self, targets, env):  # type: ignore[override]
+        """All RPCs are issued as futures first and collected afterwards."""
+        name, pb, timeout = self._call(env)
+        futs = []  # (future | None, issue error | None); grpc futures are themselves RpcError instances
+        for addr, link in targets:
+            try:
+                futs.append((link.calls[name].future(pb, timeout=timeout), None))
+            except Exception as e:
+                futs.append((None, e))
+        out = []
+        for f, err in futs:
+            if f is None:
+                out.append(err)
+                continue
+            try:
+                res = f.result()
+                out.append(res.error if res.HasField("error") else None)
+            except Exception as e:
+                out.append(e)
+        return out
+
+
 class GrpcCommunicationProtocol(BaseProtocol):
     """``Node(model, data, protocol=GrpcCommunicationProtocol)`` (the default)."""
 

@@ -119,6 +119,22 @@ class Transport(abc.ABC):
         """Send and wait for the answer; returns the peer's error string or
         None.  Raises on transport failure."""
 
+    def deliver_many(self, targets: List[Any], env: Envelope) -> List[Any]:
+        """Deliver one envelope to several ``(addr, link)`` targets; one result per target
+        (error string, None, or the exception).  Transports that can overlap the
+        round trips override this."""
+        return _deliver_many_sequential(self, targets, env)
+
+
+def _deliver_many_sequential(transport: "Transport", targets: List[Any], env: Envelope) -> List[Any]:
+    out: List[Any] = []
+    for addr, link in targets:
+        try:
+            out.append(transport.deliver(addr, link, env))
+        except Exception as e:  # noqa: PERF203
+            out.append(e)
+    return out
+
 
 class _ServerHandle:
     """``protocol._server.stop()`` is reached into by the fault-injection tests
@@ -148,9 +164,10 @@ class BaseProtocol(CommunicationProtocol):
         self._server = _ServerHandle(transport)
         from p2pfl_b200.commands.control import HeartbeatCommand
 
-        self.add_command(HeartbeatCommand(self._heartbeater))
+        self.add_command(HeartbeatCommand(self._heartbeater, self.note_direct_neighbors_of))
         self._running = False
         self._terminated = threading.Event()
+        self._direct_of: Dict[str, Any] = {}  # node -> set of its direct neighbours (from its beats)
 
     # ------------------------------------------------------------ lifecycle
     def start(self) -> None:
@@ -245,15 +262,31 @@ class BaseProtocol(CommunicationProtocol):
                     pass
 
     def broadcast(self, msg: Message, node_list: Optional[List[str]] = None) -> None:
-        targets = node_list if node_list is not None else list(self._neighbors.get_all(only_direct=True))
-        for nei in targets:
-            try:
-                self.send(nei, msg)
-            except NeighborNotConnectedError:
-                pass
+        """Send to every direct neighbour (or the direct ones among ``node_list``); the
+        round trips overlap when the transport supports it."""
+        direct = self._neighbors.get_all(only_direct=True)
+        names = [n for n in (node_list if node_list is not None else direct) if n in direct]
+        targets = [(n, direct[n].link) for n in names]
+        if not targets:
+            return
+        results = self._transport.deliver_many(targets, msg)
+        for (nei, _), res in zip(targets, results):
+            if res is None:
+                continue
+            logger.info(self.addr, f"send of '{msg.cmd}' to {nei} failed ({res}); removing neighbour")
+            self._neighbors.remove(nei, disconnect_msg=True)
 
     def _broadcast_beat(self, now: float) -> None:
-        self.broadcast(self.build_msg(HEARTBEAT_CMD, [str(now)]))
+        # second argument (ignored by reference nodes): my direct neighbours, so that
+        # receivers need not relay my broadcasts to nodes I reach myself
+        args = [str(now)]
+        direct = list(self._neighbors.get_all(only_direct=True))
+        if Settings.RELAY_PRUNING and len(direct) <= Settings.RELAY_PRUNING_MAX_LIST:
+            args.append(",".join(sorted(direct)))
+        self.broadcast(self.build_msg(HEARTBEAT_CMD, args))
+
+    def note_direct_neighbors_of(self, source: str, names: List[str]) -> None:
+        self._direct_of[source] = set(names)
 
     # ------------------------------------------------------------ neighbours
     def connect(self, addr: str, non_direct: bool = False) -> bool:
@@ -295,7 +328,10 @@ class BaseProtocol(CommunicationProtocol):
         if not self._gossiper.check_and_set_processed(msg.hash):
             return None
         if msg.ttl > 1:
-            targets = [n for n in self._neighbors.get_all(only_direct=True) if n != msg.source]
+            # flood to my direct neighbours, except the originator and - topology-aware
+            # pruning - those the originator advertises it reaches directly
+            covered = self._direct_of.get(msg.source, ()) if Settings.RELAY_PRUNING else ()
+            targets = [n for n in self._neighbors.get_all(only_direct=True) if n != msg.source and n not in covered]
             if targets:
                 self._gossiper.add_message(msg.relay_copy(), targets)
         cmd = self._commands.get(msg.cmd)

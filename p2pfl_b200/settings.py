@@ -67,6 +67,10 @@ class Settings:
     """Wire dtype of the device data plane: 'bf16' (inbox mode B) or 'fp32'."""
     DEVICE_TILE_ELEMS: int = 16384
     """Elements per data-plane tile (one arrival flag per tile)."""
+    RELAY_PRUNING: bool = True
+    """A relay skips neighbours the originator reaches directly (it says so in its
+    heartbeats): a full mesh then costs N-1 messages per broadcast, not (N-1)^2."""
+    RELAY_PRUNING_MAX_LIST: int = 64
     FUSED_EXCHANGE: bool = True
     """Use the single-kernel push+FedAvg exchange whenever the whole train set has
     device arenas on distinct GPUs; otherwise models are pulled one by one."""

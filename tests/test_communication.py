@@ -195,3 +195,57 @@ def test_unix_socket_transport(tmp_path):
         wait_convergence([a, b], 1, only_direct=True)
     finally:
         _stop([a, b])
+
+
+def test_relay_pruning_in_a_clique_and_reach_on_a_line():
+    """In a full mesh a broadcast costs N-1 deliveries (peers advertise their direct
+    neighbours in their beats, so nobody relays); on a line it still floods end to end."""
+    from p2pfl_b200.commands.command import Command
+
+    class Probe(Command):
+        hits = []
+
+        def __init__(self, who):
+            self.who = who
+
+        @staticmethod
+        def get_name():
+            return "probe2"
+
+        def execute(self, source, round, *args, **kw):
+            Probe.hits.append(self.who)
+
+    for topology in ("clique", "line"):
+        nodes = _nodes(4, InMemoryCommunicationProtocol)
+        deliveries = []
+        try:
+            for i, n in enumerate(nodes):
+                n._communication_protocol.add_command(Probe(i))
+                eng = n._communication_protocol
+                orig = eng.on_message
+
+                def counted(msg, _orig=orig, _i=i):
+                    if msg.cmd == "probe2":
+                        deliveries.append(_i)
+                    return _orig(msg)
+
+                eng.on_message = counted
+            if topology == "clique":
+                for i in range(4):
+                    for j in range(i):
+                        nodes[i].connect(nodes[j].addr)
+                wait_convergence(nodes, 3, only_direct=True)
+            else:
+                for i in range(3):
+                    nodes[i + 1].connect(nodes[i].addr)
+                wait_convergence(nodes, 3, only_direct=False)
+            time.sleep(Settings.HEARTBEAT_PERIOD * 2.5)  # let the beats advertise neighbour lists
+            Probe.hits = []
+            p = nodes[0]._communication_protocol
+            p.broadcast(p.build_msg("probe2"))
+            time.sleep(0.5)
+            assert sorted(Probe.hits) == [1, 2, 3], (topology, Probe.hits)
+            if topology == "clique":
+                assert len(deliveries) == 3, deliveries  # no redundant relays
+        finally:
+            _stop(nodes)
