@@ -211,6 +211,10 @@ class TorchLearner(NodeLearner):
             return F.cross_entropy(logits.reshape(-1, logits.shape[-1]).float(), y.reshape(-1))
         return F.cross_entropy(logits.float(), y)
 
+    def _autocast(self) -> Any:
+        on = self.device.type == "cuda" and (Settings.AMP_BF16 or bool(getattr(self.model, "amp_bf16", False)))
+        return torch.autocast(device_type=self.device.type, dtype=torch.bfloat16, enabled=on)
+
     def begin_round(self, round: Optional[int]) -> None:
         self._round_steps = 0
 
@@ -231,7 +235,8 @@ class TorchLearner(NodeLearner):
                 x = x.to(self.device, non_blocking=True)
                 y = y.to(self.device, non_blocking=True)
                 opt.zero_grad(set_to_none=True)
-                loss = self._loss(self.model(x), y)
+                with self._autocast():
+                    loss = self._loss(self.model(x), y)
                 loss.backward()
                 opt.step()
                 if step % self.LOG_EVERY == 0:
@@ -258,7 +263,8 @@ class TorchLearner(NodeLearner):
         for x, y in loader:
             x = x.to(self.device, non_blocking=True)
             y = y.to(self.device, non_blocking=True)
-            logits = self.model(x)
+            with self._autocast():
+                logits = self.model(x)
             if logits.dim() == 3:
                 logits, y = logits.reshape(-1, logits.shape[-1]), y.reshape(-1)
             loss_sum += F.cross_entropy(logits.float(), y, reduction="sum")

@@ -67,6 +67,8 @@ class Settings:
     """Wire dtype of the device data plane: 'bf16' (inbox mode B) or 'fp32'."""
     DEVICE_TILE_ELEMS: int = 16384
     """Elements per data-plane tile (one arrival flag per tile)."""
+    AMP_BF16: bool = False
+    """Eager (autograd) learners run forward/backward under bf16 autocast on CUDA."""
     RELAY_PRUNING: bool = True
     """A relay skips neighbours the originator reaches directly (it says so in its
     heartbeats): a full mesh then costs N-1 messages per broadcast, not (N-1)^2."""
