@@ -16,12 +16,32 @@ inline int grid_for(uint64_t work_items, int device, int per_sm = 8) {
   return (int)(blocks < cap ? blocks : cap);
 }
 
+struct TransposeBatch {
+  p2pfl_transpose_desc d[16];
+  int32_t tile_start[17];  // prefix sum of 32x32 tiles per matrix
+  int32_t count;
+};
+
+// write element `idx` of the flat fp32 arena into every bf16 transposed copy that covers it
+__device__ __forceinline__ void scatter_transposed(const TransposeBatch& tb, __nv_bfloat16* __restrict__ wt, uint64_t idx,
+                                                   float v) {
+  for (int k = 0; k < tb.count; ++k) {
+    const p2pfl_transpose_desc& d = tb.d[k];
+    const uint64_t rel = idx - d.src_off;
+    if (idx >= d.src_off && rel < (uint64_t)d.rows * d.cols) {
+      const uint32_t r = (uint32_t)(rel / (uint32_t)d.cols), c = (uint32_t)(rel - (uint64_t)r * d.cols);
+      wt[d.dst_off + (uint64_t)c * d.ld_t + r] = __float2bfloat16_rn(v);
+    }
+  }
+}
+
 // --------------------------------------------------------------------- Adam
 // reference: torch.optim.Adam defaults as used by mlp.py:71-73 / cnn.py:89-91
 __global__ void __launch_bounds__(kThreads)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
             __nv_bfloat16* __restrict__ p16, uint64_t n, float lr, float b1, float b2, float eps, float wd,
-            const int32_t* __restrict__ step_ptr, int32_t step_offset) {
+            const int32_t* __restrict__ step_ptr, int32_t step_offset, __nv_bfloat16* __restrict__ wt,
+            const __grid_constant__ TransposeBatch tb) {
   const int t = (step_ptr ? *step_ptr : 0) + step_offset;
   const float bc1 = 1.f - powf(b1, (float)t);
   const float bc2 = 1.f - powf(b2, (float)t);
@@ -48,6 +68,10 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
     reinterpret_cast<float4*>(m)[i] = make_float4(me[0], me[1], me[2], me[3]);
     reinterpret_cast<float4*>(v)[i] = make_float4(ve[0], ve[1], ve[2], ve[3]);
     if (p16) reinterpret_cast<uint2*>(p16)[i] = make_uint2(pack_bf16x2(pe[0], pe[1]), pack_bf16x2(pe[2], pe[3]));
+    if (wt) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) scatter_transposed(tb, wt, i * 4 + k, pe[k]);
+    }
   }
   // tail (n not a multiple of 4)
   for (uint64_t i = (n4 << 2) + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -59,6 +83,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
     m[i] = mk;
     v[i] = vk;
     if (p16) p16[i] = __float2bfloat16_rn(pk);
+    if (wt) scatter_transposed(tb, wt, i, pk);
   }
 }
 
@@ -93,12 +118,6 @@ cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, uint
 }
 
 // ------------------------------------------------------- batched transpose
-struct TransposeBatch {
-  p2pfl_transpose_desc d[16];
-  int32_t tile_start[17];  // prefix sum of 32x32 tiles per matrix
-  int32_t count;
-};
-
 __global__ void __launch_bounds__(256)
 transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, TransposeBatch tb) {
   __shared__ float tile[32][33];
@@ -209,8 +228,27 @@ int p2pfl_adam_step(int device, void* stream, float* p, const float* g, float* m
   P2PFL_REQUIRE(p && g && m && v, "null pointer passed to p2pfl_adam_step");
   P2PFL_REQUIRE((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "adam buffers must be 16-byte aligned");
   P2PFL_CUDA_OK(cudaSetDevice(device));
+  TransposeBatch tb;
+  tb.count = 0;
   adam_kernel<<<grid_for(n / 4 + 1, device), kThreads, 0, as_stream(stream)>>>(
-      p, g, m, v, (__nv_bfloat16*)p_bf16, n, lr, beta1, beta2, eps, weight_decay, step_ptr, step_offset);
+      p, g, m, v, (__nv_bfloat16*)p_bf16, n, lr, beta1, beta2, eps, weight_decay, step_ptr, step_offset, nullptr, tb);
+  P2PFL_LAUNCH_OK();
+  return 0;
+}
+
+int p2pfl_adam_step_t(int device, void* stream, float* p, const float* g, float* m, float* v, void* p_bf16, uint64_t n,
+                      float lr, float beta1, float beta2, float eps, float weight_decay, const int32_t* step_ptr,
+                      int32_t step_offset, void* wt_bf16, const p2pfl_transpose_desc* descs, int count) {
+  P2PFL_REQUIRE(p && g && m && v, "null pointer passed to p2pfl_adam_step_t");
+  P2PFL_REQUIRE((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "adam buffers must be 16-byte aligned");
+  P2PFL_REQUIRE(count >= 0 && count <= 16 && (count == 0 || (wt_bf16 && descs)), "bad transpose list");
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  TransposeBatch tb;
+  tb.count = count;
+  for (int i = 0; i < count; ++i) tb.d[i] = descs[i];
+  adam_kernel<<<grid_for(n / 4 + 1, device), kThreads, 0, as_stream(stream)>>>(
+      p, g, m, v, (__nv_bfloat16*)p_bf16, n, lr, beta1, beta2, eps, weight_decay, step_ptr, step_offset,
+      count ? (__nv_bfloat16*)wt_bf16 : nullptr, tb);
   P2PFL_LAUNCH_OK();
   return 0;
 }

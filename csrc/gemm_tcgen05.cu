@@ -19,6 +19,7 @@
 // orientations instead (see learning/b200_learner.py), which keeps every GEMM
 // of the train step on this one kernel.
 #include <cuda.h>
+#include <string.h>
 
 #include "common.cuh"
 
@@ -138,19 +139,38 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
   return d;
 }
 
-// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=BN
-template <int BN>
-__device__ __forceinline__ constexpr uint32_t make_idesc() {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=bn
+__device__ __forceinline__ uint32_t make_idesc(uint32_t bn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 }
 
+constexpr int kMaxGroup = 4;
+constexpr int kMaxBN = 256;
+constexpr uint32_t kStageBytes = kTileABytes + kMaxBN * BK * 2;  // smem ring is sized for the widest tile
+
+// Up to four independent GEMMs per launch (blockIdx.z picks one); each has its own
+// tensor maps, epilogue and N-tile width bn in {32, 64, 128, 256}.
+struct GroupedArgs {
+  CUtensorMap ma[kMaxGroup];
+  CUtensorMap mb[kMaxGroup];
+  Epilogue ep[kMaxGroup];
+  int32_t M[kMaxGroup], N[kMaxGroup], K[kMaxGroup], bn[kMaxGroup];
+  int32_t count;
+};
+
 // ------------------------------------------------------------------- kernel
-template <int BN>
 __global__ void __launch_bounds__(kThreadsGemm, 1)
-gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, Epilogue ep, int M,
-               int N, int K) {
-  constexpr uint32_t kTileBBytes = BN * BK * 2;
-  constexpr uint32_t kStageBytes = kTileABytes + kTileBBytes;
+gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
+  const int prob = blockIdx.z;
+  const int M = g.M[prob], N = g.N[prob], K = g.K[prob];
+  const uint32_t bn = (uint32_t)g.bn[prob];
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * (int)bn;
+  if (m0 >= M || n0 >= N) return;  // grid is the union of the problems' tile grids
+  const CUtensorMap* tma_a = &g.ma[prob];
+  const CUtensorMap* tma_b = &g.mb[prob];
+  const Epilogue& ep = g.ep[prob];
+  const uint32_t stage_tx = kTileABytes + bn * BK * 2;
 
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B tiles must start on 1024-byte boundaries
@@ -162,13 +182,11 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BM;
-  const int n0 = blockIdx.y * BN;
   const int num_kb = (K + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_a)) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tma_b)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tma_a)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tma_b)) : "memory");
 #pragma unroll
     for (int s = 0; s < kStages; ++s) {
       mbar_init(smem_u32(&full_bar[s]), 1);
@@ -177,7 +195,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     mbar_init(smem_u32(&tmem_full_bar), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), BN);
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), bn);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -191,15 +209,15 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         const uint32_t phase = (uint32_t)(kb / kStages) & 1u;
         mbar_wait(smem_u32(&empty_bar[s]), phase ^ 1u);
         const uint32_t bar = smem_u32(&full_bar[s]);
-        mbar_expect_tx(bar, kStageBytes);
+        mbar_expect_tx(bar, stage_tx);
         const uint32_t a_dst = smem_u32(smem + (size_t)s * kStageBytes);
-        tma_load_2d(&tma_a, bar, a_dst, kb * BK, m0);
-        tma_load_2d(&tma_b, bar, a_dst + kTileABytes, kb * BK, n0);
+        tma_load_2d(tma_a, bar, a_dst, kb * BK, m0);
+        tma_load_2d(tma_b, bar, a_dst + kTileABytes, kb * BK, n0);
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc<BN>();
+    const uint32_t idesc = make_idesc(bn);
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % kStages;
       const uint32_t phase = (uint32_t)(kb / kStages) & 1u;
@@ -227,8 +245,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     mbar_wait(smem_u32(&tmem_full_bar), 0);
     tc_fence_after();
     const float bias_row = (ep.bias && ep.bias_per_row && m < M) ? ep.bias[m] : 0.f;
+    const bool single_n_tile = gridDim.y == 1 || (int)bn >= N;
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
+    for (int c = 0; c < (int)bn / 32; ++c) {
       const int nb = n0 + c * 32;
       if (nb >= N) break;
       uint32_t r[32];
@@ -254,7 +273,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; ++j)
             if (j < valid) s += x[j];
-          atomicAdd(ep.rowsum + m, s);
+          // one N tile of <= 32 columns owns the whole row: plain store, no zero-init needed
+          if (single_n_tile && N <= 32) ep.rowsum[m] = s;
+          else atomicAdd(ep.rowsum + m, s);
         }
         if (ep.out_f32) {
           float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
@@ -304,7 +325,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, BN);
+    tmem_dealloc(tmem_base, bn);
   }
 }
 
@@ -346,32 +367,15 @@ int make_map(CUtensorMap* map, const void* base, int rows, int cols, int ld, int
   return 0;
 }
 
-template <int BN>
-int launch(int device, cudaStream_t stream, const p2pfl_gemm_args& a, const Epilogue& ep) {
-  CUtensorMap ma, mb;
-  if (int rc = make_map(&ma, a.A, a.M, a.K, a.lda, BM)) return rc;
-  if (int rc = make_map(&mb, a.B, a.N, a.K, a.ldb, BN)) return rc;
-  constexpr size_t smem = (size_t)kStages * (kTileABytes + BN * BK * 2) + 1024;
-  static bool attr_set[64] = {false};
-  if (device >= 0 && device < 64 && !attr_set[device]) {
-    P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_tn_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set[device] = true;
-  }
-  dim3 grid((a.M + BM - 1) / BM, (a.N + BN - 1) / BN, 1);
-  gemm_tn_kernel<BN><<<grid, kThreadsGemm, smem, stream>>>(ma, mb, ep, a.M, a.N, a.K);
-  P2PFL_LAUNCH_OK();
-  return 0;
-}
+int pick_bn(int N) { return N <= 32 ? 32 : N <= 64 ? 64 : N <= 128 ? 128 : 256; }
 
-}  // namespace
-
-extern "C" int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* args) {
-  P2PFL_REQUIRE(args != nullptr, "null args");
-  const p2pfl_gemm_args& a = *args;
+int fill_problem(GroupedArgs& g, int idx, const p2pfl_gemm_args& a) {
   P2PFL_REQUIRE(a.A && a.B && a.M > 0 && a.N > 0 && a.K > 0, "bad GEMM shape or operands");
   P2PFL_REQUIRE(a.out_f32 || a.out_bf16 || a.out_f32_t || a.out_bf16_t || a.rowsum, "GEMM needs an output");
-  P2PFL_CUDA_OK(cudaSetDevice(device));
-  Epilogue ep;
+  const int bn = pick_bn(a.N);
+  if (int rc = make_map(&g.ma[idx], a.A, a.M, a.K, a.lda, BM)) return rc;
+  if (int rc = make_map(&g.mb[idx], a.B, a.N, a.K, a.ldb, bn)) return rc;
+  Epilogue& ep = g.ep[idx];
   ep.bias = a.bias;
   ep.mask = reinterpret_cast<const __nv_bfloat16*>(a.mask);
   ep.out_f32 = a.out_f32;
@@ -387,9 +391,43 @@ extern "C" int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* ar
   ep.ld_bf16_t = a.ld_bf16_t;
   ep.bias_per_row = a.bias_per_row;
   ep.relu = a.relu;
-  cudaStream_t s = as_stream(stream);
-  if (a.N <= 32) return launch<32>(device, s, a, ep);
-  if (a.N <= 64) return launch<64>(device, s, a, ep);
-  if (a.N <= 128) return launch<128>(device, s, a, ep);
-  return launch<256>(device, s, a, ep);
+  g.M[idx] = a.M;
+  g.N[idx] = a.N;
+  g.K[idx] = a.K;
+  g.bn[idx] = bn;
+  return 0;
+}
+
+int launch_group(int device, cudaStream_t stream, const p2pfl_gemm_args* args, int count) {
+  P2PFL_REQUIRE(args != nullptr && count >= 1 && count <= kMaxGroup, "a grouped GEMM launch takes 1..4 problems");
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  GroupedArgs g;
+  memset(&g, 0, sizeof(g));
+  g.count = count;
+  int gx = 0, gy = 0;
+  for (int i = 0; i < count; ++i) {
+    if (int rc = fill_problem(g, i, args[i])) return rc;
+    const int tx = (args[i].M + BM - 1) / BM, ty = (args[i].N + g.bn[i] - 1) / g.bn[i];
+    gx = tx > gx ? tx : gx;
+    gy = ty > gy ? ty : gy;
+  }
+  constexpr size_t smem = (size_t)kStages * kStageBytes + 1024;
+  static bool attr_set[64] = {false};
+  if (device >= 0 && device < 64 && !attr_set[device]) {
+    P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set[device] = true;
+  }
+  gemm_tn_kernel<<<dim3(gx, gy, count), kThreadsGemm, smem, stream>>>(g);
+  P2PFL_LAUNCH_OK();
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* args) {
+  return launch_group(device, as_stream(stream), args, 1);
+}
+
+extern "C" int p2pfl_gemm_tn_grouped(int device, void* stream, const p2pfl_gemm_args* args, int count) {
+  return launch_group(device, as_stream(stream), args, count);
 }

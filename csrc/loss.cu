@@ -12,12 +12,20 @@ namespace {
 __global__ void __launch_bounds__(256)
 softmax_xent_kernel(const float* __restrict__ logits, int ld_logits, const int32_t* __restrict__ labels, int B, int C,
                     __nv_bfloat16* __restrict__ dl, int ld_d, __nv_bfloat16* __restrict__ dlt, int ld_dt,
-                    float* __restrict__ dbias, float* __restrict__ loss_sum) {
+                    float* __restrict__ dbias, float* __restrict__ loss_sum, int single_block) {
+  // single_block: one CTA owns every row, so the bias gradient is reduced in shared
+  // memory and STORED (the training step's case, B <= 256); otherwise it is
+  // accumulated with atomics into a buffer the host zeroed
+  __shared__ float s_db[1024];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps = blockDim.x >> 5;
   const float inv_b = 1.f / (float)B;
   float block_loss = 0.f;
+  if (single_block) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) s_db[c] = 0.f;
+    __syncthreads();
+  }
   for (int row = blockIdx.x * warps + warp; row < B; row += gridDim.x * warps) {
     const float* x = logits + (uint64_t)row * ld_logits;
     float mx = -INFINITY;
@@ -35,9 +43,13 @@ softmax_xent_kernel(const float* __restrict__ logits, int ld_logits, const int32
       if (dl) dl[(uint64_t)row * ld_d + c] = gb;
       if (dlt) dlt[(uint64_t)c * ld_dt + row] = gb;
       // the bias gradient is the column sum of exactly what the GEMMs will see
-      if (dbias) atomicAdd(dbias + c, __bfloat162float(gb));
+      if (dbias) atomicAdd(single_block ? s_db + c : dbias + c, __bfloat162float(gb));
     }
     if (lane == 0 && y >= 0 && y < C) block_loss += lse - x[y];
+  }
+  if (single_block && dbias) {
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) dbias[c] = s_db[c];
   }
   if (loss_sum) {
     __shared__ float sh[8];
@@ -117,11 +129,13 @@ int p2pfl_softmax_xent(int device, void* stream, const float* logits, int ld_log
                        void* dlogits_bf16, int ld_d, void* dlogits_t_bf16, int ld_dt, float* dbias, float* loss_sum) {
   P2PFL_REQUIRE(logits && labels && B > 0 && C > 0, "bad arguments to p2pfl_softmax_xent");
   P2PFL_CUDA_OK(cudaSetDevice(device));
-  int blocks = (B + 7) / 8;
+  const int single = (B <= 256 && C <= 1024) ? 1 : 0;
+  int blocks = single ? 1 : (B + 7) / 8;
   int cap = sm_count(device) * 4;
+  if (!single && dbias) P2PFL_CUDA_OK(cudaMemsetAsync(dbias, 0, sizeof(float) * C, as_stream(stream)));
   softmax_xent_kernel<<<blocks < cap ? blocks : cap, 256, 0, as_stream(stream)>>>(
       logits, ld_logits, labels, B, C, (__nv_bfloat16*)dlogits_bf16, ld_d, (__nv_bfloat16*)dlogits_t_bf16, ld_dt, dbias,
-      loss_sum);
+      loss_sum, single);
   P2PFL_LAUNCH_OK();
   return 0;
 }

@@ -35,6 +35,13 @@ int p2pfl_rt_can_access_peer(int device, int peer_device, int* out_yes);
 int p2pfl_rt_memset32(int device, void* stream, void* ptr, uint32_t value, uint64_t count);
 int p2pfl_rt_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, uint64_t* total_mem);
 
+/* One 2-D matrix inside the flat arena and where its bf16 transpose goes. */
+typedef struct p2pfl_transpose_desc_s {
+  uint64_t src_off; /* elements into src (fp32) */
+  uint64_t dst_off; /* elements into dst (bf16) */
+  int32_t rows, cols, ld_t, pad_;
+} p2pfl_transpose_desc;
+
 /* --------------------------------------------------------------- optimizers
  * K5: torch.optim.Adam.step (mlp.py:71-73, cnn.py:89-91) as ONE kernel over
  * the flat parameter arena; optionally also refreshes the bf16 working copy.
@@ -42,6 +49,12 @@ int p2pfl_rt_device_info(int device, int* sm_count, int* cc_major, int* cc_minor
 int p2pfl_adam_step(int device, void* stream, float* p, const float* g, float* m, float* v,
                     void* p_bf16 /* nullable */, uint64_t n, float lr, float beta1, float beta2,
                     float eps, float weight_decay, const int32_t* step_ptr, int32_t step_offset);
+/* Same, and additionally refreshes the bf16 TRANSPOSED copies of the listed weight
+ * matrices (operands of the dgrad GEMMs) in the same pass - one launch less per step. */
+int p2pfl_adam_step_t(int device, void* stream, float* p, const float* g, float* m, float* v,
+                      void* p_bf16, uint64_t n, float lr, float beta1, float beta2, float eps,
+                      float weight_decay, const int32_t* step_ptr, int32_t step_offset,
+                      void* wt_bf16, const struct p2pfl_transpose_desc_s* descs, int count);
 int p2pfl_sgd_step(int device, void* stream, float* p, const float* g, float* mom /* nullable */,
                    void* p_bf16 /* nullable */, uint64_t n, float lr, float momentum);
 int p2pfl_add_i32(int device, void* stream, int32_t* ptr, int32_t delta);
@@ -49,11 +62,6 @@ int p2pfl_add_i32(int device, void* stream, int32_t* ptr, int32_t delta);
 int p2pfl_cast_f32_bf16(int device, void* stream, const float* src, void* dst, uint64_t n);
 /* Batched 2-D transpose+cast: for each of `count` matrices (rows x cols fp32 at
  * src_off) write the bf16 transpose (cols x rows, leading dim ld_t) at dst_off. */
-typedef struct {
-  uint64_t src_off; /* elements into src (fp32) */
-  uint64_t dst_off; /* elements into dst (bf16) */
-  int32_t rows, cols, ld_t, pad_;
-} p2pfl_transpose_desc;
 int p2pfl_transpose_cast(int device, void* stream, const float* src, void* dst,
                          const p2pfl_transpose_desc* descs, int count);
 
@@ -61,8 +69,8 @@ int p2pfl_transpose_cast(int device, void* stream, const float* src, void* dst,
  * K3/K9: log_softmax + cross_entropy forward AND backward in one kernel
  * (mlp.py:68,78; cnn.py:73,96).  logits fp32 [B, ld_logits]; labels int32 [B].
  * Writes dlogits (already divided by B) as bf16 in both layouts the GEMMs
- * consume ([B, ld_d] and [C, ld_dt]), the last layer's bias gradient, and
- * adds the summed loss to *loss_sum. */
+ * consume ([B, ld_d] and [C, ld_dt]), the last layer's bias gradient
+ * (overwritten), and adds the summed loss to *loss_sum. */
 int p2pfl_softmax_xent(int device, void* stream, const float* logits, int ld_logits,
                        const int32_t* labels, int B, int C, void* dlogits_bf16, int ld_d,
                        void* dlogits_t_bf16, int ld_dt, float* dbias /* nullable */,
@@ -176,7 +184,8 @@ int p2pfl_gossip_exchange_static(int device, void* stream, int n_ranks, float* c
  * epilogue (mlp.py:63-67 Linear+ReLU forward, autograd dgrad/wgrad backward).
  * Epilogue, in order: + bias (per row if bias_per_row else per column), ReLU if
  * relu, zero where mask<=0 (mask bf16 [M, ld_mask], same layout as D), then any
- * of the four outputs (nullable), and row sums (rowsum[m] += sum_n D[m,n]). */
+ * of the four outputs (nullable), and row sums (rowsum[m] += sum_n D[m,n]; when
+ * N <= 32 the row sum is stored, not accumulated, so no zero-init is needed). */
 typedef struct {
   const void* A; int32_t lda;   /* bf16 [M, lda] */
   const void* B; int32_t ldb;   /* bf16 [N, ldb] */
@@ -192,6 +201,9 @@ typedef struct {
   float alpha;                          /* scales the accumulator before the epilogue */
 } p2pfl_gemm_args;
 int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* args);
+/* Up to 4 independent GEMMs in ONE launch (e.g. a layer's wgrad and dgrad, which
+ * both depend only on that layer's dZ): fewer launches on the latency-bound step. */
+int p2pfl_gemm_tn_grouped(int device, void* stream, const p2pfl_gemm_args* args, int count);
 
 /* ------------------------------------------------------------ data movement
  * K11/N8: device-resident dataset; gather a shuffled epoch in bf16, both as

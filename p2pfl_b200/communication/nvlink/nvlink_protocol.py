@@ -254,10 +254,11 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         # pulled models stay fp32 (exact): this path carries initial weights, diffusion and
         # partial aggregates, none of which is bandwidth critical; the wire dtype applies
         # to the fused exchange
-        with torch.cuda.stream(learner.stream):
+        comm = learner.comm_stream  # not the compute stream: that one may be capturing a graph
+        with torch.cuda.stream(comm):
             out = torch.empty(ref.n, dtype=torch.float32, device=learner.device)
             ops.fedavg_into([src], [1.0], out, None)  # copy kernel reading peer memory over NVLink
-        learner.stream.synchronize()  # the sender may reuse its buffer once the RPC returns
+        comm.synchronize()  # the sender may reuse its buffer once the RPC returns
         self.stats["pulled"] += 1
         self.stats["pulled_bytes"] += ref.n * 4
         extra = {k: torch.tensor(v) for k, v in ref.extra.items()}

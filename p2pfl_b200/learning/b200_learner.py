@@ -75,6 +75,9 @@ class B200Learner(TorchLearner):
         self.kernel_launches_per_epoch = 0
         super().__init__(model, data, self_addr, epochs, device)
         self.stream = torch.cuda.Stream(device=self.device)
+        # data-plane copies issued by OTHER threads (inbound pulls) must never touch the
+        # compute stream: it may be capturing a graph at that moment
+        self.comm_stream = torch.cuda.Stream(device=self.device)
 
     # --------------------------------------------------------------- storage
     def _alloc_flat(self, total: int) -> torch.Tensor:
@@ -279,7 +282,11 @@ class B200Learner(TorchLearner):
         feat = Ls[0].in_f
         ldB = act["ldB"]
         C = Ls[-1].out_f
-        self.grads.zero_()
+        # no gradient memset: every weight gradient is overwritten by its wgrad GEMM and every
+        # bias gradient is stored (not accumulated) by the CE kernel / the dgrad row sums
+        # (batches wider than one 32-column tile accumulate row sums, so they do need zeros)
+        if bsz > 32:
+            self.grads.zero_()
         self._forward(x16, feat, bsz, act, train=True)
         ops.softmax_xent(act["logits"], act["ld_logits"], y, bsz, C, act["dZ"][-1], _pad8(C), act["dZT"][-1], ldB,
                          self.grads[Ls[-1].b_off :], loss_slot)  # fmt: skip
@@ -287,19 +294,21 @@ class B200Learner(TorchLearner):
             L = Ls[li]
             # wgrad: dW[out, in] = dZ^T[out, bsz] . (X^T[in, bsz])^T   (K = batch)
             Bm = xT16 if li == 0 else act["HT"][li - 1]
-            ops.gemm_tn(act["dZT"][li], ldB, Bm, ldB, L.out_f, L.in_f, bsz,
-                        out_f32=self.grads[L.w_off :], ld_f32=L.in_f)  # fmt: skip
+            group = [ops.gemm_args(act["dZT"][li], ldB, Bm, ldB, L.out_f, L.in_f, bsz,
+                                   out_f32=self.grads[L.w_off :], ld_f32=L.in_f)]  # fmt: skip
             if li > 0:
                 # dgrad: dH^T[in, bsz] = W^T[in, out] . dZ[bsz, out]^T, masked by ReLU, bias grad = row sums
                 P = Ls[li - 1]
-                ops.gemm_tn(self.wT16[L.wt_off :], _pad8(L.out_f), act["dZ"][li], _pad8(L.out_f), L.in_f, bsz, L.out_f,
-                            mask=act["HT"][li - 1], ld_mask=ldB,
-                            out_bf16=act["dZT"][li - 1], ld_bf16=ldB,
-                            out_bf16_t=act["dZ"][li - 1] if li - 1 > 0 else None, ld_bf16_t=_pad8(P.out_f),
-                            rowsum=self.grads[P.b_off :])  # fmt: skip
-        ops.adam_step(self.flat, self.grads, self.adam_m, self.adam_v, self.w16, lr, self.adam_step, step_offset)
-        if self._tdescs:
-            ops.transpose_cast(self.flat, self.wT16, self._tdescs)
+                group.append(ops.gemm_args(
+                    self.wT16[L.wt_off :], _pad8(L.out_f), act["dZ"][li], _pad8(L.out_f), L.in_f, bsz, L.out_f,
+                    mask=act["HT"][li - 1], ld_mask=ldB, out_bf16=act["dZT"][li - 1], ld_bf16=ldB,
+                    out_bf16_t=act["dZ"][li - 1] if li - 1 > 0 else None, ld_bf16_t=_pad8(P.out_f),
+                    rowsum=self.grads[P.b_off :]))  # fmt: skip
+            # a layer's wgrad and dgrad both depend only on its dZ: one launch for the pair
+            ops.gemm_tn_grouped(self.device, group)
+        # Adam over the whole arena, refreshing the bf16 copy AND the transposed dgrad operands
+        ops.adam_step_t(self.flat, self.grads, self.adam_m, self.adam_v, self.w16, lr, self.adam_step, step_offset,
+                        self.wT16, self._tdescs)  # fmt: skip
 
     def debug_single_step(self, x: torch.Tensor, y: torch.Tensor) -> float:
         """One eager (un-graphed) fused step on the given batch; returns the mean loss.

@@ -163,6 +163,24 @@ def adam_step(
     _count()
 
 
+def adam_step_t(
+    p, g, m, v, p_bf16, lr: float, step_ptr, step_offset: int, wt_bf16, descs: Sequence[tuple],
+    beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, weight_decay: float = 0.0,
+) -> None:  # fmt: skip
+    """Adam + bf16 refresh + bf16 transposed weight copies (descs as in transpose_cast) in one launch."""
+    arr = (TransposeDesc * max(1, len(descs)))()
+    for j, (so, do, r, c, ld) in enumerate(descs):
+        arr[j] = TransposeDesc(so, do, r, c, ld, 0)
+    _check(
+        lib().p2pfl_adam_step_t(
+            _dev(p), _stream(), _p(p), _p(g), _p(m), _p(v), _p(p_bf16), C.c_uint64(p.numel()),
+            C.c_float(lr), C.c_float(beta1), C.c_float(beta2), C.c_float(eps), C.c_float(weight_decay),
+            _p(step_ptr), C.c_int32(step_offset), _p(wt_bf16), arr, C.c_int(len(descs)),
+        )
+    )  # fmt: skip
+    _count()
+
+
 def sgd_step(p, g, mom, p_bf16, lr: float, momentum: float = 0.0) -> None:
     _check(
         lib().p2pfl_sgd_step(
@@ -258,7 +276,7 @@ def fedavg_flat(models: List[torch.Tensor], weights: List[float], out_dtype: tor
 
 
 # ------------------------------------------------------------------------ GEMM
-def gemm_tn(
+def gemm_args(
     A: torch.Tensor, lda: int, B: torch.Tensor, ldb: int, M: int, N: int, K: int,
     bias: Optional[torch.Tensor] = None, bias_per_row: bool = True, relu: bool = False,
     mask: Optional[torch.Tensor] = None, ld_mask: int = 0,
@@ -267,9 +285,9 @@ def gemm_tn(
     out_f32_t: Optional[torch.Tensor] = None, ld_f32_t: int = 0,
     out_bf16_t: Optional[torch.Tensor] = None, ld_bf16_t: int = 0,
     rowsum: Optional[torch.Tensor] = None, alpha: float = 1.0,
-) -> None:  # fmt: skip
-    """D[M,N] = alpha * A[M,K] @ B[N,K]^T with the fused epilogue (tcgen05 kernel)."""
-    a = GemmArgs(
+) -> GemmArgs:  # fmt: skip
+    """Describe D[M,N] = alpha * A[M,K] @ B[N,K]^T with its fused epilogue."""
+    return GemmArgs(
         A.data_ptr(), lda, B.data_ptr(), ldb, M, N, K,
         0 if bias is None else bias.data_ptr(), int(bias_per_row), int(relu),
         0 if mask is None else mask.data_ptr(), ld_mask,
@@ -279,7 +297,20 @@ def gemm_tn(
         0 if out_bf16_t is None else out_bf16_t.data_ptr(), ld_bf16_t,
         0 if rowsum is None else rowsum.data_ptr(), alpha,
     )  # fmt: skip
+
+
+def gemm_tn(A: torch.Tensor, *args, **kwargs) -> None:
+    """One tcgen05 GEMM launch (see :func:`gemm_args` for the parameters)."""
+    a = gemm_args(A, *args, **kwargs)
     _check(lib().p2pfl_gemm_tn(_dev(A), _stream(), C.byref(a)))
+    _count()
+
+
+def gemm_tn_grouped(device: torch.device, problems: Sequence[GemmArgs]) -> None:
+    """Up to four independent GEMMs in ONE launch."""
+    arr = (GemmArgs * len(problems))(*problems)
+    dev = device.index if device.index is not None else torch.cuda.current_device()
+    _check(lib().p2pfl_gemm_tn_grouped(dev, _stream(), arr, C.c_int(len(problems))))
     _count()
 
 

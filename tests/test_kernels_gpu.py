@@ -337,3 +337,66 @@ def test_gossip_push_then_reduce_and_timeout(ops):
     finally:
         a.close()
         b.close()
+
+
+# ------------------------------------------------- launch-reduction variants
+def test_gemm_grouped_matches_single_launches(ops):
+    """A layer's wgrad and dgrad in ONE launch (different shapes, tile widths, epilogues)."""
+    torch.manual_seed(11)
+    B = 32
+    dZT = (torch.randn(128, B, device=DEV) / 8).to(torch.bfloat16)  # [out, B]
+    HT = torch.randn(256, B, device=DEV).to(torch.bfloat16)  # [in, B]
+    wT = (torch.randn(256, 128, device=DEV) / 16).to(torch.bfloat16)  # [in, out]
+    dZ = dZT.t().contiguous()  # [B, out]
+    grad_w = torch.full((128, 256), 7.0, device=DEV)
+    dHT = torch.zeros(256, B, device=DEV, dtype=torch.bfloat16)
+    dH = torch.zeros(B, 256, device=DEV, dtype=torch.bfloat16)
+    db = torch.full((256,), 5.0, device=DEV)  # stale content must be overwritten (N <= 32 stores)
+    ops.gemm_tn_grouped(
+        torch.device(DEV),
+        [
+            ops.gemm_args(dZT, B, HT, B, 128, 256, B, out_f32=grad_w, ld_f32=256),
+            ops.gemm_args(wT, 128, dZ, 128, 256, B, 128, mask=HT, ld_mask=B, out_bf16=dHT, ld_bf16=B,
+                          out_bf16_t=dH, ld_bf16_t=256, rowsum=db),
+        ],
+    )  # fmt: skip
+    ref_w = dZT.float() @ HT.float().t()
+    ref_d = torch.where(HT.float() > 0, wT.float() @ dZ.float().t(), torch.zeros(256, B, device=DEV))
+    assert torch.allclose(grad_w, ref_w, atol=2e-3, rtol=2e-3)
+    assert torch.allclose(dHT.float(), ref_d, atol=2e-2, rtol=2e-2)
+    assert torch.equal(dH, dHT.t())
+    assert torch.allclose(db, ref_d.sum(1), atol=1e-2, rtol=1e-2)
+
+
+def test_adam_with_transposed_copies(ops):
+    n = 300 * 70 + 64 + 10 * 128
+    torch.manual_seed(2)
+    p = torch.randn(n, device=DEV)
+    ref = p.clone()
+    g = torch.randn(n, device=DEV)
+    m, v, m2, v2 = (torch.zeros(n, device=DEV) for _ in range(4))
+    p16 = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+    wt = torch.zeros(70 * 304 + 128 * 16, device=DEV, dtype=torch.bfloat16)
+    descs = [(0, 0, 300, 70, 304), (300 * 70 + 64, 70 * 304, 10, 128, 16)]
+    ops.adam_step_t(p, g, m, v, p16, 1e-2, None, 1, wt, descs)
+    ops.adam_step(ref, g, m2, v2, None, 1e-2, None, 1)
+    assert torch.equal(p, ref) and torch.equal(p16, p.to(torch.bfloat16))
+    a = p[: 300 * 70].view(300, 70)
+    b = p[300 * 70 + 64 :].view(10, 128)
+    assert torch.equal(wt[: 70 * 304].view(70, 304)[:, :300], a.t().to(torch.bfloat16))
+    assert torch.equal(wt[70 * 304 :].view(128, 16)[:, :10], b.t().to(torch.bfloat16))
+
+
+def test_softmax_xent_overwrites_dbias(ops):
+    B, Cn = 32, 10
+    logits = torch.randn(B, 16, device=DEV)
+    labels = torch.randint(0, Cn, (B,), device=DEV, dtype=torch.int32)
+    dl = torch.zeros(B, 16, device=DEV, dtype=torch.bfloat16)
+    for big in (False, True):
+        Bb = 512 if big else B  # > 256 rows takes the multi-block path
+        lg = torch.randn(Bb, 16, device=DEV)
+        lb = torch.randint(0, Cn, (Bb,), device=DEV, dtype=torch.int32)
+        d = torch.zeros(Bb, 16, device=DEV, dtype=torch.bfloat16)
+        db = torch.full((Cn,), 123.0, device=DEV)
+        ops.softmax_xent(lg, 16, lb, Bb, Cn, d, 16, None, 0, db, None)
+        assert torch.allclose(db, d[:, :Cn].float().sum(0), atol=1e-4), big
