@@ -42,6 +42,8 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
             __nv_bfloat16* __restrict__ p16, uint64_t n, float lr, float b1, float b2, float eps, float wd,
             const int32_t* __restrict__ step_ptr, int32_t step_offset, __nv_bfloat16* __restrict__ wt,
             const __grid_constant__ TransposeBatch tb) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int t = (step_ptr ? *step_ptr : 0) + step_offset;
   const float bc1 = 1.f - powf(b1, (float)t);
   const float bc2 = 1.f - powf(b2, (float)t);
@@ -230,9 +232,9 @@ int p2pfl_adam_step(int device, void* stream, float* p, const float* g, float* m
   P2PFL_CUDA_OK(cudaSetDevice(device));
   TransposeBatch tb;
   tb.count = 0;
-  adam_kernel<<<grid_for(n / 4 + 1, device), kThreads, 0, as_stream(stream)>>>(
-      p, g, m, v, (__nv_bfloat16*)p_bf16, n, lr, beta1, beta2, eps, weight_decay, step_ptr, step_offset, nullptr, tb);
-  P2PFL_LAUNCH_OK();
+  P2PFL_CUDA_OK(launch_pdl(adam_kernel, dim3(grid_for(n / 4 + 1, device)), dim3(kThreads), 0, as_stream(stream), p, g, m, v,
+                           (__nv_bfloat16*)p_bf16, n, lr, beta1, beta2, eps, weight_decay, step_ptr, step_offset,
+                           (__nv_bfloat16*)nullptr, tb));
   return 0;
 }
 
@@ -246,10 +248,9 @@ int p2pfl_adam_step_t(int device, void* stream, float* p, const float* g, float*
   TransposeBatch tb;
   tb.count = count;
   for (int i = 0; i < count; ++i) tb.d[i] = descs[i];
-  adam_kernel<<<grid_for(n / 4 + 1, device), kThreads, 0, as_stream(stream)>>>(
-      p, g, m, v, (__nv_bfloat16*)p_bf16, n, lr, beta1, beta2, eps, weight_decay, step_ptr, step_offset,
-      count ? (__nv_bfloat16*)wt_bf16 : nullptr, tb);
-  P2PFL_LAUNCH_OK();
+  P2PFL_CUDA_OK(launch_pdl(adam_kernel, dim3(grid_for(n / 4 + 1, device)), dim3(kThreads), 0, as_stream(stream), p, g, m, v,
+                           (__nv_bfloat16*)p_bf16, n, lr, beta1, beta2, eps, weight_decay, step_ptr, step_offset,
+                           count ? (__nv_bfloat16*)wt_bf16 : (__nv_bfloat16*)nullptr, tb));
   return 0;
 }
 

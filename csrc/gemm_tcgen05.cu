@@ -196,10 +196,12 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), bn);
+  pdl_launch_dependents();  // let the next kernel of the chain start its own prologue
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();  // everything above overlapped the predecessor; its outputs are visible from here on
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -417,8 +419,7 @@ int launch_group(int device, cudaStream_t stream, const p2pfl_gemm_args* args, i
     P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set[device] = true;
   }
-  gemm_tn_kernel<<<dim3(gx, gy, count), kThreadsGemm, smem, stream>>>(g);
-  P2PFL_LAUNCH_OK();
+  P2PFL_CUDA_OK(launch_pdl(gemm_tn_kernel, dim3(gx, gy, count), dim3(kThreadsGemm), smem, stream, g));
   return 0;
 }
 

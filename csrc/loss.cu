@@ -17,6 +17,8 @@ softmax_xent_kernel(const float* __restrict__ logits, int ld_logits, const int32
   // memory and STORED (the training step's case, B <= 256); otherwise it is
   // accumulated with atomics into a buffer the host zeroed
   __shared__ float s_db[1024];
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps = blockDim.x >> 5;
@@ -133,10 +135,9 @@ int p2pfl_softmax_xent(int device, void* stream, const float* logits, int ld_log
   int blocks = single ? 1 : (B + 7) / 8;
   int cap = sm_count(device) * 4;
   if (!single && dbias) P2PFL_CUDA_OK(cudaMemsetAsync(dbias, 0, sizeof(float) * C, as_stream(stream)));
-  softmax_xent_kernel<<<blocks < cap ? blocks : cap, 256, 0, as_stream(stream)>>>(
-      logits, ld_logits, labels, B, C, (__nv_bfloat16*)dlogits_bf16, ld_d, (__nv_bfloat16*)dlogits_t_bf16, ld_dt, dbias,
-      loss_sum, single);
-  P2PFL_LAUNCH_OK();
+  P2PFL_CUDA_OK(launch_pdl(softmax_xent_kernel, dim3(blocks < cap ? blocks : cap), dim3(256), 0, as_stream(stream), logits,
+                           ld_logits, labels, B, C, (__nv_bfloat16*)dlogits_bf16, ld_d, (__nv_bfloat16*)dlogits_t_bf16,
+                           ld_dt, dbias, loss_sum, single));
   return 0;
 }
 

@@ -18,6 +18,11 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static int g_pdl = 1;
+}  // namespace p2pfl
+namespace p2pfl {
+bool pdl_enabled() { return g_pdl != 0; }
+
 int sm_count(int device) {
   static int cache[64] = {0};
   if (device < 0 || device >= 64) return 148;
@@ -37,6 +42,12 @@ extern "C" {
 
 const char* p2pfl_last_error(void) { return g_err; }
 int p2pfl_version(void) { return 100; }
+
+int p2pfl_set_pdl(int enabled) {
+  int old = g_pdl;
+  g_pdl = enabled ? 1 : 0;
+  return old;
+}
 
 int p2pfl_rt_alloc(int device, uint64_t bytes, void** out_ptr) {
   P2PFL_REQUIRE(out_ptr != nullptr && bytes > 0, "bad arguments to p2pfl_rt_alloc");

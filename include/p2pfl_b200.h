@@ -21,6 +21,9 @@ extern "C" {
 
 const char* p2pfl_last_error(void);
 int p2pfl_version(void);
+/* Programmatic dependent launch for the train-step kernels (GEMM, loss, Adam): on by
+ * default; returns the previous setting.  Off = plain stream-ordered launches. */
+int p2pfl_set_pdl(int enabled);
 
 /* ------------------------------------------------------------------ runtime
  * Device arenas that can be mapped into peer GPUs / peer processes.

@@ -129,6 +129,11 @@ def _count(n: int = 1) -> None:
     _launches += n
 
 
+def set_pdl(enabled: bool) -> bool:
+    """Programmatic dependent launch for the train-step kernels; returns the previous setting."""
+    return bool(lib().p2pfl_set_pdl(C.c_int(int(enabled))))
+
+
 def launch_count() -> int:
     return _launches
 

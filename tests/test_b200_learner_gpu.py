@@ -137,3 +137,26 @@ def test_federation_on_gpu_in_memory():
     finally:
         for n in nodes:
             n.stop()
+
+
+def test_pdl_on_and_off_give_identical_training():
+    """Programmatic dependent launch only overlaps prologues: results must not change."""
+    from p2pfl_b200 import ops
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.models import MLP
+
+    flats = []
+    for pdl in (True, False):
+        prev = ops.set_pdl(pdl)
+        try:
+            dm = _dm(n_train=640, n_test=128)
+            torch.manual_seed(0)
+            learner = B200Learner(MLP(seed=3), dm, "p", epochs=1, device=DEV)
+            x, y = dm.tensors("train")
+            for i in range(4):
+                learner.debug_single_step(x[i * 32 : (i + 1) * 32], y[i * 32 : (i + 1) * 32])
+            flats.append(learner.flat.clone())
+            learner.close()
+        finally:
+            ops.set_pdl(prev)
+    assert torch.equal(flats[0], flats[1])
