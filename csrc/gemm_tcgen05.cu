@@ -29,7 +29,7 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
-constexpr int kStages = 4;
+constexpr int kMaxStages = 10;  // barriers are sized for this; the ring depth is chosen per problem
 constexpr int kThreadsGemm = 192;
 constexpr uint32_t kTileABytes = BM * BK * 2;
 
@@ -146,7 +146,7 @@ __device__ __forceinline__ uint32_t make_idesc(uint32_t bn) {
 
 constexpr int kMaxGroup = 4;
 constexpr int kMaxBN = 256;
-constexpr uint32_t kStageBytes = kTileABytes + kMaxBN * BK * 2;  // smem ring is sized for the widest tile
+constexpr uint32_t kRingBytes = 4 * (kTileABytes + kMaxBN * BK * 2);  // 4 stages of the widest tile = 192 KB
 
 // Up to four independent GEMMs per launch (blockIdx.z picks one); each has its own
 // tensor maps, epilogue and N-tile width bn in {32, 64, 128, 256}.
@@ -171,12 +171,17 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
   const CUtensorMap* tma_b = &g.mb[prob];
   const Epilogue& ep = g.ep[prob];
   const uint32_t stage_tx = kTileABytes + bn * BK * 2;
+  // narrow tiles get a deeper ring out of the same shared memory: the small-batch GEMMs of
+  // the train step are latency bound, and more loads in flight shorten their K loop
+  const uint32_t stage_bytes = stage_tx;
+  int n_stages = (int)(kRingBytes / stage_bytes);
+  n_stages = n_stages > kMaxStages ? kMaxStages : n_stages;
 
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B tiles must start on 1024-byte boundaries
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  __shared__ __align__(8) uint64_t full_bar[kStages];
-  __shared__ __align__(8) uint64_t empty_bar[kStages];
+  __shared__ __align__(8) uint64_t full_bar[kMaxStages];
+  __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
   __shared__ __align__(8) uint64_t tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
 
@@ -187,8 +192,7 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tma_a)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tma_b)) : "memory");
-#pragma unroll
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < n_stages; ++s) {
       mbar_init(smem_u32(&full_bar[s]), 1);
       mbar_init(smem_u32(&empty_bar[s]), 1);
     }
@@ -207,12 +211,12 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % kStages;
-        const uint32_t phase = (uint32_t)(kb / kStages) & 1u;
+        const int s = kb % n_stages;
+        const uint32_t phase = (uint32_t)(kb / n_stages) & 1u;
         mbar_wait(smem_u32(&empty_bar[s]), phase ^ 1u);
         const uint32_t bar = smem_u32(&full_bar[s]);
         mbar_expect_tx(bar, stage_tx);
-        const uint32_t a_dst = smem_u32(smem + (size_t)s * kStageBytes);
+        const uint32_t a_dst = smem_u32(smem + (size_t)s * stage_bytes);
         tma_load_2d(tma_a, bar, a_dst, kb * BK, m0);
         tma_load_2d(tma_b, bar, a_dst + kTileABytes, kb * BK, n0);
       }
@@ -221,12 +225,12 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
     // ===================== MMA issuer =====================
     const uint32_t idesc = make_idesc(bn);
     for (int kb = 0; kb < num_kb; ++kb) {
-      const int s = kb % kStages;
-      const uint32_t phase = (uint32_t)(kb / kStages) & 1u;
+      const int s = kb % n_stages;
+      const uint32_t phase = (uint32_t)(kb / n_stages) & 1u;
       mbar_wait(smem_u32(&full_bar[s]), phase);
       tc_fence_after();
       if (elect_one()) {
-        const uint32_t a_addr = smem_u32(smem + (size_t)s * kStageBytes);
+        const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
         const uint64_t da = make_smem_desc(a_addr);
         const uint64_t db = make_smem_desc(a_addr + kTileABytes);
 #pragma unroll
@@ -268,8 +272,29 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
         for (int j = 0; j < 32; ++j)
           if (nb + j < N && !(__bfloat162float(mk[j]) > 0.f)) x[j] = 0.f;
       }
+      const int valid = (N - nb) < 32 ? (N - nb) : 32;
+      if (ep.out_f32 || ep.out_bf16) {
+        // Direct ([M, ld]) outputs: a thread owns one row, so storing from registers would
+        // touch 32 different lines per instruction.  Stage the warp's 32x32 block in shared
+        // memory (the operand ring is idle now) and write whole 128-byte row segments.
+        float* st = reinterpret_cast<float*>(smem) + q * (32 * 33);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) st[lane * 33 + j] = x[j];
+        __syncwarp();
+        const int mrow0 = m0 + q * 32;
+#pragma unroll 4
+        for (int rr = 0; rr < 32; ++rr) {
+          const int mr = mrow0 + rr;
+          if (mr >= M) break;
+          const float v = st[rr * 33 + lane];
+          if (lane < valid) {
+            if (ep.out_f32) ep.out_f32[(size_t)mr * ep.ld_f32 + nb + lane] = v;
+            if (ep.out_bf16) ep.out_bf16[(size_t)mr * ep.ld_bf16 + nb + lane] = __float2bfloat16_rn(v);
+          }
+        }
+        __syncwarp();
+      }
       if (m < M) {
-        const int valid = (N - nb) < 32 ? (N - nb) : 32;
         if (ep.rowsum) {
           float s = 0.f;
 #pragma unroll
@@ -278,35 +303,6 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
           // one N tile of <= 32 columns owns the whole row: plain store, no zero-init needed
           if (single_n_tile && N <= 32) ep.rowsum[m] = s;
           else atomicAdd(ep.rowsum + m, s);
-        }
-        if (ep.out_f32) {
-          float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
-          if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j < valid) o[j] = x[j];
-          }
-        }
-        if (ep.out_bf16) {
-          __nv_bfloat16* o = ep.out_bf16 + (size_t)m * ep.ld_bf16 + nb;
-          if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint4 u;
-              u.x = pack_bf16x2(x[j], x[j + 1]);
-              u.y = pack_bf16x2(x[j + 2], x[j + 3]);
-              u.z = pack_bf16x2(x[j + 4], x[j + 5]);
-              u.w = pack_bf16x2(x[j + 6], x[j + 7]);
-              *reinterpret_cast<uint4*>(o + j) = u;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j < valid) o[j] = __float2bfloat16_rn(x[j]);
-          }
         }
         // transposed outputs: consecutive lanes hold consecutive m -> coalesced per column
         if (ep.out_f32_t) {
@@ -413,7 +409,7 @@ int launch_group(int device, cudaStream_t stream, const p2pfl_gemm_args* args, i
     gx = tx > gx ? tx : gx;
     gy = ty > gy ? ty : gy;
   }
-  constexpr size_t smem = (size_t)kStages * kStageBytes + 1024;
+  constexpr size_t smem = (size_t)kRingBytes + 1024;
   static bool attr_set[64] = {false};
   if (device >= 0 && device < 64 && !attr_set[device]) {
     P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
