@@ -273,27 +273,6 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
           if (nb + j < N && !(__bfloat162float(mk[j]) > 0.f)) x[j] = 0.f;
       }
       const int valid = (N - nb) < 32 ? (N - nb) : 32;
-      if (ep.out_f32 || ep.out_bf16) {
-        // Direct ([M, ld]) outputs: a thread owns one row, so storing from registers would
-        // touch 32 different lines per instruction.  Stage the warp's 32x32 block in shared
-        // memory (the operand ring is idle now) and write whole 128-byte row segments.
-        float* st = reinterpret_cast<float*>(smem) + q * (32 * 33);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) st[lane * 33 + j] = x[j];
-        __syncwarp();
-        const int mrow0 = m0 + q * 32;
-#pragma unroll 4
-        for (int rr = 0; rr < 32; ++rr) {
-          const int mr = mrow0 + rr;
-          if (mr >= M) break;
-          const float v = st[rr * 33 + lane];
-          if (lane < valid) {
-            if (ep.out_f32) ep.out_f32[(size_t)mr * ep.ld_f32 + nb + lane] = v;
-            if (ep.out_bf16) ep.out_bf16[(size_t)mr * ep.ld_bf16 + nb + lane] = __float2bfloat16_rn(v);
-          }
-        }
-        __syncwarp();
-      }
       if (m < M) {
         if (ep.rowsum) {
           float s = 0.f;
@@ -303,6 +282,36 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
           // one N tile of <= 32 columns owns the whole row: plain store, no zero-init needed
           if (single_n_tile && N <= 32) ep.rowsum[m] = s;
           else atomicAdd(ep.rowsum + m, s);
+        }
+        // direct ([M, ld]) outputs: each thread writes its row's 32 contiguous values
+        if (ep.out_f32) {
+          float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
+          if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < valid) o[j] = x[j];
+          }
+        }
+        if (ep.out_bf16) {
+          __nv_bfloat16* o = ep.out_bf16 + (size_t)m * ep.ld_bf16 + nb;
+          if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 u;
+              u.x = pack_bf16x2(x[j], x[j + 1]);
+              u.y = pack_bf16x2(x[j + 2], x[j + 3]);
+              u.z = pack_bf16x2(x[j + 4], x[j + 5]);
+              u.w = pack_bf16x2(x[j + 6], x[j + 7]);
+              *reinterpret_cast<uint4*>(o + j) = u;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < valid) o[j] = __float2bfloat16_rn(x[j]);
+          }
         }
         // transposed outputs: consecutive lanes hold consecutive m -> coalesced per column
         if (ep.out_f32_t) {
@@ -365,12 +374,20 @@ int make_map(CUtensorMap* map, const void* base, int rows, int cols, int ld, int
   return 0;
 }
 
-int pick_bn(int N) { return N <= 32 ? 32 : N <= 64 ? 64 : N <= 128 ? 128 : 256; }
+// N-tile width: the widest that fits, but narrow it while the grid would leave most SMs
+// idle - small-K problems (wgrad of a small batch) are bound by the epilogue stores, which
+// spread over more SMs with narrower tiles.
+int pick_bn(int M, int N) {
+  int bn = N <= 32 ? 32 : N <= 64 ? 64 : N <= 128 ? 128 : 256;
+  const int tiles_m = (M + BM - 1) / BM;
+  while (bn > 32 && tiles_m * ((N + bn - 1) / bn) < 74) bn >>= 1;
+  return bn;
+}
 
 int fill_problem(GroupedArgs& g, int idx, const p2pfl_gemm_args& a) {
   P2PFL_REQUIRE(a.A && a.B && a.M > 0 && a.N > 0 && a.K > 0, "bad GEMM shape or operands");
   P2PFL_REQUIRE(a.out_f32 || a.out_bf16 || a.out_f32_t || a.out_bf16_t || a.rowsum, "GEMM needs an output");
-  const int bn = pick_bn(a.N);
+  const int bn = pick_bn(a.M, a.N);
   if (int rc = make_map(&g.ma[idx], a.A, a.M, a.K, a.lda, BM)) return rc;
   if (int rc = make_map(&g.mb[idx], a.B, a.N, a.K, a.ldb, bn)) return rc;
   Epilogue& ep = g.ep[idx];

@@ -208,6 +208,45 @@ int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* args);
  * both depend only on that layer's dZ): fewer launches on the latency-bound step. */
 int p2pfl_gemm_tn_grouped(int device, void* stream, const p2pfl_gemm_args* args, int count);
 
+/* ----------------------------------------------------------- convolution path
+ * K6/K7 (cnn.py:78-81 Conv2d + ReLU + MaxPool2d through cuDNN/ATen) and the
+ * ResNet-style blocks of BASELINE.json config 3.  Activations are NHWC bf16.
+ * Convolutions are implicit GEMMs on p2pfl_gemm_tn: `col` is the im2col matrix
+ * [B*Ho*Wo, ld_col] with K ordered (c, i, j) like a flattened PyTorch conv weight;
+ * `col_t` (nullable) is its transpose [C*kh*kw, ld_t] for the weight-gradient GEMM. */
+int p2pfl_im2col(int device, void* stream, const void* x_nhwc, int B, int H, int W, int C, int kh,
+                 int kw, int stride, int pad, void* col, int ld_col, void* col_t, int64_t ld_t);
+/* gradient of im2col: dx[b,h,w,c] gathers its kh*kw contributions (no atomics) */
+int p2pfl_col2im(int device, void* stream, const void* dcol, int ld_col, int B, int H, int W, int C,
+                 int kh, int kw, int stride, int pad, void* dx_nhwc);
+/* 2x2/2 max pool; `arg` (uint8) keeps the winner; `flat` / `flat_t` (nullable) are the
+ * output in NCHW-flatten order [B, C*Ho*Wo] and transposed, for a following Linear. */
+int p2pfl_maxpool2_fwd(int device, void* stream, const void* x_nhwc, int B, int H, int W, int C,
+                       void* y_nhwc /* nullable */, void* arg, void* flat, void* flat_t, int ld_flat_t);
+/* backward of ReLU -> max pool in one pass: routes dy (NHWC or NCHW-flat, whichever is
+ * given) to the winners, applies the ReLU mask of `act_nhwc`, writes [pixels, C] and
+ * [C, ld_t], and accumulates the per-channel sum (conv bias gradient) into dbias. */
+int p2pfl_maxpool2_relu_bwd(int device, void* stream, const void* dy_nhwc, const void* dy_flat,
+                            const void* arg, const void* act_nhwc, int B, int H, int W, int C,
+                            void* dx, void* dx_t /* nullable */, int64_t ld_t, float* dbias /* nullable */);
+/* fp32 [rows, cols] -> bf16 [rows, ld] with zero padding (16-byte row pitch for TMA) */
+int p2pfl_pad_cast(int device, void* stream, const float* src, int rows, int cols, void* dst_bf16, int ld);
+int p2pfl_nchw_to_nhwc(int device, void* stream, const float* x, int B, int C, int H, int W, void* y_bf16);
+/* training-mode BatchNorm2d over NHWC (+ optional residual add and ReLU), saving
+ * mean / rstd for the backward pass and updating the running statistics */
+int p2pfl_bn_fwd(int device, void* stream, const void* x_nhwc, int64_t pixels, int C,
+                 const float* gamma, const float* beta, float* running_mean, float* running_var,
+                 float momentum, float eps, int relu, const void* residual /* nullable */, void* y,
+                 float* save_mean, float* save_rstd);
+int p2pfl_bn_bwd(int device, void* stream, const void* x_nhwc, const void* y, const void* dy,
+                 int64_t pixels, int C, const float* gamma, const float* save_mean,
+                 const float* save_rstd, int relu, void* dx, void* d_residual /* nullable */,
+                 float* dgamma, float* dbeta);
+/* global average pool over HW: [B, HW, C] -> [B, C] (+ transpose), and its backward */
+int p2pfl_avgpool_fwd(int device, void* stream, const void* x_nhwc, int B, int HW, int C, void* y,
+                      void* y_t /* nullable */, int ld_t);
+int p2pfl_avgpool_bwd(int device, void* stream, const void* dy, int B, int HW, int C, void* dx_nhwc);
+
 /* ------------------------------------------------------------ data movement
  * K11/N8: device-resident dataset; gather a shuffled epoch in bf16, both as
  * [n, feat] and per-batch transposed [n/B][feat][B] for the wgrad GEMM. */

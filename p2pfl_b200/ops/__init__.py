@@ -330,6 +330,90 @@ def gather_rows(src, perm, n_rows: int, feat: int, batch: int, dst, dst_t=None, 
     _count()
 
 
+# ------------------------------------------------------------ convolution path
+def conv_out(size: int, k: int, stride: int, pad: int) -> int:
+    return (size + 2 * pad - k) // stride + 1
+
+
+def im2col(x, B: int, H: int, W: int, Cc: int, kh: int, kw: int, stride: int, pad: int, col, ld_col: int, col_t=None, ld_t: int = 0) -> None:
+    _check(
+        lib().p2pfl_im2col(
+            _dev(x), _stream(), _p(x), C.c_int(B), C.c_int(H), C.c_int(W), C.c_int(Cc), C.c_int(kh), C.c_int(kw),
+            C.c_int(stride), C.c_int(pad), _p(col), C.c_int(ld_col), _p(col_t), C.c_int64(ld_t),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def col2im(dcol, ld_col: int, B: int, H: int, W: int, Cc: int, kh: int, kw: int, stride: int, pad: int, dx) -> None:
+    _check(
+        lib().p2pfl_col2im(
+            _dev(dcol), _stream(), _p(dcol), C.c_int(ld_col), C.c_int(B), C.c_int(H), C.c_int(W), C.c_int(Cc),
+            C.c_int(kh), C.c_int(kw), C.c_int(stride), C.c_int(pad), _p(dx),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def maxpool2_fwd(x, B: int, H: int, W: int, Cc: int, y, arg, flat=None, flat_t=None, ld_flat_t: int = 0) -> None:
+    _check(
+        lib().p2pfl_maxpool2_fwd(
+            _dev(x), _stream(), _p(x), C.c_int(B), C.c_int(H), C.c_int(W), C.c_int(Cc), _p(y), _p(arg), _p(flat), _p(flat_t), C.c_int(ld_flat_t)
+        )
+    )
+    _count()
+
+
+def maxpool2_relu_bwd(dy_nhwc, dy_flat, arg, act, B: int, H: int, W: int, Cc: int, dx, dx_t=None, ld_t: int = 0, dbias=None) -> None:
+    _check(
+        lib().p2pfl_maxpool2_relu_bwd(
+            _dev(act), _stream(), _p(dy_nhwc), _p(dy_flat), _p(arg), _p(act), C.c_int(B), C.c_int(H), C.c_int(W), C.c_int(Cc),
+            _p(dx), _p(dx_t), C.c_int64(ld_t), _p(dbias),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def pad_cast(src, rows: int, cols: int, dst, ld: int) -> None:
+    _check(lib().p2pfl_pad_cast(_dev(src), _stream(), _p(src), C.c_int(rows), C.c_int(cols), _p(dst), C.c_int(ld)))
+    _count()
+
+
+def nchw_to_nhwc(x, B: int, Cc: int, H: int, W: int, y) -> None:
+    _check(lib().p2pfl_nchw_to_nhwc(_dev(x), _stream(), _p(x), C.c_int(B), C.c_int(Cc), C.c_int(H), C.c_int(W), _p(y)))
+    _count()
+
+
+def bn_fwd(x, pixels: int, Cc: int, gamma, beta, running_mean, running_var, momentum: float, eps: float, relu: bool, residual, y, save_mean, save_rstd) -> None:
+    _check(
+        lib().p2pfl_bn_fwd(
+            _dev(x), _stream(), _p(x), C.c_int64(pixels), C.c_int(Cc), _p(gamma), _p(beta), _p(running_mean), _p(running_var),
+            C.c_float(momentum), C.c_float(eps), C.c_int(int(relu)), _p(residual), _p(y), _p(save_mean), _p(save_rstd),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def bn_bwd(x, y, dy, pixels: int, Cc: int, gamma, save_mean, save_rstd, relu: bool, dx, d_residual, dgamma, dbeta) -> None:
+    _check(
+        lib().p2pfl_bn_bwd(
+            _dev(x), _stream(), _p(x), _p(y), _p(dy), C.c_int64(pixels), C.c_int(Cc), _p(gamma), _p(save_mean), _p(save_rstd),
+            C.c_int(int(relu)), _p(dx), _p(d_residual), _p(dgamma), _p(dbeta),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def avgpool_fwd(x, B: int, HW: int, Cc: int, y, y_t=None, ld_t: int = 0) -> None:
+    _check(lib().p2pfl_avgpool_fwd(_dev(x), _stream(), _p(x), C.c_int(B), C.c_int(HW), C.c_int(Cc), _p(y), _p(y_t), C.c_int(ld_t)))
+    _count()
+
+
+def avgpool_bwd(dy, B: int, HW: int, Cc: int, dx) -> None:
+    _check(lib().p2pfl_avgpool_bwd(_dev(dy), _stream(), _p(dy), C.c_int(B), C.c_int(HW), C.c_int(Cc), _p(dx)))
+    _count()
+
+
 # ---------------------------------------------------------------------- gossip
 def make_push_table(inbox_ptrs: Sequence[int], flag_ptrs: Sequence[int], wire_bf16: bool) -> PushTable:
     if len(inbox_ptrs) > MAX_PEERS:
