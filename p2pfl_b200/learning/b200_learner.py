@@ -111,6 +111,18 @@ class B200Learner(TorchLearner):
         ``nn.Linear`` layers with ReLU in between (the reference MLP)."""
         self.fused = False
         self._layers = []
+        self.cnn = None
+        self._tdescs = []
+        if getattr(self.model, "fused_spec", None) == "cnn":
+            from p2pfl_b200.learning.b200_cnn import CnnPlan
+
+            plan = CnnPlan(self)
+            if plan.ok:
+                self.cnn = plan
+                self._feat, self._ncls = plan.feat, plan.ncls
+                self._tdescs, self.wT16 = plan.tdescs, plan.wT16
+                self.fused = True
+            return
         if getattr(self.model, "fused_spec", None) != "mlp":
             return
         linears = [(n, m) for n, m in self.model.named_children() if isinstance(m, nn.Linear)]
@@ -137,6 +149,7 @@ class B200Learner(TorchLearner):
             self._tdescs.append((L.w_off, off, L.out_f, L.in_f, ld))
             off += L.in_f * ld
         self.wT16 = torch.zeros(max(off, 8), dtype=torch.bfloat16, device=self.device)
+        self._feat, self._ncls = self._layers[0].in_f, self._layers[-1].out_f
         self.fused = True
 
     def _params_written(self) -> None:
@@ -145,14 +158,19 @@ class B200Learner(TorchLearner):
             return
         with torch.cuda.stream(self._s()):
             ops.cast_f32_bf16(self.flat, self.w16)
-            if self.fused and self._tdescs:
+            if self.fused and self.cnn is not None:
+                self.cnn.refresh()
+            elif self.fused and self._tdescs:
                 ops.transpose_cast(self.flat, self.wT16, self._tdescs)
 
     def _params_written_by_plane(self) -> None:
         """The data plane wrote fp32 params AND the bf16 copy; only the transposes are stale."""
-        if self.fused and self._tdescs:
+        if self.fused and (self._tdescs or self.cnn is not None):
             with torch.cuda.stream(self._s()):
-                ops.transpose_cast(self.flat, self.wT16, self._tdescs)
+                if self.cnn is not None:
+                    self.cnn.refresh()
+                else:
+                    ops.transpose_cast(self.flat, self.wT16, self._tdescs)
 
     def _s(self) -> torch.cuda.Stream:
         return getattr(self, "stream", None) or torch.cuda.current_stream(self.device)
@@ -263,6 +281,8 @@ class B200Learner(TorchLearner):
                             out_bf16_t=act["H"][li], ld_bf16_t=_pad8(L.out_f))  # fmt: skip
 
     def _alloc_act(self, B: int, train: bool) -> Dict[str, Any]:
+        if self.cnn is not None:
+            return self.cnn.alloc(B, train)
         dev = self.device
         Ls = self._layers
         ldB = _pad8(B)
@@ -277,6 +297,9 @@ class B200Learner(TorchLearner):
         return act
 
     def _train_step(self, x16, xT16, y, bsz: int, act, loss_slot, step_offset: int, lr: float) -> None:
+        if self.cnn is not None:
+            self.cnn.train_step(x16, y, bsz, act, loss_slot, step_offset, lr)
+            return
         Ls = self._layers
         nL = len(Ls)
         feat = Ls[0].in_f
@@ -314,7 +337,7 @@ class B200Learner(TorchLearner):
         """One eager (un-graphed) fused step on the given batch; returns the mean loss.
         Test hook: leaves the gradients in ``self.grads``."""
         B = x.shape[0]
-        feat = self._layers[0].in_f
+        feat = self._feat
         with torch.cuda.stream(self._s()):
             xf = x.reshape(B, -1).to(self.device, torch.float32).contiguous()
             yi = y.to(self.device).to(torch.int32)
@@ -333,14 +356,16 @@ class B200Learner(TorchLearner):
     def _build_epoch(self, n: int, B: int) -> Dict[str, Any]:
         """Capture one whole epoch (gather + every step) as a single CUDA graph."""
         dev = self.device
-        feat = self._layers[0].in_f
+        feat = self._feat
         nb = (n + B - 1) // B
         x, y = self._train_dev
         ep: Dict[str, Any] = {"n": n, "B": B, "nb": nb}
         ep["perm"] = torch.arange(n, dtype=torch.int32, device=dev)
         ep["perm_host"] = torch.empty(n, dtype=torch.int32).pin_memory()
         ep["xs"] = torch.zeros(nb * B, feat, dtype=torch.bfloat16, device=dev)
-        ep["xsT"] = torch.zeros(nb, feat, _pad8(B), dtype=torch.bfloat16, device=dev)
+        # the MLP's first wgrad GEMM wants each batch transposed as well; the CNN does not
+        need_t = self.cnn is None
+        ep["xsT"] = torch.zeros(nb if need_t else 1, feat, _pad8(B), dtype=torch.bfloat16, device=dev)
         ep["ys"] = torch.zeros(nb * B, dtype=torch.int32, device=dev)
         ep["loss"] = torch.zeros(nb, dtype=torch.float32, device=dev)
         ep["act"] = self._alloc_act(B, train=True)
@@ -348,10 +373,10 @@ class B200Learner(TorchLearner):
 
         def body() -> None:
             ep["loss"].zero_()
-            ops.gather_rows(x, ep["perm"], n, feat, _pad8(B), ep["xs"], ep["xsT"], y, ep["ys"])
+            ops.gather_rows(x, ep["perm"], n, feat, _pad8(B), ep["xs"], ep["xsT"] if need_t else None, y, ep["ys"])
             for i in range(nb):
                 bsz = min(B, n - i * B)
-                self._train_step(ep["xs"][i * B :], ep["xsT"][i], ep["ys"][i * B :], bsz, ep["act"],
+                self._train_step(ep["xs"][i * B :], ep["xsT"][i if need_t else 0], ep["ys"][i * B :], bsz, ep["act"],
                                  ep["loss"][i:], i + 1, lr)  # fmt: skip
             ops.add_i32(self.adam_step, nb)
 
@@ -420,12 +445,16 @@ class B200Learner(TorchLearner):
     # -------------------------------------------------------------- evaluate
     def _build_eval(self, split: str, n: int) -> Dict[str, Any]:
         dev = self.device
-        feat = self._layers[0].in_f
-        C = self._layers[-1].out_f
+        feat, C = self._feat, self._ncls
         x, y = self._eval_dev[split]
         ev: Dict[str, Any] = {"n": n}
         ev["x16"] = torch.zeros(n, feat, dtype=torch.bfloat16, device=dev)
-        ev["act"] = self._alloc_act(n, train=False)
+        if self.cnn is not None:
+            ev["act"] = self._alloc_act(min(n, self.cnn.EVAL_CHUNK), train=False)
+            ev["logits"] = torch.zeros(n, _pad8(C), dtype=torch.float32, device=dev)
+        else:
+            ev["act"] = self._alloc_act(n, train=False)
+            ev["logits"] = ev["act"]["logits"]
         ev["loss"] = torch.zeros(1, dtype=torch.float32, device=dev)
         ev["correct"] = torch.zeros(1, dtype=torch.int32, device=dev)
         ev["out"] = torch.zeros(2, dtype=torch.float32, device=dev)
@@ -434,8 +463,11 @@ class B200Learner(TorchLearner):
             ev["loss"].zero_()
             ev["correct"].zero_()
             ops.gather_rows(x, None, n, feat, 8, ev["x16"])
-            self._forward(ev["x16"], feat, n, ev["act"], train=False)
-            ops.eval_reduce(ev["act"]["logits"], ev["act"]["ld_logits"], y, n, C, ev["loss"], ev["correct"])
+            if self.cnn is not None:
+                self.cnn.forward_eval(ev["x16"], n, ev["act"], ev["logits"])
+            else:
+                self._forward(ev["x16"], feat, n, ev["act"], train=False)
+            ops.eval_reduce(ev["logits"], ev["act"]["ld_logits"], y, n, C, ev["loss"], ev["correct"])
             ev["out"][0].copy_(ev["loss"][0])
             ev["out"][1].copy_(ev["correct"][0])
 

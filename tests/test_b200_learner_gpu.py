@@ -97,11 +97,58 @@ def test_wire_roundtrip_and_set_parameters():
     b.close()
 
 
-def test_non_fused_model_falls_back_to_autograd():
+def test_cnn_fused_step_gradients_match_autograd():
+    """The implicit-GEMM CNN step (im2col + tcgen05 GEMMs + fused pool/ReLU backward) vs autograd."""
     from p2pfl_b200.learning.b200_learner import B200Learner
     from p2pfl_b200.models import CNN
 
+    torch.manual_seed(0)
+    model = CNN(seed=0)
+    ref = copy.deepcopy(model).to(DEV)
     dm = _dm(n_train=320, n_test=64)
+    learner = B200Learner(model, dm, "c", epochs=1, device=DEV)
+    assert learner.fused and learner.cnn is not None
+    x, y = dm.tensors("train")
+    x, y = x[:32], y[:32]
+    loss = learner.debug_single_step(x, y)
+    with torch.no_grad():
+        for p in ref.parameters():
+            if p.dim() > 1:
+                p.copy_(p.to(torch.bfloat16).float())
+    out = ref(x.to(DEV).to(torch.bfloat16).float())
+    ref_loss = F.cross_entropy(out, y.to(DEV))
+    ref_loss.backward()
+    assert abs(loss - float(ref_loss.detach())) < 3e-2 * max(1.0, float(ref_loss.detach()))
+    views = learner.layout.views(learner.grads)
+    for name, p in ref.named_parameters():
+        rel = (views[name] - p.grad).norm() / (p.grad.norm() + 1e-12)
+        assert rel < 6e-2, f"{name}: relative gradient error {float(rel):.4f}"
+    learner.close()
+
+
+def test_cnn_fused_fit_and_evaluate():
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.learning.torch_learner import TorchLearner
+    from p2pfl_b200.models import CNN
+
+    dm = _dm(n_train=700, n_test=300, noise=6.0)  # 630 train (partial last batch), eval in chunks of 250 + 50
+    learner = B200Learner(CNN(seed=1), dm, "c", epochs=1, device=DEV)
+    oracle = TorchLearner(CNN(seed=1), dm, "o", epochs=1, device=DEV)
+    r0, o0 = learner.evaluate(), oracle.evaluate()
+    assert abs(r0["test_loss"] - o0["test_loss"]) < 3e-2
+    learner.fit()
+    oracle.fit()
+    r1, o1 = learner.evaluate(), oracle.evaluate()
+    assert r1["test_loss"] < r0["test_loss"]
+    assert abs(r1["test_loss"] - o1["test_loss"]) < 0.25 * max(o1["test_loss"], 0.2)
+    learner.close()
+
+
+def test_non_fused_model_falls_back_to_autograd():
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.models import ResNet18 as CNN
+
+    dm = __import__("p2pfl_b200.learning.data", fromlist=["Cifar10FederatedDM"]).Cifar10FederatedDM(0, 1, n_train=160, n_test=64)
     learner = B200Learner(CNN(seed=0), dm, "c", epochs=1, device=DEV)
     assert not learner.fused
     r0 = learner.evaluate()
