@@ -15,12 +15,23 @@ from p2pfl_b200.management.logger import logger
 from p2pfl_b200.node_state import NodeState
 
 
+# value of a beat's `round` field that says "the originator speaks this framework's extensions";
+# reference nodes ignore the field (their handler takes the time argument only)
+EXTENDED_MARK = -2
+
+# the commands a reference node understands; anything else is only sent to extended peers
+REFERENCE_COMMANDS = frozenset(
+    ["beat", "start_learning", "stop_learning", "model_initialized", "vote_train_set", "models_aggregated",
+     "models_ready", "metrics", "init_model", "add_model"]
+)  # fmt: skip
+
+
 class HeartbeatCommand(Command):
     """``beat [time]`` (reference: commands/heartbeat_command.py:39-52)."""
 
-    def __init__(self, heartbeater: Any, on_neighbors: Any = None) -> None:
+    def __init__(self, heartbeater: Any, on_extended: Any = None) -> None:
         self._hb = heartbeater
-        self._on_neighbors = on_neighbors
+        self._on_extended = on_extended
 
     @staticmethod
     def get_name() -> str:
@@ -28,8 +39,23 @@ class HeartbeatCommand(Command):
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
         self._hb.beat(source, float(args[0]))
-        if len(args) > 1 and self._on_neighbors is not None:
-            self._on_neighbors(source, [n for n in args[1].split(",") if n])
+        if round == EXTENDED_MARK and self._on_extended is not None:
+            self._on_extended(source)
+
+
+class NeighborsHintCommand(Command):
+    """``neighbors_hint [n1, n2, ...]``: the sender's direct neighbours (never relayed, only sent
+    between nodes of this framework).  Lets a relay skip nodes the originator reaches itself."""
+
+    def __init__(self, on_neighbors: Any) -> None:
+        self._on_neighbors = on_neighbors
+
+    @staticmethod
+    def get_name() -> str:
+        return "neighbors_hint"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        self._on_neighbors(source, list(args))
 
 
 class StartLearningCommand(Command):
@@ -43,8 +69,8 @@ class StartLearningCommand(Command):
         return "start_learning"
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
-        # optional third argument: the experiment's data-plane sequence base (ignored by reference nodes)
-        self._start(int(args[0]), int(args[1]), int(args[2]) if len(args) > 2 else 0)
+        # `round` carries the experiment's data-plane sequence base (-1 / absent from reference nodes)
+        self._start(int(args[0]), int(args[1]), round if round is not None and round > 0 else 0)
 
 
 class StopLearningCommand(Command):

@@ -162,9 +162,11 @@ class BaseProtocol(CommunicationProtocol):
         self._gossiper = Gossiper(self.addr, self.send)
         self._heartbeater = Heartbeater(self.addr, self._neighbors, self._broadcast_beat)
         self._server = _ServerHandle(transport)
-        from p2pfl_b200.commands.control import HeartbeatCommand
+        from p2pfl_b200.commands.control import HeartbeatCommand, NeighborsHintCommand
 
-        self.add_command(HeartbeatCommand(self._heartbeater, self.note_direct_neighbors_of))
+        self._extended: set = set()  # peers known to understand this framework's extra commands
+        self.add_command(HeartbeatCommand(self._heartbeater, self._extended.add))
+        self.add_command(NeighborsHintCommand(self.note_direct_neighbors_of))
         self._running = False
         self._terminated = threading.Event()
         self._direct_of: Dict[str, Any] = {}  # node -> set of its direct neighbours (from its beats)
@@ -264,8 +266,12 @@ class BaseProtocol(CommunicationProtocol):
     def broadcast(self, msg: Message, node_list: Optional[List[str]] = None) -> None:
         """Send to every direct neighbour (or the direct ones among ``node_list``); the
         round trips overlap when the transport supports it."""
+        from p2pfl_b200.commands.control import REFERENCE_COMMANDS
+
         direct = self._neighbors.get_all(only_direct=True)
         names = [n for n in (node_list if node_list is not None else direct) if n in direct]
+        if msg.cmd not in REFERENCE_COMMANDS:
+            names = [n for n in names if n in self._extended]  # a reference node evicts on unknown commands
         targets = [(n, direct[n].link) for n in names]
         if not targets:
             return
@@ -276,21 +282,37 @@ class BaseProtocol(CommunicationProtocol):
             logger.info(self.addr, f"send of '{msg.cmd}' to {nei} failed ({res}); removing neighbour")
             self._neighbors.remove(nei, disconnect_msg=True)
 
+    def _beat_msg(self, now: float) -> Message:
+        from p2pfl_b200.commands.control import EXTENDED_MARK
+
+        return self.build_msg(HEARTBEAT_CMD, [str(now)], round=EXTENDED_MARK)
+
     def _broadcast_beat(self, now: float) -> None:
-        # second argument (ignored by reference nodes): my direct neighbours, so that
-        # receivers need not relay my broadcasts to nodes I reach myself
-        args = [str(now)]
+        self.broadcast(self._beat_msg(now))
+        # tell extended direct neighbours whom I reach directly, so that they need not relay
+        # my broadcasts there (sent point-to-point, ttl 1: a reference node never sees it)
         direct = list(self._neighbors.get_all(only_direct=True))
         if Settings.RELAY_PRUNING and len(direct) <= Settings.RELAY_PRUNING_MAX_LIST:
-            args.append(",".join(sorted(direct)))
-        self.broadcast(self.build_msg(HEARTBEAT_CMD, args))
+            hint = self.build_msg("neighbors_hint", sorted(direct))
+            hint.ttl = 1
+            self.broadcast(hint)
+
+    def _greet(self, addr: str) -> None:
+        """Right after a link comes up: an immediate beat, so both ends learn at once whether
+        the other speaks the extended commands (queued: never re-enter the peer synchronously)."""
+        import time as _time
+
+        self._gossiper.add_message(self._beat_msg(_time.time()), [addr])
 
     def note_direct_neighbors_of(self, source: str, names: List[str]) -> None:
         self._direct_of[source] = set(names)
 
     # ------------------------------------------------------------ neighbours
     def connect(self, addr: str, non_direct: bool = False) -> bool:
-        return self._neighbors.add(addr, non_direct=non_direct)
+        ok = self._neighbors.add(addr, non_direct=non_direct)
+        if ok and not non_direct and self._running:
+            self._greet(addr)
+        return ok
 
     def disconnect(self, nei: str, disconnect_msg: bool = True) -> None:
         self._neighbors.remove(nei, disconnect_msg=disconnect_msg)
@@ -308,6 +330,7 @@ class BaseProtocol(CommunicationProtocol):
         if not self._running:
             return "node not running"
         if self._neighbors.add(addr, non_direct=False, handshake=False):
+            self._greet(addr)
             return None
         # already a direct neighbour is fine (both sides connected at once)
         try:
@@ -330,8 +353,12 @@ class BaseProtocol(CommunicationProtocol):
         if msg.ttl > 1:
             # flood to my direct neighbours, except the originator and - topology-aware
             # pruning - those the originator advertises it reaches directly
+            from p2pfl_b200.commands.control import REFERENCE_COMMANDS
+
             covered = self._direct_of.get(msg.source, ()) if Settings.RELAY_PRUNING else ()
             targets = [n for n in self._neighbors.get_all(only_direct=True) if n != msg.source and n not in covered]
+            if msg.cmd not in REFERENCE_COMMANDS:
+                targets = [n for n in targets if n in self._extended]
             if targets:
                 self._gossiper.add_message(msg.relay_copy(), targets)
         cmd = self._commands.get(msg.cmd)

@@ -173,7 +173,9 @@ class Node:
         # data-plane sequence numbers must grow from one experiment to the next (arenas and
         # their arrival flags are reused): derive the base from the wall clock
         seq_base = (int(time.time()) % (1 << 18)) * 4096
-        proto.broadcast(proto.build_msg("start_learning", [str(rounds), str(epochs), str(seq_base)]))
+        # the reference's handler takes exactly (rounds, epochs); the base rides in the message's
+        # `round` field, which the reference passes along and ignores for this command
+        proto.broadcast(proto.build_msg("start_learning", [str(rounds), str(epochs)], round=seq_base))
         self.state.model_initialized.set()
         proto.broadcast(proto.build_msg("model_initialized"))
         self.__start_learning_thread(rounds, epochs, seq_base)

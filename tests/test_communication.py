@@ -94,6 +94,9 @@ def test_bad_msg_evicts(protocol):
         n1.connect(n2.addr)
         wait_convergence([n1, n2], 1, only_direct=True)
         proto = n1._communication_protocol
+        deadline = time.time() + 5  # commands outside the reference's set only go to peers known to speak them
+        while n2.addr not in proto._extended and time.time() < deadline:
+            time.sleep(0.01)
         proto.broadcast(proto.build_msg("BAD_MSG"))
         wait_convergence([n1, n2], 0, only_direct=True, wait=4)
     finally:
@@ -143,6 +146,7 @@ def test_ttl_bounds_reach_and_relay_copies_message():
         for i in range(5):
             nodes[i + 1].connect(nodes[i].addr)
         wait_convergence(nodes[1:5], 2, only_direct=True)
+        time.sleep(0.5)  # greeting beats: every node learns its neighbours speak the extended commands
         proto = nodes[0]._communication_protocol
         msg = proto.build_msg("probe")
         proto.broadcast(msg)
