@@ -146,6 +146,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     Settings.TRAIN_SET_SIZE = world
     Settings.DEVICE_INBOX_SLOTS = max(world, 2)
     Settings.GOSSIP_MODELS_PERIOD = 0.05
+    Settings.GOSSIP_PERIOD = 0.0
     Settings.WAIT_HEARTBEATS_CONVERGENCE = 0.2
     Settings.HEARTBEAT_PERIOD = 1.0
     Settings.HEARTBEAT_TIMEOUT = 30.0

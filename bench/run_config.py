@@ -90,6 +90,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     Settings.DEVICE_INBOX_SLOTS = max(2, min(16, s["train_set"]))
     Settings.TTL = s.get("ttl", Settings.TTL)
     Settings.GOSSIP_MODELS_PERIOD = 0.05
+    Settings.GOSSIP_PERIOD = 0.0
     Settings.GOSSIP_MODELS_PER_ROUND = 4
     Settings.WAIT_HEARTBEATS_CONVERGENCE = 0.3
     Settings.HEARTBEAT_PERIOD = 2.0

@@ -118,7 +118,9 @@ class VoteTrainSetCommand(Command):
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
         st = self._state
-        if st.round is None or round not in (st.round, st.round + 1):
+        # ballots are filed under their round: early ones (a faster node pre-voting for a later
+        # round) are kept until this node gets there; stale ones are dropped
+        if st.round is None or not (st.round <= round <= st.round + 3):
             logger.debug(st.addr, f"vote from {source} for round {round} ignored (mine: {st.round})")
             return
         if len(args) % 2:

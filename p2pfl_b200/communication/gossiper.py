@@ -62,6 +62,12 @@ class Gossiper(threading.Thread):
             return True
 
     # ---------------------------------------------------------- relay queue
+    def add_broadcast(self, msg: Message, broadcast_fn: Callable[[Message], None]) -> None:
+        """Queue a whole broadcast (performed with overlapped round trips by ``broadcast_fn``)."""
+        with self._cv:
+            self._pending.append((msg, broadcast_fn))  # type: ignore[arg-type]
+            self._cv.notify()
+
     def add_message(self, msg: Message, pending_neis: List[str]) -> None:
         if not pending_neis:
             return
@@ -80,6 +86,11 @@ class Gossiper(threading.Thread):
                 batch: List[Tuple[Message, str]] = []
                 while self._pending and budget > 0:
                     msg, neis = self._pending[0]
+                    if callable(neis):  # a queued broadcast
+                        self._pending.popleft()
+                        batch.append((msg, neis))  # type: ignore[arg-type]
+                        budget -= 1
+                        continue
                     take = neis[:budget]
                     del neis[: len(take)]
                     budget -= len(take)
@@ -89,6 +100,9 @@ class Gossiper(threading.Thread):
             t0 = time.time()
             for msg, nei in batch:
                 try:
+                    if callable(nei):
+                        nei(msg)
+                        continue
                     self._send(nei, msg, False)
                 except Exception as e:  # a dead neighbour must not kill the relay thread
                     logger.debug(self._addr, f"relay to {nei} failed: {e}")

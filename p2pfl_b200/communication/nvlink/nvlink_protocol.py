@@ -309,6 +309,7 @@ class FusedExchange:
                  peers: Dict[str, PeerArena], samples: Dict[str, int]) -> None:  # fmt: skip
         self.proto, self.state, self.learner = proto, state, learner
         self.train_set, self.peers, self.samples = train_set, peers, samples
+        self.complete = False
 
     def run(self, seq: int) -> Tuple[List[str], int]:
         """Launch, wait, and return (contributors included, total weight)."""
@@ -355,7 +356,8 @@ class FusedExchange:
         learner._params_written_by_plane()
         self.proto.stats["fused"] += 1
         self.proto.stats["fused_bytes"] += arena.n * (2 if wire_bf16 else 4) * len(others)
-        if int(status[0]) != 0:
+        self.complete = int(status[0]) == 0
+        if not self.complete:
             logger.warning(me, "fused exchange finished with missing contributors (timeout/abort)")
         return list(self.train_set), int(total)
 

@@ -170,6 +170,7 @@ class BaseProtocol(CommunicationProtocol):
         self._running = False
         self._terminated = threading.Event()
         self._direct_of: Dict[str, Any] = {}  # node -> set of its direct neighbours (from its beats)
+        self._temp_links: Dict[str, Any] = {}  # cached links to non-neighbours (create_connection sends)
 
     # ------------------------------------------------------------ lifecycle
     def start(self) -> None:
@@ -183,6 +184,12 @@ class BaseProtocol(CommunicationProtocol):
         self._heartbeater.stop()
         self._gossiper.stop()
         self._neighbors.clear_neighbors()
+        for addr, link in list(self._temp_links.items()):
+            try:
+                self._transport.close_link(addr, link, False)
+            except Exception:
+                pass
+        self._temp_links.clear()
         self._transport.stop()
         self._terminated.set()
 
@@ -246,8 +253,11 @@ class BaseProtocol(CommunicationProtocol):
             if link is None:
                 if not create_connection:
                     raise NeighborNotConnectedError(f"{nei} is not a direct neighbour of {self.addr}")
-                temp_link = self._transport.open_link(nei, False)
-                link = temp_link
+                # links to non-neighbours (train-set peers) are kept for reuse instead of
+                # being opened and torn down around every model send
+                link = self._temp_links.get(nei)
+                if link is None:
+                    link = self._temp_links[nei] = self._transport.open_link(nei, False)
             err = self._transport.deliver(nei, link, msg)
             if err:
                 raise CommunicationError(f"{nei} answered with error: {err}")
@@ -255,6 +265,12 @@ class BaseProtocol(CommunicationProtocol):
             raise
         except Exception as e:
             logger.info(self.addr, f"send of '{msg.cmd}' to {nei} failed ({e}); removing neighbour")
+            stale = self._temp_links.pop(nei, None)
+            if stale is not None:
+                try:
+                    self._transport.close_link(nei, stale, False)
+                except Exception:
+                    pass
             self._neighbors.remove(nei, disconnect_msg=True)
         finally:
             if temp_link is not None:
@@ -281,6 +297,16 @@ class BaseProtocol(CommunicationProtocol):
                 continue
             logger.info(self.addr, f"send of '{msg.cmd}' to {nei} failed ({res}); removing neighbour")
             self._neighbors.remove(nei, disconnect_msg=True)
+
+    def broadcast_async(self, msg: Message) -> None:
+        """Fire-and-forget broadcast: queued to the gossiper thread, which performs the
+        (overlapped) sends and evicts neighbours that fail, exactly like :meth:`broadcast`."""
+        if not Settings.ASYNC_BOOKKEEPING:
+            self.broadcast(msg)
+            return
+        targets = list(self._neighbors.get_all(only_direct=True))
+        if targets:
+            self._gossiper.add_broadcast(msg, self.broadcast)
 
     def _beat_msg(self, now: float) -> Message:
         from p2pfl_b200.commands.control import EXTENDED_MARK

@@ -27,6 +27,8 @@ class NodeState:
         self.learner: Any = None
         # base of the data-plane sequence numbers of this experiment (agreed through start_learning)
         self.seq_base: int = 0
+        # round whose fused device exchange completed with every contributor (None otherwise)
+        self.fused_complete_round: Optional[int] = None
 
         # who aggregated what this round: node -> list of contributors
         self.models_aggregated: Dict[str, List[str]] = {}

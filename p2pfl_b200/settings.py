@@ -67,6 +67,12 @@ class Settings:
     """Wire dtype of the device data plane: 'bf16' (inbox mode B) or 'fp32'."""
     DEVICE_TILE_ELEMS: int = 16384
     """Elements per data-plane tile (one arrival flag per tile)."""
+    PREVOTE: bool = True
+    """Cast the ballot for round r+1 while round r trains (ballots are random and
+    ``vote_train_set`` already accepts round+1), so the vote is no barrier between rounds."""
+    ASYNC_BOOKKEEPING: bool = True
+    """``metrics`` / ``models_aggregated`` / ``models_ready`` broadcasts leave through the
+    gossiper thread instead of blocking the learning thread on N-1 round trips."""
     AMP_BF16: bool = False
     """Eager (autograd) learners run forward/backward under bf16 autocast on CUDA."""
     RELAY_PRUNING: bool = True

@@ -36,7 +36,7 @@ class GossipModelStage(Stage):
             return None
         st.learner.set_parameters(params)
         contributors = agg.get_aggregated_models()
-        proto.broadcast(proto.build_msg("models_ready", [], round=st.round))
+        getattr(proto, "broadcast_async", proto.broadcast)(proto.build_msg("models_ready", [], round=st.round))
         t1 = time.time()
         GossipModelStage._diffuse(ctx, params, contributors, t1)
         ctx.timings["aggregate"] = ctx.timings.get("aggregate", 0.0) + t1 - t0
@@ -50,6 +50,8 @@ class GossipModelStage(Stage):
         st, proto = ctx.state, ctx.communication_protocol
         fixed_round = st.round
         train_set = set(st.train_set)
+        # after a complete fused exchange every trainer holds the aggregate by construction
+        trainers_done = getattr(st, "fused_complete_round", None) == fixed_round
 
         def candidates() -> List[str]:
             # trainers normally finish on their own; give them a grace period
@@ -59,13 +61,19 @@ class GossipModelStage(Stage):
             for n in proto.get_neighbors(only_direct=True):
                 if st.nei_status.get(n, -1) >= fixed_round:  # Q17: .get
                     continue
+                if trainers_done and n in train_set:
+                    continue
                 if n in train_set and not grace_over:
                     continue
                 out.append(n)
             return out
 
         def pending() -> List[str]:
-            return [n for n in proto.get_neighbors(only_direct=True) if st.nei_status.get(n, -1) < fixed_round]
+            return [
+                n
+                for n in proto.get_neighbors(only_direct=True)
+                if st.nei_status.get(n, -1) < fixed_round and not (trainers_done and n in train_set)
+            ]
 
         cache: List[Any] = []
 

@@ -32,6 +32,7 @@ class TrainStage(Stage):
         agg.set_nodes_to_aggregate(st.train_set)
         TrainStage.replay_early_models(ctx)
         st.learner.begin_round(st.round)
+        TrainStage.prevote(ctx)
 
         if ctx.early_stopping_fn():
             return None
@@ -55,7 +56,10 @@ class TrainStage(Stage):
             # FedAvg-accumulates theirs into the live parameters as the tiles land
             contributors, total_w = fused.run(st.seq_base + st.round + 1)
             held = agg.add_model(st.learner.live_params(), contributors, total_w)
-            proto.broadcast(proto.build_msg("models_aggregated", held, round=st.round))
+            # every trainer that ran the exchange to completion holds the aggregate by
+            # construction: GossipModelStage need not wait for their `models_ready`
+            st.fused_complete_round = st.round if fused.complete else None
+            getattr(proto, "broadcast_async", proto.broadcast)(proto.build_msg("models_aggregated", held, round=st.round))
         else:
             held = agg.add_model(st.learner.export_model(), [st.addr], st.learner.get_num_samples()[0])
             proto.broadcast(proto.build_msg("models_aggregated", held, round=st.round))
@@ -66,6 +70,20 @@ class TrainStage(Stage):
         if ctx.early_stopping_fn():
             return None
         return StageFactory.get_stage("GossipModelStage")
+
+    @staticmethod
+    def prevote(ctx: LearningContext) -> None:
+        """Cast next round's ballot now, so that it travels while this round trains."""
+        from p2pfl_b200.settings import Settings
+
+        st = ctx.state
+        if not (Settings.PREVOTE and Settings.VOTE_EVERY_ROUND):
+            return
+        if st.round is None or st.total_rounds is None or st.round + 1 >= st.total_rounds:
+            return
+        from p2pfl_b200.stages.base_node.vote_train_set_stage import VoteTrainSetStage
+
+        VoteTrainSetStage.cast_ballot(ctx, st.round + 1)
 
     @staticmethod
     def replay_early_models(ctx: LearningContext) -> None:

@@ -60,19 +60,27 @@ class VoteTrainSetStage(Stage):
 
     @staticmethod
     def _vote(ctx: LearningContext) -> None:
+        VoteTrainSetStage.cast_ballot(ctx, ctx.state.round)
+
+    @staticmethod
+    def cast_ballot(ctx: LearningContext, rnd: int) -> None:
+        """Sample candidates, weight them, record and broadcast the ballot for round ``rnd``
+        (a no-op when this node already voted for that round, e.g. by pre-voting)."""
         st, proto = ctx.state, ctx.communication_protocol
+        if st.addr in st.train_set_votes.get(rnd, {}):
+            return
         candidates = list(proto.get_neighbors(only_direct=False).keys())
         if st.addr not in candidates:
             candidates.append(st.addr)
         k = min(Settings.TRAIN_SET_SIZE, len(candidates))
         picked = random.sample(candidates, k)
         ballot = {c: math.floor(random.randint(0, 1000) / (i + 1)) for i, c in enumerate(picked)}
-        st.train_set_votes.setdefault(st.round, {})[st.addr] = ballot
+        st.train_set_votes.setdefault(rnd, {})[st.addr] = ballot
         flat: List[str] = []
         for c, w in ballot.items():
             flat += [c, str(w)]
-        logger.debug(st.addr, f"voting: {ballot}")
-        proto.broadcast(proto.build_msg("vote_train_set", flat, round=st.round))
+        logger.debug(st.addr, f"voting for round {rnd}: {ballot}")
+        proto.broadcast(proto.build_msg("vote_train_set", flat, round=rnd))
 
     @staticmethod
     def _aggregate_votes(ctx: LearningContext) -> List[str]:

@@ -19,4 +19,5 @@ class WaitAggregatedModelsStage(Stage):
     def execute(ctx: LearningContext) -> Optional[Type[Stage]]:
         ctx.aggregator.set_waiting_aggregated_model(ctx.state.train_set)
         TrainStage.replay_early_models(ctx)
+        TrainStage.prevote(ctx)
         return StageFactory.get_stage("GossipModelStage")

@@ -24,7 +24,8 @@ def broadcast_metrics(protocol: Any, state: Any, results: Dict[str, float]) -> N
     flat: List[str] = []
     for k, v in results.items():
         flat += [str(k), str(v)]
-    protocol.broadcast(protocol.build_msg("metrics", flat, round=state.round))
+    msg = protocol.build_msg("metrics", flat, round=state.round)
+    getattr(protocol, "broadcast_async", protocol.broadcast)(msg)  # nobody waits on metrics
 
 
 def evaluate_and_share(ctx: Any) -> None:
