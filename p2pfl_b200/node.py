@@ -126,6 +126,10 @@ class Node:
 
     def start(self, wait: bool = False) -> None:
         self.assert_running(False)
+        if Settings.GIL_SWITCH_INTERVAL and Settings.GIL_SWITCH_INTERVAL > 0:
+            import sys
+
+            sys.setswitchinterval(Settings.GIL_SWITCH_INTERVAL)
         self.__running = True
         logger.register_node(self.addr, self.state, self.state.simulation)
         self._communication_protocol.start()

@@ -67,6 +67,10 @@ class Settings:
     """Wire dtype of the device data plane: 'bf16' (inbox mode B) or 'fp32'."""
     DEVICE_TILE_ELEMS: int = 16384
     """Elements per data-plane tile (one arrival flag per tile)."""
+    GIL_SWITCH_INTERVAL: float = 0.0005
+    """``sys.setswitchinterval`` applied when a node starts.  The learning thread shares the
+    interpreter with the RPC workers, the gossiper and the heartbeater; with CPython's default
+    5 ms a thread returning from a CUDA wait can sit that long before it runs again."""
     PREVOTE: bool = True
     """Cast the ballot for round r+1 while round r trains (ballots are random and
     ``vote_train_set`` already accepts round+1), so the vote is no barrier between rounds."""
