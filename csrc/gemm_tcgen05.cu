@@ -144,6 +144,88 @@ __device__ __forceinline__ uint32_t make_idesc(uint32_t bn) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 }
 
+// Drain one 128 x bn accumulator tile: TMEM -> registers -> fused epilogue -> global.
+// Called by the four epilogue warps; `q` is the warp's TMEM lane quarter.
+__device__ __forceinline__ void epilogue_tile(const Epilogue& ep, int M, int N, int m0, int n0, uint32_t bn,
+                                              uint32_t tmem_base, int q, int lane, bool single_n_tile) {
+  const int m = m0 + q * 32 + lane;
+  const float bias_row = (ep.bias && ep.bias_per_row && m < M) ? ep.bias[m] : 0.f;
+#pragma unroll 1
+  for (int c = 0; c < (int)bn / 32; ++c) {
+    const int nb = n0 + c * 32;
+    if (nb >= N) break;
+    uint32_t r[32];
+    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), r);
+    float x[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      float v = __uint_as_float(r[j]) * ep.alpha;
+      if (ep.bias) v += ep.bias_per_row ? bias_row : ((nb + j < N) ? ep.bias[nb + j] : 0.f);
+      if (ep.relu) v = fmaxf(v, 0.f);
+      x[j] = v;
+    }
+    if (ep.mask && m < M) {
+      const __nv_bfloat16* mk = ep.mask + (size_t)m * ep.ld_mask + nb;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (nb + j < N && !(__bfloat162float(mk[j]) > 0.f)) x[j] = 0.f;
+    }
+    const int valid = (N - nb) < 32 ? (N - nb) : 32;
+    if (m < M) {
+      if (ep.rowsum) {
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < valid) s += x[j];
+        // one N tile of <= 32 columns owns the whole row: plain store, no zero-init needed
+        if (single_n_tile && N <= 32) ep.rowsum[m] = s;
+        else atomicAdd(ep.rowsum + m, s);
+      }
+      // direct ([M, ld]) outputs: each thread writes its row's 32 contiguous values
+      if (ep.out_f32) {
+        float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
+        if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < valid) o[j] = x[j];
+        }
+      }
+      if (ep.out_bf16) {
+        __nv_bfloat16* o = ep.out_bf16 + (size_t)m * ep.ld_bf16 + nb;
+        if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 u;
+            u.x = pack_bf16x2(x[j], x[j + 1]);
+            u.y = pack_bf16x2(x[j + 2], x[j + 3]);
+            u.z = pack_bf16x2(x[j + 4], x[j + 5]);
+            u.w = pack_bf16x2(x[j + 6], x[j + 7]);
+            *reinterpret_cast<uint4*>(o + j) = u;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < valid) o[j] = __float2bfloat16_rn(x[j]);
+        }
+      }
+      // transposed outputs: consecutive lanes hold consecutive m -> coalesced per column
+      if (ep.out_f32_t) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < valid) ep.out_f32_t[(size_t)(nb + j) * ep.ld_f32_t + m] = x[j];
+      }
+      if (ep.out_bf16_t) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < valid) ep.out_bf16_t[(size_t)(nb + j) * ep.ld_bf16_t + m] = __float2bfloat16_rn(x[j]);
+      }
+    }
+  }
+}
+
 constexpr int kMaxGroup = 4;
 constexpr int kMaxBN = 256;
 constexpr uint32_t kRingBytes = 4 * (kTileABytes + kMaxBN * BK * 2);  // 4 stages of the widest tile = 192 KB
@@ -250,82 +332,7 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
     const int m = m0 + q * 32 + lane;
     mbar_wait(smem_u32(&tmem_full_bar), 0);
     tc_fence_after();
-    const float bias_row = (ep.bias && ep.bias_per_row && m < M) ? ep.bias[m] : 0.f;
-    const bool single_n_tile = gridDim.y == 1 || (int)bn >= N;
-#pragma unroll 1
-    for (int c = 0; c < (int)bn / 32; ++c) {
-      const int nb = n0 + c * 32;
-      if (nb >= N) break;
-      uint32_t r[32];
-      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), r);
-      float x[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        float v = __uint_as_float(r[j]) * ep.alpha;
-        if (ep.bias) v += ep.bias_per_row ? bias_row : ((nb + j < N) ? ep.bias[nb + j] : 0.f);
-        if (ep.relu) v = fmaxf(v, 0.f);
-        x[j] = v;
-      }
-      if (ep.mask && m < M) {
-        const __nv_bfloat16* mk = ep.mask + (size_t)m * ep.ld_mask + nb;
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (nb + j < N && !(__bfloat162float(mk[j]) > 0.f)) x[j] = 0.f;
-      }
-      const int valid = (N - nb) < 32 ? (N - nb) : 32;
-      if (m < M) {
-        if (ep.rowsum) {
-          float s = 0.f;
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < valid) s += x[j];
-          // one N tile of <= 32 columns owns the whole row: plain store, no zero-init needed
-          if (single_n_tile && N <= 32) ep.rowsum[m] = s;
-          else atomicAdd(ep.rowsum + m, s);
-        }
-        // direct ([M, ld]) outputs: each thread writes its row's 32 contiguous values
-        if (ep.out_f32) {
-          float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
-          if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j < valid) o[j] = x[j];
-          }
-        }
-        if (ep.out_bf16) {
-          __nv_bfloat16* o = ep.out_bf16 + (size_t)m * ep.ld_bf16 + nb;
-          if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint4 u;
-              u.x = pack_bf16x2(x[j], x[j + 1]);
-              u.y = pack_bf16x2(x[j + 2], x[j + 3]);
-              u.z = pack_bf16x2(x[j + 4], x[j + 5]);
-              u.w = pack_bf16x2(x[j + 6], x[j + 7]);
-              *reinterpret_cast<uint4*>(o + j) = u;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j < valid) o[j] = __float2bfloat16_rn(x[j]);
-          }
-        }
-        // transposed outputs: consecutive lanes hold consecutive m -> coalesced per column
-        if (ep.out_f32_t) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < valid) ep.out_f32_t[(size_t)(nb + j) * ep.ld_f32_t + m] = x[j];
-        }
-        if (ep.out_bf16_t) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < valid) ep.out_bf16_t[(size_t)(nb + j) * ep.ld_bf16_t + m] = __float2bfloat16_rn(x[j]);
-        }
-      }
-    }
+    epilogue_tile(ep, M, N, m0, n0, bn, tmem_base, q, lane, gridDim.y == 1 || (int)bn >= N);
     tc_fence_before();
   }
 
@@ -444,4 +451,247 @@ extern "C" int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* ar
 
 extern "C" int p2pfl_gemm_tn_grouped(int device, void* stream, const p2pfl_gemm_args* args, int count) {
   return launch_group(device, as_stream(stream), args, count);
+}
+
+// ===========================================================================
+// GEMM chain: the DEPENDENT part of a small-batch train step in one launch.
+//
+// The MLP step (mlp.py:57-80 + autograd) is a chain of tiny GEMMs in which every
+// link needs the previous link's output: fwd1 -> fwd2 -> fwd3 -> softmax/CE ->
+// dgrad3 -> dgrad2.  As separate launches each link pays a launch + prologue +
+// drain (~5 us for ~0.1 us of math).  Here ONE CTA walks the whole list: barriers,
+// TMEM and tensor maps are set up once, the TMA / MMA / epilogue warps keep their
+// pipeline state across links, and a CTA-wide barrier with a generic->async proxy
+// fence separates links (the next link's TMA loads read what this link's epilogue
+// stored).  N (the batch) is tiled in 32 columns; two 32-column TMEM accumulators
+// let the MMA of the next tile overlap the epilogue of the current one.
+namespace {
+
+constexpr int kChainMaxGemm = 8;
+constexpr int kChainMaxPhases = 12;
+constexpr uint32_t kChainBN = 32;
+constexpr uint32_t kChainStageBytes = kTileABytes + kChainBN * BK * 2;  // 20 KB
+constexpr int kChainStages = 9;
+
+struct ChainArgs {
+  CUtensorMap ma[kChainMaxGemm];
+  CUtensorMap mb[kChainMaxGemm];
+  Epilogue ep[kChainMaxGemm];
+  int32_t M[kChainMaxGemm], N[kChainMaxGemm], K[kChainMaxGemm];
+  int32_t kind[kChainMaxPhases];  // 0 = GEMM, 1 = softmax cross-entropy
+  int32_t idx[kChainMaxPhases];
+  int32_t n_phases;
+  p2pfl_ce_args ce;
+};
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// log-softmax + cross-entropy forward/backward by the 128 epilogue threads (one warp per row)
+__device__ void chain_ce(const p2pfl_ce_args& a, int ewarp, int lane, float* s_db) {
+  const int et = ewarp * 32 + lane;
+  const int C = a.C, B = a.B;
+  for (int c = et; c < C; c += 128) s_db[c] = 0.f;
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  const float inv_b = 1.f / (float)B;
+  float wloss = 0.f;
+  __nv_bfloat16* dl = reinterpret_cast<__nv_bfloat16*>(a.dlogits_bf16);
+  __nv_bfloat16* dlt = reinterpret_cast<__nv_bfloat16*>(a.dlogits_t_bf16);
+  for (int row = ewarp; row < B; row += 4) {
+    const float* x = a.logits + (size_t)row * a.ld_logits;
+    float mx = -INFINITY;
+    for (int c = lane; c < C; c += 32) mx = fmaxf(mx, x[c]);
+    mx = warp_max(mx);
+    float se = 0.f;
+    for (int c = lane; c < C; c += 32) se += __expf(x[c] - mx);
+    se = warp_sum(se);
+    const float lse = mx + __logf(se);
+    const int y = a.labels[row];
+    for (int c = lane; c < C; c += 32) {
+      const float g = (__expf(x[c] - lse) - (c == y ? 1.f : 0.f)) * inv_b;
+      const __nv_bfloat16 gb = __float2bfloat16_rn(g);
+      if (dl) dl[(size_t)row * a.ld_d + c] = gb;
+      if (dlt) dlt[(size_t)c * a.ld_dt + row] = gb;
+      atomicAdd(s_db + c, __bfloat162float(gb));
+    }
+    if (lane == 0 && y >= 0 && y < C) wloss += lse - x[y];
+  }
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  if (a.dbias)
+    for (int c = et; c < C; c += 128) a.dbias[c] = s_db[c];
+  if (a.loss_sum && lane == 0 && wloss != 0.f) atomicAdd(a.loss_sum, wloss);
+}
+
+__global__ void __launch_bounds__(kThreadsGemm, 1)
+gemm_chain_kernel(const __grid_constant__ ChainArgs g) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  __shared__ __align__(8) uint64_t full_bar[kChainStages];
+  __shared__ __align__(8) uint64_t empty_bar[kChainStages];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ float s_db[256];
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int p = 0; p < g.n_phases; ++p)
+      if (g.kind[p] == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&g.ma[g.idx[p]])) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&g.mb[g.idx[p]])) : "memory");
+      }
+    for (int s = 0; s < kChainStages; ++s) {
+      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(smem_u32(&tmem_full_bar[a]), 1);
+      mbar_init(smem_u32(&tmem_empty_bar[a]), 4);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), 64);
+  pdl_launch_dependents();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();
+
+  uint32_t it = 0;       // k-block counter over the whole chain (smem ring position)
+  uint32_t tile_it = 0;  // output-tile counter over the whole chain (TMEM accumulator position)
+  const uint32_t idesc = make_idesc(kChainBN);
+
+  for (int p = 0; p < g.n_phases; ++p) {
+    if (g.kind[p] == 0) {
+      const int gi = g.idx[p];
+      const int M = g.M[gi], N = g.N[gi], K = g.K[gi];
+      const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + (int)kChainBN - 1) / (int)kChainBN;
+      const int num_kb = (K + BK - 1) / BK;
+      const int n_tiles = tiles_m * tiles_n;
+      if (warp == 0) {
+        // ---------------- TMA producer ----------------
+        if (elect_one()) {
+          uint32_t lit = it;  // every lane of the warp advances `it` below, whoever is elected
+          for (int t = 0; t < n_tiles; ++t) {
+            const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * (int)kChainBN;
+            for (int kb = 0; kb < num_kb; ++kb, ++lit) {
+              const uint32_t s = lit % kChainStages, ph = (lit / kChainStages) & 1u;
+              mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
+              const uint32_t bar = smem_u32(&full_bar[s]);
+              mbar_expect_tx(bar, kChainStageBytes);
+              const uint32_t dst = smem_u32(smem + (size_t)s * kChainStageBytes);
+              tma_load_2d(&g.ma[gi], bar, dst, kb * BK, m0);
+              tma_load_2d(&g.mb[gi], bar, dst + kTileABytes, kb * BK, n0);
+            }
+          }
+        }
+        __syncwarp();
+      } else if (warp == 1) {
+        // ---------------- MMA issuer ----------------
+        for (int t = 0; t < n_tiles; ++t, ++tile_it) {
+          const uint32_t acc = tile_it & 1u, aph = (tile_it >> 1) & 1u;
+          mbar_wait(smem_u32(&tmem_empty_bar[acc]), aph ^ 1u);  // epilogue drained this accumulator
+          tc_fence_after();
+          for (int kb = 0; kb < num_kb; ++kb, ++it) {
+            const uint32_t s = it % kChainStages, ph = (it / kChainStages) & 1u;
+            mbar_wait(smem_u32(&full_bar[s]), ph);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t a_addr = smem_u32(smem + (size_t)s * kChainStageBytes);
+              const uint64_t da = make_smem_desc(a_addr);
+              const uint64_t db = make_smem_desc(a_addr + kTileABytes);
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                umma_bf16(tmem_base + acc * kChainBN, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                          (kb | k) != 0 ? 1u : 0u);
+              umma_commit(smem_u32(&empty_bar[s]));
+              if (kb == num_kb - 1) umma_commit(smem_u32(&tmem_full_bar[acc]));
+            }
+            __syncwarp();
+          }
+        }
+      } else {
+        // ---------------- epilogue ----------------
+        const int q = warp & 3;
+        for (int t = 0; t < n_tiles; ++t, ++tile_it) {
+          const uint32_t acc = tile_it & 1u, aph = (tile_it >> 1) & 1u;
+          const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * (int)kChainBN;
+          mbar_wait(smem_u32(&tmem_full_bar[acc]), aph);
+          tc_fence_after();
+          epilogue_tile(g.ep[gi], M, N, m0, n0, kChainBN, tmem_base + acc * kChainBN, q, lane, tiles_n == 1);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&tmem_empty_bar[acc]));
+        }
+      }
+      // the roles that did not iterate still advance the shared counters
+      if (warp == 0) tile_it += n_tiles;
+      if (warp != 1) it += (uint32_t)(n_tiles * num_kb);
+    } else if (warp >= 2) {
+      chain_ce(g.ce, warp - 2, lane, s_db);
+    }
+    // ---- link boundary: this link's global stores (generic proxy) must be visible to the
+    // next link's TMA loads (async proxy) and to its plain loads
+    __threadfence();
+    asm volatile("fence.proxy.async;" ::: "memory");
+    __syncthreads();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 64);
+  }
+}
+
+}  // namespace
+
+extern "C" int p2pfl_gemm_chain(int device, void* stream, const p2pfl_gemm_args* gemms, int n_gemm,
+                                const int32_t* phase_kind, const int32_t* phase_idx, int n_phases,
+                                const p2pfl_ce_args* ce) {
+  P2PFL_REQUIRE(n_gemm >= 0 && n_gemm <= kChainMaxGemm && n_phases >= 1 && n_phases <= kChainMaxPhases,
+                "a GEMM chain takes at most 8 GEMMs in at most 12 links");
+  P2PFL_REQUIRE(phase_kind && phase_idx, "null phase list");
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  ChainArgs g;
+  memset(&g, 0, sizeof(g));
+  GroupedArgs tmp;  // reuse the single-problem filler (maps + epilogue), then copy across
+  for (int i = 0; i < n_gemm; ++i) {
+    const p2pfl_gemm_args& a = gemms[i];
+    P2PFL_REQUIRE(a.A && a.B && a.M > 0 && a.N > 0 && a.K > 0, "bad GEMM shape or operands");
+    memset(&tmp, 0, sizeof(tmp));
+    if (int rc = fill_problem(tmp, 0, a)) return rc;
+    g.ma[i] = tmp.ma[0];
+    if (int rc = make_map(&g.mb[i], a.B, a.N, a.K, a.ldb, (int)kChainBN)) return rc;  // chain tiles N by 32
+    g.ep[i] = tmp.ep[0];
+    g.M[i] = a.M;
+    g.N[i] = a.N;
+    g.K[i] = a.K;
+  }
+  bool has_ce = false;
+  for (int p = 0; p < n_phases; ++p) {
+    P2PFL_REQUIRE(phase_kind[p] == 0 || phase_kind[p] == 1, "unknown link kind");
+    P2PFL_REQUIRE(phase_kind[p] == 1 || (phase_idx[p] >= 0 && phase_idx[p] < n_gemm), "link refers to a missing GEMM");
+    g.kind[p] = phase_kind[p];
+    g.idx[p] = phase_idx[p];
+    has_ce |= phase_kind[p] == 1;
+  }
+  g.n_phases = n_phases;
+  if (has_ce) {
+    P2PFL_REQUIRE(ce && ce->logits && ce->labels && ce->B > 0 && ce->C > 0 && ce->C <= 256, "bad cross-entropy link");
+    g.ce = *ce;
+  }
+  constexpr size_t smem = (size_t)kChainStages * kChainStageBytes + 1024;
+  static bool attr_set[64] = {false};
+  if (device >= 0 && device < 64 && !attr_set[device]) {
+    P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set[device] = true;
+  }
+  P2PFL_CUDA_OK(launch_pdl(gemm_chain_kernel, dim3(1), dim3(kThreadsGemm), smem, as_stream(stream), g));
+  return 0;
 }

@@ -208,6 +208,22 @@ int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* args);
  * both depend only on that layer's dZ): fewer launches on the latency-bound step. */
 int p2pfl_gemm_tn_grouped(int device, void* stream, const p2pfl_gemm_args* args, int count);
 
+/* The dependent part of a small-batch train step as ONE launch: a single CTA walks a
+ * list of links - GEMMs (same arguments as p2pfl_gemm_tn; N tiled by 32) and at most
+ * one softmax-cross-entropy link - each consuming what the previous one stored
+ * (mlp.py:57-80 forward chain + loss + autograd dgrad chain). */
+typedef struct {
+  const float* logits; int32_t ld_logits;   /* fp32 [B, ld_logits] */
+  const int32_t* labels; int32_t B, C;       /* C <= 256 */
+  void* dlogits_bf16; int32_t ld_d;          /* bf16 [B, ld_d], already / B */
+  void* dlogits_t_bf16; int32_t ld_dt;       /* bf16 [C, ld_dt] */
+  float* dbias;                              /* [C], overwritten (nullable) */
+  float* loss_sum;                           /* += sum of per-sample losses (nullable) */
+} p2pfl_ce_args;
+int p2pfl_gemm_chain(int device, void* stream, const p2pfl_gemm_args* gemms, int n_gemm,
+                     const int32_t* link_kind /* 0 GEMM, 1 cross-entropy */, const int32_t* link_idx,
+                     int n_links, const p2pfl_ce_args* ce);
+
 /* ----------------------------------------------------------- convolution path
  * K6/K7 (cnn.py:78-81 Conv2d + ReLU + MaxPool2d through cuDNN/ATen) and the
  * ResNet-style blocks of BASELINE.json config 3.  Activations are NHWC bf16.

@@ -305,6 +305,9 @@ class B200Learner(TorchLearner):
         feat = Ls[0].in_f
         ldB = act["ldB"]
         C = Ls[-1].out_f
+        if Settings.MLP_CHAIN and 2 * nL - 1 <= 8 and C <= 256:
+            self._train_step_chain(x16, xT16, y, bsz, act, loss_slot, step_offset, lr)
+            return
         # no gradient memset: every weight gradient is overwritten by its wgrad GEMM and every
         # bias gradient is stored (not accumulated) by the CE kernel / the dgrad row sums
         # (batches wider than one 32-column tile accumulate row sums, so they do need zeros)
@@ -330,6 +333,52 @@ class B200Learner(TorchLearner):
             # a layer's wgrad and dgrad both depend only on its dZ: one launch for the pair
             ops.gemm_tn_grouped(self.device, group)
         # Adam over the whole arena, refreshing the bf16 copy AND the transposed dgrad operands
+        ops.adam_step_t(self.flat, self.grads, self.adam_m, self.adam_v, self.w16, lr, self.adam_step, step_offset,
+                        self.wT16, self._tdescs)  # fmt: skip
+
+    def _train_step_chain(self, x16, xT16, y, bsz: int, act, loss_slot, step_offset: int, lr: float) -> None:
+        """Three launches per step: (1) ONE single-CTA kernel for every dependent link - the
+        forward chain, the loss and the dgrad chain; (2) all weight-gradient GEMMs, which
+        depend only on (1), as one grouped launch; (3) Adam + bf16 refresh + transposes."""
+        Ls = self._layers
+        nL = len(Ls)
+        feat = Ls[0].in_f
+        ldB = act["ldB"]
+        C = Ls[-1].out_f
+        if bsz > 32:
+            self.grads.zero_()  # row sums of wider batches are accumulated
+        gemms, links = [], []
+        for li, L in enumerate(Ls):  # forward, swap-AB: D[out, bsz] = W[out, in] . X[bsz, in]^T
+            last = li == nL - 1
+            Bm, ldb = (x16, feat) if li == 0 else (act["H"][li - 1], _pad8(L.in_f))
+            common = dict(bias=self.flat[L.b_off :], bias_per_row=True)
+            if last:
+                gemms.append(ops.gemm_args(self.w16[L.w_off :], L.in_f, Bm, ldb, L.out_f, bsz, L.in_f,
+                                           out_f32_t=act["logits"], ld_f32_t=act["ld_logits"], **common))  # fmt: skip
+            else:
+                gemms.append(ops.gemm_args(self.w16[L.w_off :], L.in_f, Bm, ldb, L.out_f, bsz, L.in_f, relu=True,
+                                           out_bf16=act["HT"][li], ld_bf16=ldB, out_bf16_t=act["H"][li],
+                                           ld_bf16_t=_pad8(L.out_f), **common))  # fmt: skip
+            links.append(("gemm", len(gemms) - 1))
+        links.append(("ce", 0))
+        ce = ops.ce_args(act["logits"], act["ld_logits"], y, bsz, C, act["dZ"][-1], _pad8(C), act["dZT"][-1], ldB,
+                         self.grads[Ls[-1].b_off :], loss_slot)  # fmt: skip
+        for li in range(nL - 1, 0, -1):  # dgrad: dH^T[in, bsz] = W^T[in, out] . dZ[bsz, out]^T, ReLU mask, bias grad
+            L, P = Ls[li], Ls[li - 1]
+            gemms.append(ops.gemm_args(
+                self.wT16[L.wt_off :], _pad8(L.out_f), act["dZ"][li], _pad8(L.out_f), L.in_f, bsz, L.out_f,
+                mask=act["HT"][li - 1], ld_mask=ldB, out_bf16=act["dZT"][li - 1], ld_bf16=ldB,
+                out_bf16_t=act["dZ"][li - 1] if li - 1 > 0 else None, ld_bf16_t=_pad8(P.out_f),
+                rowsum=self.grads[P.b_off :]))  # fmt: skip
+            links.append(("gemm", len(gemms) - 1))
+        ops.gemm_chain(self.device, gemms, links, ce)
+        wg = []
+        for li, L in enumerate(Ls):  # wgrad: dW[out, in] = dZ^T[out, bsz] . (X^T[in, bsz])^T   (K = batch)
+            Bm = xT16 if li == 0 else act["HT"][li - 1]
+            wg.append(ops.gemm_args(act["dZT"][li], ldB, Bm, ldB, L.out_f, L.in_f, bsz,
+                                    out_f32=self.grads[L.w_off :], ld_f32=L.in_f))  # fmt: skip
+        for i in range(0, len(wg), 4):
+            ops.gemm_tn_grouped(self.device, wg[i : i + 4])
         ops.adam_step_t(self.flat, self.grads, self.adam_m, self.adam_v, self.w16, lr, self.adam_step, step_offset,
                         self.wT16, self._tdescs)  # fmt: skip
 

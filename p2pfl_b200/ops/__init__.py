@@ -48,6 +48,17 @@ class GemmArgs(C.Structure):
     ]  # fmt: skip
 
 
+class CeArgs(C.Structure):
+    _fields_ = [
+        ("logits", C.c_void_p), ("ld_logits", C.c_int32),
+        ("labels", C.c_void_p), ("B", C.c_int32), ("C", C.c_int32),
+        ("dlogits", C.c_void_p), ("ld_d", C.c_int32),
+        ("dlogits_t", C.c_void_p), ("ld_dt", C.c_int32),
+        ("dbias", C.c_void_p),
+        ("loss_sum", C.c_void_p),
+    ]  # fmt: skip
+
+
 class PushTable(C.Structure):
     _fields_ = [
         ("inbox", C.c_void_p * MAX_PEERS),
@@ -308,6 +319,26 @@ def gemm_tn(A: torch.Tensor, *args, **kwargs) -> None:
     """One tcgen05 GEMM launch (see :func:`gemm_args` for the parameters)."""
     a = gemm_args(A, *args, **kwargs)
     _check(lib().p2pfl_gemm_tn(_dev(A), _stream(), C.byref(a)))
+    _count()
+
+
+def ce_args(logits, ld_logits: int, labels, B: int, Cn: int, dlogits, ld_d: int, dlogits_t, ld_dt: int, dbias, loss_sum) -> CeArgs:
+    g = lambda t: 0 if t is None else t.data_ptr()  # noqa: E731
+    return CeArgs(g(logits), ld_logits, g(labels), B, Cn, g(dlogits), ld_d, g(dlogits_t), ld_dt, g(dbias), g(loss_sum))
+
+
+def gemm_chain(device: torch.device, gemms: Sequence[GemmArgs], links: Sequence[tuple], ce: Optional[CeArgs] = None) -> None:
+    """ONE launch for a list of dependent links: ``("gemm", i)`` runs ``gemms[i]``, ``("ce", 0)`` the
+    softmax-cross-entropy described by ``ce``; each link sees what the previous one stored."""
+    arr = (GemmArgs * max(1, len(gemms)))(*gemms)
+    kinds = (C.c_int32 * len(links))(*[0 if k == "gemm" else 1 for k, _ in links])
+    idxs = (C.c_int32 * len(links))(*[i for _, i in links])
+    dev = device.index if device.index is not None else torch.cuda.current_device()
+    _check(
+        lib().p2pfl_gemm_chain(
+            dev, _stream(), arr, C.c_int(len(gemms)), kinds, idxs, C.c_int(len(links)), C.byref(ce) if ce is not None else None
+        )
+    )
     _count()
 
 

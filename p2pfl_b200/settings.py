@@ -77,6 +77,9 @@ class Settings:
     ASYNC_BOOKKEEPING: bool = True
     """``metrics`` / ``models_aggregated`` / ``models_ready`` broadcasts leave through the
     gossiper thread instead of blocking the learning thread on N-1 round trips."""
+    MLP_CHAIN: bool = True
+    """Run the dependent links of the fused MLP step (forward chain, loss, dgrad chain) as
+    one single-CTA kernel (``p2pfl_gemm_chain``) instead of one launch per link."""
     AMP_BF16: bool = False
     """Eager (autograd) learners run forward/backward under bf16 autocast on CUDA."""
     RELAY_PRUNING: bool = True

@@ -211,3 +211,28 @@ def test_pdl_on_and_off_give_identical_training():
         finally:
             ops.set_pdl(prev)
     assert torch.equal(flats[0], flats[1])
+
+
+def test_chain_kernel_matches_per_link_launches():
+    """The single-CTA GEMM chain (forward + loss + dgrad links in one launch) must reproduce
+    the per-link launches bit for bit: same tiles, same MMA order, same epilogues."""
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.models import MLP
+    from p2pfl_b200.settings import Settings
+
+    results = []
+    for chain in (True, False):
+        Settings.MLP_CHAIN = chain
+        try:
+            dm = _dm(n_train=640, n_test=128)
+            learner = B200Learner(MLP(seed=3), dm, "p", epochs=1, device=DEV)
+            x, y = dm.tensors("train")
+            losses = [learner.debug_single_step(x[i * 32 : (i + 1) * 32], y[i * 32 : (i + 1) * 32]) for i in range(3)]
+            losses.append(learner.debug_single_step(x[96:126], y[96:126]))  # partial batch of 30
+            results.append((learner.flat.clone(), learner.grads.clone(), losses))
+            learner.close()
+        finally:
+            Settings.MLP_CHAIN = True
+    assert results[0][2] == results[1][2], (results[0][2], results[1][2])
+    assert torch.equal(results[0][1], results[1][1])
+    assert torch.equal(results[0][0], results[1][0])
