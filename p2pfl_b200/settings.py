@@ -77,9 +77,12 @@ class Settings:
     ASYNC_BOOKKEEPING: bool = True
     """``metrics`` / ``models_aggregated`` / ``models_ready`` broadcasts leave through the
     gossiper thread instead of blocking the learning thread on N-1 round trips."""
-    MLP_CHAIN: bool = True
+    MLP_CHAIN: bool = False
     """Run the dependent links of the fused MLP step (forward chain, loss, dgrad chain) as
-    one single-CTA kernel (``p2pfl_gemm_chain``) instead of one launch per link."""
+    one single-CTA kernel (``p2pfl_gemm_chain``) instead of one launch per link.  Measured
+    on B200 (profiles/README.md): 3 launches per step instead of 8, but 13.4 vs 10.6 ms per
+    round - one SM streams all the weights (about 0.5 MB per step) and its TMA bandwidth, not
+    the launch count, becomes the bound.  Off by default; kept for narrower models."""
     AMP_BF16: bool = False
     """Eager (autograd) learners run forward/backward under bf16 autocast on CUDA."""
     RELAY_PRUNING: bool = True

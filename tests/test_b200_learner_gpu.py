@@ -215,12 +215,14 @@ def test_pdl_on_and_off_give_identical_training():
 
 def test_chain_kernel_matches_per_link_launches():
     """The single-CTA GEMM chain (forward + loss + dgrad links in one launch) must reproduce
-    the per-link launches bit for bit: same tiles, same MMA order, same epilogues."""
+    the per-link launches: same tiles, same MMA order, same epilogues (only the loss sum and
+    the last layer's bias gradient are reduced with atomics, whose order may differ)."""
     from p2pfl_b200.learning.b200_learner import B200Learner
     from p2pfl_b200.models import MLP
     from p2pfl_b200.settings import Settings
 
     results = []
+    default = Settings.MLP_CHAIN
     for chain in (True, False):
         Settings.MLP_CHAIN = chain
         try:
@@ -232,7 +234,7 @@ def test_chain_kernel_matches_per_link_launches():
             results.append((learner.flat.clone(), learner.grads.clone(), losses))
             learner.close()
         finally:
-            Settings.MLP_CHAIN = True
-    assert results[0][2] == results[1][2], (results[0][2], results[1][2])
-    assert torch.equal(results[0][1], results[1][1])
-    assert torch.equal(results[0][0], results[1][0])
+            Settings.MLP_CHAIN = default
+    assert all(abs(a - b) < 1e-5 for a, b in zip(results[0][2], results[1][2])), (results[0][2], results[1][2])
+    assert torch.allclose(results[0][1], results[1][1], atol=1e-6, rtol=1e-5)
+    assert torch.allclose(results[0][0], results[1][0], atol=1e-5)
