@@ -65,6 +65,9 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
   const long long t0 = clock64();
@@ -343,6 +346,119 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
   }
 }
 
+// ------------------------------------------------------ persistent variant
+// Large problems (many more tiles than SMs): one CTA per SM walks its share of the
+// output tiles.  Barriers, TMEM and the smem ring are set up once; TWO accumulators in
+// TMEM (2 x bn columns) let the MMA warp start tile i+1 while the epilogue warps are
+// still draining tile i, so the tensor pipe does not idle during epilogues.
+// Tiles are visited M-fastest inside an N panel, which keeps the B panel in L2.
+__global__ void __launch_bounds__(kThreadsGemm, 1)
+gemm_tn_persistent_kernel(const __grid_constant__ GroupedArgs g) {
+  const int M = g.M[0], N = g.N[0], K = g.K[0];
+  const uint32_t bn = (uint32_t)g.bn[0];
+  const CUtensorMap* tma_a = &g.ma[0];
+  const CUtensorMap* tma_b = &g.mb[0];
+  const Epilogue& ep = g.ep[0];
+  const uint32_t stage_bytes = kTileABytes + bn * BK * 2;
+  int n_stages = (int)(kRingBytes / stage_bytes);
+  n_stages = n_stages > kMaxStages ? kMaxStages : n_stages;
+  const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + (int)bn - 1) / (int)bn;
+  const int n_tiles = tiles_m * tiles_n;
+  const int num_kb = (K + BK - 1) / BK;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  __shared__ __align__(8) uint64_t full_bar[kMaxStages];
+  __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tma_a)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tma_b)) : "memory");
+    for (int s = 0; s < n_stages; ++s) {
+      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(smem_u32(&tmem_full_bar[a]), 1);
+      mbar_init(smem_u32(&tmem_empty_bar[a]), 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), 2 * bn);
+  pdl_launch_dependents();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();
+
+  if (warp == 0) {
+    if (elect_one()) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int m0 = (t % tiles_m) * BM, n0 = (t / tiles_m) * (int)bn;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const uint32_t s = it % n_stages, ph = (it / n_stages) & 1u;
+          mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
+          const uint32_t bar = smem_u32(&full_bar[s]);
+          mbar_expect_tx(bar, stage_bytes);
+          const uint32_t dst = smem_u32(smem + (size_t)s * stage_bytes);
+          tma_load_2d(tma_a, bar, dst, kb * BK, m0);
+          tma_load_2d(tma_b, bar, dst + kTileABytes, kb * BK, n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = make_idesc(bn);
+    uint32_t it = 0, tile_it = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tile_it) {
+      const uint32_t acc = tile_it & 1u, aph = (tile_it >> 1) & 1u;
+      mbar_wait(smem_u32(&tmem_empty_bar[acc]), aph ^ 1u);
+      tc_fence_after();
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const uint32_t s = it % n_stages, ph = (it / n_stages) & 1u;
+        mbar_wait(smem_u32(&full_bar[s]), ph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+          const uint64_t da = make_smem_desc(a_addr);
+          const uint64_t db = make_smem_desc(a_addr + kTileABytes);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16(tmem_base + acc * bn, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit(smem_u32(&empty_bar[s]));
+          if (kb == num_kb - 1) umma_commit(smem_u32(&tmem_full_bar[acc]));
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    uint32_t tile_it = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tile_it) {
+      const uint32_t acc = tile_it & 1u, aph = (tile_it >> 1) & 1u;
+      const int m0 = (t % tiles_m) * BM, n0 = (t / tiles_m) * (int)bn;
+      mbar_wait(smem_u32(&tmem_full_bar[acc]), aph);
+      tc_fence_after();
+      epilogue_tile(ep, M, N, m0, n0, bn, tmem_base + acc * bn, q, lane, tiles_n == 1);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&tmem_empty_bar[acc]));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * bn);
+  }
+}
+
 // ------------------------------------------------------------- host: TMA maps
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -439,6 +555,17 @@ int launch_group(int device, cudaStream_t stream, const p2pfl_gemm_args* args, i
     P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set[device] = true;
   }
+  const int sms = sm_count(device);
+  if (count == 1 && gx * gy >= 2 * sms) {
+    // many more tiles than SMs: persistent CTAs with double-buffered accumulators
+    static bool pattr_set[64] = {false};
+    if (device >= 0 && device < 64 && !pattr_set[device]) {
+      P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_tn_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      pattr_set[device] = true;
+    }
+    P2PFL_CUDA_OK(launch_pdl(gemm_tn_persistent_kernel, dim3(sms), dim3(kThreadsGemm), smem, stream, g));
+    return 0;
+  }
   P2PFL_CUDA_OK(launch_pdl(gemm_tn_kernel, dim3(gx, gy, count), dim3(kThreadsGemm), smem, stream, g));
   return 0;
 }
@@ -483,10 +610,6 @@ struct ChainArgs {
   int32_t n_phases;
   p2pfl_ce_args ce;
 };
-
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
 
 // log-softmax + cross-entropy forward/backward by the 128 epilogue threads (one warp per row)
 __device__ void chain_ce(const p2pfl_ce_args& a, int ewarp, int lane, float* s_db) {

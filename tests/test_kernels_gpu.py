@@ -213,6 +213,9 @@ GEMM_SHAPES = [
     (300, 200, 136),
     (512, 512, 512),
     (1024, 256, 4096),
+    # many more tiles than SMs: persistent kernel with double-buffered TMEM accumulators
+    (4096, 4096, 256),
+    (5000, 3000, 136),
 ]
 
 
