@@ -33,6 +33,7 @@ class TrainStage(Stage):
         TrainStage.replay_early_models(ctx)
         st.learner.begin_round(st.round)
         TrainStage.prevote(ctx)
+        ctx.timings["arm"] = ctx.timings.get("arm", 0.0) + time.time() - t0
 
         if ctx.early_stopping_fn():
             return None
@@ -83,7 +84,7 @@ class TrainStage(Stage):
             return
         from p2pfl_b200.stages.base_node.vote_train_set_stage import VoteTrainSetStage
 
-        VoteTrainSetStage.cast_ballot(ctx, st.round + 1)
+        VoteTrainSetStage.cast_ballot(ctx, st.round + 1, background=True)
 
     @staticmethod
     def replay_early_models(ctx: LearningContext) -> None:

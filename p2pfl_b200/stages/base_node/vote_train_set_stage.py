@@ -63,7 +63,7 @@ class VoteTrainSetStage(Stage):
         VoteTrainSetStage.cast_ballot(ctx, ctx.state.round)
 
     @staticmethod
-    def cast_ballot(ctx: LearningContext, rnd: int) -> None:
+    def cast_ballot(ctx: LearningContext, rnd: int, background: bool = False) -> None:
         """Sample candidates, weight them, record and broadcast the ballot for round ``rnd``
         (a no-op when this node already voted for that round, e.g. by pre-voting)."""
         st, proto = ctx.state, ctx.communication_protocol
@@ -80,7 +80,11 @@ class VoteTrainSetStage(Stage):
         for c, w in ballot.items():
             flat += [c, str(w)]
         logger.debug(st.addr, f"voting for round {rnd}: {ballot}")
-        proto.broadcast(proto.build_msg("vote_train_set", flat, round=rnd))
+        msg = proto.build_msg("vote_train_set", flat, round=rnd)
+        if background:  # a pre-vote is not urgent: do not hold the learning thread for N-1 round trips
+            getattr(proto, "broadcast_async", proto.broadcast)(msg)
+        else:
+            proto.broadcast(msg)
 
     @staticmethod
     def _aggregate_votes(ctx: LearningContext) -> List[str]:

@@ -32,7 +32,11 @@ def evaluate_and_share(ctx: Any) -> None:
     st = ctx.state
     if st.learner is None:
         return
+    import time as _t
+
     logger.debug(st.addr, "evaluating")
+    t0 = _t.time()
     results = st.learner.evaluate()
+    ctx.timings["evaluate_learner"] = ctx.timings.get("evaluate_learner", 0.0) + _t.time() - t0
     logger.debug(st.addr, f"evaluated: {results}")
     broadcast_metrics(ctx.communication_protocol, st, results)
