@@ -127,7 +127,8 @@ class Aggregator:
                     return []
             now_held = self.get_aggregated_models()
         if accepted:
-            logger.debug(self.node_name, f"model added ({len(now_held)}/{len(self._train_set)}) from {contributors}")
+            if logger.is_debug():
+                logger.debug(self.node_name, f"model added ({len(now_held)}/{len(self._train_set)}) from {contributors}")
             for fn in self._listeners:
                 try:
                     fn()

@@ -60,7 +60,9 @@ class TrainStage(Stage):
             # every trainer that ran the exchange to completion holds the aggregate by
             # construction: GossipModelStage need not wait for their `models_ready`
             st.fused_complete_round = st.round if fused.complete else None
-            getattr(proto, "broadcast_async", proto.broadcast)(proto.build_msg("models_aggregated", held, round=st.round))
+            if not fused.complete:
+                # only an incomplete exchange leaves somebody who may need to know what we hold
+                getattr(proto, "broadcast_async", proto.broadcast)(proto.build_msg("models_aggregated", held, round=st.round))
         else:
             held = agg.add_model(st.learner.export_model(), [st.addr], st.learner.get_num_samples()[0])
             proto.broadcast(proto.build_msg("models_aggregated", held, round=st.round))
