@@ -71,6 +71,13 @@ class Settings:
     """``sys.setswitchinterval`` applied when a node starts.  The learning thread shares the
     interpreter with the RPC workers, the gossiper and the heartbeater; with CPython's default
     5 ms a thread returning from a CUDA wait can sit that long before it runs again."""
+    OWN_MODEL_PUSH: str = "auto"
+    """Exchange policy among trainers when the fused kernel is not used.  "never": the
+    reference's policy - send each peer the aggregate of everything it still lacks (partial
+    aggregates; fewer messages on sparse overlays, but overlapping partials get rejected and
+    re-sent).  "always": every trainer sends only its own model to every train-set peer, which
+    can never overlap: exactly |T|(|T|-1) transfers (SURVEY Appendix C, rule 1).  "auto": own
+    model on device data planes (any-to-any over NVLink is free), partial aggregates otherwise."""
     PREVOTE: bool = True
     """Cast the ballot for round r+1 while round r trains (ballots are random and
     ``vote_train_set`` already accepts round+1), so the vote is no barrier between rounds."""

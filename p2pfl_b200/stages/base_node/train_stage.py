@@ -103,11 +103,17 @@ class TrainStage(Stage):
     def _gossip_partial_aggregates(ctx: LearningContext) -> None:
         st, proto, agg = ctx.state, ctx.communication_protocol, ctx.aggregator
 
+        from p2pfl_b200.settings import Settings
+
+        own_only = Settings.OWN_MODEL_PUSH == "always" or (
+            Settings.OWN_MODEL_PUSH == "auto" and getattr(proto, "device_payloads", False)
+        )
+
         def has(n: str) -> List[str]:
             return st.models_aggregated.get(n, [])
 
         def candidates() -> List[str]:
-            mine = set(agg.get_aggregated_models())
+            mine = {st.addr} if own_only else set(agg.get_aggregated_models())
             known = proto.get_neighbors(only_direct=False)
             return [n for n in st.train_set if n != st.addr and n in known and (mine - set(has(n)))]
 
@@ -119,7 +125,12 @@ class TrainStage(Stage):
         def model_fn(n: str) -> Any:
             if st.learner is None or st.round is None:
                 return None
-            model, contributors, weight = agg.get_partial_aggregation(has(n))
+            if own_only:
+                # everything but my own entry is "already there" from this sender's point of view
+                others = [c for c in agg.get_aggregated_models() if c != st.addr]
+                model, contributors, weight = agg.get_partial_aggregation(others + has(n))
+            else:
+                model, contributors, weight = agg.get_partial_aggregation(has(n))
             if model is None:
                 return None
             key = tuple(sorted(contributors))

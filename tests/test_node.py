@@ -231,3 +231,17 @@ def test_aggregator_admission_rules():
     agg.set_nodes_to_aggregate(["a", "b"])
     agg.add_model(m(4), ["a"], 1)
     assert float(agg.wait_and_get_aggregation(timeout=0.05)["w"]) == 4.0
+
+
+def test_own_model_push_policy():
+    """Every trainer sends only its own model: no overlapping partial aggregates, same result."""
+    Settings.OWN_MODEL_PUSH = "always"
+    Settings.TRAIN_SET_SIZE = 4
+    nodes = _line(4, InMemoryCommunicationProtocol)
+    try:
+        nodes[0].set_start_learning(rounds=2, epochs=1)
+        wait_4_results(nodes, 120)
+        check_equal_models(nodes, atol=1e-6)
+    finally:
+        Settings.OWN_MODEL_PUSH = "auto"
+        _stop(nodes)
