@@ -57,7 +57,7 @@ im2col_kernel(const __nv_bfloat16* __restrict__ x, int B, int H, int W, int C, i
 // Gather form: one thread per input element, no atomics.
 __global__ void __launch_bounds__(kThreads)
 col2im_kernel(const __nv_bfloat16* __restrict__ dcol, int ld_col, int B, int H, int W, int C, int kh, int kw, int stride,
-              int pad, int Ho, int Wo, __nv_bfloat16* __restrict__ dx) {
+              int pad, int Ho, int Wo, __nv_bfloat16* __restrict__ dx, const __nv_bfloat16* __restrict__ extra) {
   const int64_t total = (int64_t)B * H * W * C;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(idx % C);
@@ -79,6 +79,7 @@ col2im_kernel(const __nv_bfloat16* __restrict__ dcol, int ld_col, int B, int H, 
         acc += __bfloat162float(dcol[pix * ld_col + c * kh * kw + i * kw + j]);
       }
     }
+    if (extra) acc += __bfloat162float(extra[idx]);  // e.g. the residual branch's gradient
     dx[idx] = __float2bfloat16_rn(acc);
   }
 }
@@ -178,94 +179,161 @@ nchw_to_nhwc_kernel(const float* __restrict__ x, int B, int C, int H, int W, __n
 }
 
 // ---------------------------------------------------------------- BatchNorm
-// Training-mode BatchNorm2d over NHWC: one block per channel reduces mean / biased
-// variance over the B*H*W pixels, updates the running statistics, normalises.
-__device__ __forceinline__ float block_sum(float v, float* sh) {
-  v = warp_sum(v);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (lane == 0) sh[warp] = v;
-  __syncthreads();
-  float t = 0.f;
-  if (warp == 0) {
-    t = lane < (blockDim.x >> 5) ? sh[lane] : 0.f;
-    t = warp_sum(t);
-    if (lane == 0) sh[0] = t;
-  }
-  __syncthreads();
-  t = sh[0];
-  __syncthreads();
-  return t;
-}
-
+// Training-mode BatchNorm2d over NHWC [pixels, C].  Every pass reads rows of C contiguous
+// channels (coalesced): (1) per-channel sum / sum of squares with register partials and one
+// atomic per channel per block, (2) a C-thread finalize (mean, rstd, running statistics),
+// (3) an elementwise apply (+ residual, + ReLU).  Backward mirrors it: (1) per-channel
+// sum(dy) and sum(dy * xhat) straight into dbeta / dgamma, (2) a tiled apply that writes dx
+// in both orientations (the conv weight-gradient GEMM wants [C, pixels]).
 __global__ void __launch_bounds__(kThreads)
-bn_fwd_kernel(const __nv_bfloat16* __restrict__ x, int64_t pixels, int C, const float* __restrict__ gamma,
-              const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
-              float momentum, float eps, int relu, const __nv_bfloat16* __restrict__ residual,
-              __nv_bfloat16* __restrict__ y, float* __restrict__ save_mean, float* __restrict__ save_rstd) {
-  __shared__ float sh[32];
-  for (int c = blockIdx.x; c < C; c += gridDim.x) {
-    float s = 0.f, ss = 0.f;
-    for (int64_t p = threadIdx.x; p < pixels; p += blockDim.x) {
-      const float v = __bfloat162float(x[p * C + c]);
-      s += v;
-      ss += v * v;
-    }
-    s = block_sum(s, sh);
-    ss = block_sum(ss, sh);
-    const float mean = s / (float)pixels;
-    const float var = fmaxf(ss / (float)pixels - mean * mean, 0.f);
-    const float rstd = rsqrtf(var + eps);
-    if (threadIdx.x == 0) {
-      save_mean[c] = mean;
-      save_rstd[c] = rstd;
-      if (running_mean) {
-        const float unbiased = pixels > 1 ? var * (float)pixels / (float)(pixels - 1) : var;
-        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int64_t pixels, int C, float* __restrict__ sum,
+                float* __restrict__ sumsq) {
+  __shared__ float sh_s[kThreads], sh_q[kThreads];
+  const int cpb = C < kThreads ? C : kThreads;  // channels per block pass
+  const int rpp = kThreads / cpb;               // pixel rows per pass
+  const int tx = threadIdx.x % cpb, ty = threadIdx.x / cpb;
+  for (int cc = 0; cc < C; cc += cpb) {
+    const int c = cc + tx;
+    float s = 0.f, q = 0.f;
+    if (c < C && ty < rpp) {
+      for (int64_t p = (int64_t)blockIdx.x * rpp + ty; p < pixels; p += (int64_t)gridDim.x * rpp) {
+        const float v = __bfloat162float(x[p * C + c]);
+        s += v;
+        q += v * v;
       }
     }
-    const float g = gamma[c], bt = beta[c];
-    for (int64_t p = threadIdx.x; p < pixels; p += blockDim.x) {
-      float v = (__bfloat162float(x[p * C + c]) - mean) * rstd * g + bt;
-      if (residual) v += __bfloat162float(residual[p * C + c]);
-      if (relu) v = fmaxf(v, 0.f);
-      y[p * C + c] = __float2bfloat16_rn(v);
+    sh_s[threadIdx.x] = s;
+    sh_q[threadIdx.x] = q;
+    __syncthreads();
+    if (ty == 0 && c < C) {
+      for (int r = 1; r < rpp; ++r) {
+        s += sh_s[r * cpb + tx];
+        q += sh_q[r * cpb + tx];
+      }
+      atomicAdd(sum + c, s);
+      atomicAdd(sumsq + c, q);
     }
+    __syncthreads();
   }
 }
 
-// Backward of y = [relu]( bn(x) [+ residual] ):  dy is masked by (y > 0) when relu,
-// passed through to d_residual, and pushed through the normalisation.
+// sum / sumsq (in save_mean / save_rstd) -> mean / rstd in place, running statistics updated
+__global__ void bn_finalize_kernel(float* __restrict__ save_mean, float* __restrict__ save_rstd, int64_t pixels, int C,
+                                   float* __restrict__ running_mean, float* __restrict__ running_var, float momentum,
+                                   float eps) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float mean = save_mean[c] / (float)pixels;
+  const float var = fmaxf(save_rstd[c] / (float)pixels - mean * mean, 0.f);
+  save_mean[c] = mean;
+  save_rstd[c] = rsqrtf(var + eps);
+  if (running_mean) {
+    const float unbiased = pixels > 1 ? var * (float)pixels / (float)(pixels - 1) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+  }
+}
+
+// y = [relu]( (x - mean) * rstd * gamma + beta [+ residual] ); also used for inference with
+// mean = running_mean, rstd computed from running_var by the caller-side kernel below
 __global__ void __launch_bounds__(kThreads)
-bn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy,
-              int64_t pixels, int C, const float* __restrict__ gamma, const float* __restrict__ save_mean,
-              const float* __restrict__ save_rstd, int relu, __nv_bfloat16* __restrict__ dx,
-              __nv_bfloat16* __restrict__ d_residual, float* __restrict__ dgamma, float* __restrict__ dbeta) {
-  __shared__ float sh[32];
-  for (int c = blockIdx.x; c < C; c += gridDim.x) {
-    const float mean = save_mean[c], rstd = save_rstd[c], g = gamma[c];
-    float sdy = 0.f, sdyx = 0.f;
-    for (int64_t p = threadIdx.x; p < pixels; p += blockDim.x) {
-      float d = __bfloat162float(dy[p * C + c]);
-      if (relu && !(__bfloat162float(y[p * C + c]) > 0.f)) d = 0.f;
-      const float xh = (__bfloat162float(x[p * C + c]) - mean) * rstd;
-      sdy += d;
-      sdyx += d * xh;
+bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int64_t total, int C, const float* __restrict__ gamma,
+                const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ rstd_or_var,
+                float eps, int var_given, int relu, const __nv_bfloat16* __restrict__ residual,
+                __nv_bfloat16* __restrict__ y) {
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % C);
+    const float rstd = var_given ? rsqrtf(rstd_or_var[c] + eps) : rstd_or_var[c];
+    float v = (__bfloat162float(x[idx]) - mean[c]) * rstd * gamma[c] + beta[c];
+    if (residual) v += __bfloat162float(residual[idx]);
+    if (relu) v = fmaxf(v, 0.f);
+    y[idx] = __float2bfloat16_rn(v);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
+                     const __nv_bfloat16* __restrict__ dy, int64_t pixels, int C, const float* __restrict__ save_mean,
+                     const float* __restrict__ save_rstd, int relu, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  __shared__ float sh_s[kThreads], sh_q[kThreads];
+  const int cpb = C < kThreads ? C : kThreads;
+  const int rpp = kThreads / cpb;
+  const int tx = threadIdx.x % cpb, ty = threadIdx.x / cpb;
+  for (int cc = 0; cc < C; cc += cpb) {
+    const int c = cc + tx;
+    float s = 0.f, q = 0.f;
+    if (c < C && ty < rpp) {
+      const float mean = save_mean[c], rstd = save_rstd[c];
+      for (int64_t p = (int64_t)blockIdx.x * rpp + ty; p < pixels; p += (int64_t)gridDim.x * rpp) {
+        float d = __bfloat162float(dy[p * C + c]);
+        if (relu && !(__bfloat162float(y[p * C + c]) > 0.f)) d = 0.f;
+        s += d;
+        q += d * (__bfloat162float(x[p * C + c]) - mean) * rstd;
+      }
     }
-    sdy = block_sum(sdy, sh);
-    sdyx = block_sum(sdyx, sh);
-    if (threadIdx.x == 0) {
-      dgamma[c] = sdyx;
-      dbeta[c] = sdy;
+    sh_s[threadIdx.x] = s;
+    sh_q[threadIdx.x] = q;
+    __syncthreads();
+    if (ty == 0 && c < C) {
+      for (int r = 1; r < rpp; ++r) {
+        s += sh_s[r * cpb + tx];
+        q += sh_q[r * cpb + tx];
+      }
+      atomicAdd(dbeta + c, s);
+      atomicAdd(dgamma + c, q);
     }
-    const float inv_n = 1.f / (float)pixels;
-    for (int64_t p = threadIdx.x; p < pixels; p += blockDim.x) {
-      float d = __bfloat162float(dy[p * C + c]);
-      if (relu && !(__bfloat162float(y[p * C + c]) > 0.f)) d = 0.f;
-      if (d_residual) d_residual[p * C + c] = __float2bfloat16_rn(d);
-      const float xh = (__bfloat162float(x[p * C + c]) - mean) * rstd;
-      dx[p * C + c] = __float2bfloat16_rn(g * rstd * (d - sdy * inv_n - xh * sdyx * inv_n));
+    __syncthreads();
+  }
+}
+
+// 32 pixels x 32 channels per block (32 x 8 threads): dx row-major, and dx_t through a smem transpose
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
+                    const __nv_bfloat16* __restrict__ dy, int64_t pixels, int C, const float* __restrict__ gamma,
+                    const float* __restrict__ save_mean, const float* __restrict__ save_rstd, int relu,
+                    const float* __restrict__ dgamma, const float* __restrict__ dbeta, __nv_bfloat16* __restrict__ dx,
+                    __nv_bfloat16* __restrict__ dx_t, int64_t ld_t, __nv_bfloat16* __restrict__ d_residual) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int tiles_c = (C + 31) / 32;
+  const int64_t tiles_p = (pixels + 31) / 32;
+  const float inv_n = 1.f / (float)pixels;
+  for (int64_t t = blockIdx.x; t < tiles_p * tiles_c; t += gridDim.x) {
+    const int64_t p0 = (t / tiles_c) * 32;
+    const int c = (int)(t % tiles_c) * 32 + tx;
+    float g = 0.f, mean = 0.f, rstd = 0.f, sdy = 0.f, sdyx = 0.f;
+    if (c < C) {
+      g = gamma[c];
+      mean = save_mean[c];
+      rstd = save_rstd[c];
+      sdy = dbeta[c];
+      sdyx = dgamma[c];
     }
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+      const int64_t p = p0 + ty + j;
+      float out = 0.f;
+      if (p < pixels && c < C) {
+        const int64_t idx = p * C + c;
+        float d = __bfloat162float(dy[idx]);
+        if (relu && !(__bfloat162float(y[idx]) > 0.f)) d = 0.f;
+        if (d_residual) d_residual[idx] = __float2bfloat16_rn(d);
+        const float xh = (__bfloat162float(x[idx]) - mean) * rstd;
+        out = g * rstd * (d - sdy * inv_n - xh * sdyx * inv_n);
+        dx[idx] = __float2bfloat16_rn(out);
+      }
+      tile[ty + j][tx] = out;
+    }
+    if (dx_t) {
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        const int cc = (int)(t % tiles_c) * 32 + ty + j;
+        const int64_t p = p0 + tx;
+        if (cc < C && p < pixels) dx_t[(int64_t)cc * ld_t + p] = __float2bfloat16_rn(tile[tx][ty + j]);
+      }
+    }
+    __syncthreads();
   }
 }
 
@@ -317,11 +385,17 @@ int p2pfl_im2col(int device, void* stream, const void* x_nhwc, int B, int H, int
 
 int p2pfl_col2im(int device, void* stream, const void* dcol, int ld_col, int B, int H, int W, int C, int kh, int kw,
                  int stride, int pad, void* dx_nhwc) {
+  return p2pfl_col2im_add(device, stream, dcol, ld_col, B, H, W, C, kh, kw, stride, pad, dx_nhwc, nullptr);
+}
+
+int p2pfl_col2im_add(int device, void* stream, const void* dcol, int ld_col, int B, int H, int W, int C, int kh, int kw,
+                     int stride, int pad, void* dx_nhwc, const void* extra) {
   P2PFL_REQUIRE(dcol && dx_nhwc, "bad arguments to p2pfl_col2im");
   const int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
   P2PFL_CUDA_OK(cudaSetDevice(device));
   col2im_kernel<<<grid_for((int64_t)B * H * W * C, device), kThreads, 0, as_stream(stream)>>>(
-      (const __nv_bfloat16*)dcol, ld_col, B, H, W, C, kh, kw, stride, pad, Ho, Wo, (__nv_bfloat16*)dx_nhwc);
+      (const __nv_bfloat16*)dcol, ld_col, B, H, W, C, kh, kw, stride, pad, Ho, Wo, (__nv_bfloat16*)dx_nhwc,
+      (const __nv_bfloat16*)extra);
   P2PFL_LAUNCH_OK();
   return 0;
 }
@@ -372,9 +446,32 @@ int p2pfl_bn_fwd(int device, void* stream, const void* x_nhwc, int64_t pixels, i
                  const void* residual, void* y, float* save_mean, float* save_rstd) {
   P2PFL_REQUIRE(x_nhwc && y && gamma && beta && save_mean && save_rstd && pixels > 0 && C > 0, "bad arguments to p2pfl_bn_fwd");
   P2PFL_CUDA_OK(cudaSetDevice(device));
-  bn_fwd_kernel<<<C, kThreads, 0, as_stream(stream)>>>((const __nv_bfloat16*)x_nhwc, pixels, C, gamma, beta, running_mean,
-                                                        running_var, momentum, eps, relu, (const __nv_bfloat16*)residual,
-                                                        (__nv_bfloat16*)y, save_mean, save_rstd);
+  cudaStream_t s = as_stream(stream);
+  P2PFL_CUDA_OK(cudaMemsetAsync(save_mean, 0, sizeof(float) * C, s));
+  P2PFL_CUDA_OK(cudaMemsetAsync(save_rstd, 0, sizeof(float) * C, s));
+  const int rpp = kThreads / (C < kThreads ? C : kThreads);
+  int64_t blocks = (pixels + rpp - 1) / rpp / 8 + 1;
+  const int64_t cap = (int64_t)sm_count(device) * 4;
+  bn_stats_kernel<<<(int)(blocks < cap ? blocks : cap), kThreads, 0, s>>>((const __nv_bfloat16*)x_nhwc, pixels, C, save_mean,
+                                                                           save_rstd);
+  P2PFL_LAUNCH_OK();
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, s>>>(save_mean, save_rstd, pixels, C, running_mean, running_var, momentum, eps);
+  P2PFL_LAUNCH_OK();
+  bn_apply_kernel<<<grid_for(pixels * C, device), kThreads, 0, s>>>((const __nv_bfloat16*)x_nhwc, pixels * C, C, gamma, beta,
+                                                                     save_mean, save_rstd, eps, 0, relu,
+                                                                     (const __nv_bfloat16*)residual, (__nv_bfloat16*)y);
+  P2PFL_LAUNCH_OK();
+  return 0;
+}
+
+int p2pfl_bn_infer(int device, void* stream, const void* x_nhwc, int64_t pixels, int C, const float* gamma,
+                   const float* beta, const float* running_mean, const float* running_var, float eps, int relu,
+                   const void* residual, void* y) {
+  P2PFL_REQUIRE(x_nhwc && y && gamma && beta && running_mean && running_var, "bad arguments to p2pfl_bn_infer");
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  bn_apply_kernel<<<grid_for(pixels * C, device), kThreads, 0, as_stream(stream)>>>(
+      (const __nv_bfloat16*)x_nhwc, pixels * C, C, gamma, beta, running_mean, running_var, eps, 1, relu,
+      (const __nv_bfloat16*)residual, (__nv_bfloat16*)y);
   P2PFL_LAUNCH_OK();
   return 0;
 }
@@ -382,12 +479,31 @@ int p2pfl_bn_fwd(int device, void* stream, const void* x_nhwc, int64_t pixels, i
 int p2pfl_bn_bwd(int device, void* stream, const void* x_nhwc, const void* y, const void* dy, int64_t pixels, int C,
                  const float* gamma, const float* save_mean, const float* save_rstd, int relu, void* dx,
                  void* d_residual, float* dgamma, float* dbeta) {
+  return p2pfl_bn_bwd_t(device, stream, x_nhwc, y, dy, pixels, C, gamma, save_mean, save_rstd, relu, dx, nullptr, 0,
+                        d_residual, dgamma, dbeta);
+}
+
+int p2pfl_bn_bwd_t(int device, void* stream, const void* x_nhwc, const void* y, const void* dy, int64_t pixels, int C,
+                   const float* gamma, const float* save_mean, const float* save_rstd, int relu, void* dx, void* dx_t,
+                   int64_t ld_t, void* d_residual, float* dgamma, float* dbeta) {
   P2PFL_REQUIRE(x_nhwc && dy && dx && gamma && save_mean && save_rstd && dgamma && dbeta, "bad arguments to p2pfl_bn_bwd");
   P2PFL_REQUIRE(!relu || y, "bn_bwd with relu needs the forward output");
   P2PFL_CUDA_OK(cudaSetDevice(device));
-  bn_bwd_kernel<<<C, kThreads, 0, as_stream(stream)>>>((const __nv_bfloat16*)x_nhwc, (const __nv_bfloat16*)y,
-                                                        (const __nv_bfloat16*)dy, pixels, C, gamma, save_mean, save_rstd,
-                                                        relu, (__nv_bfloat16*)dx, (__nv_bfloat16*)d_residual, dgamma, dbeta);
+  cudaStream_t s = as_stream(stream);
+  P2PFL_CUDA_OK(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, s));
+  P2PFL_CUDA_OK(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, s));
+  const int rpp = kThreads / (C < kThreads ? C : kThreads);
+  int64_t blocks = (pixels + rpp - 1) / rpp / 8 + 1;
+  const int64_t cap = (int64_t)sm_count(device) * 4;
+  bn_bwd_reduce_kernel<<<(int)(blocks < cap ? blocks : cap), kThreads, 0, s>>>(
+      (const __nv_bfloat16*)x_nhwc, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, pixels, C, save_mean, save_rstd, relu,
+      dgamma, dbeta);
+  P2PFL_LAUNCH_OK();
+  const int64_t tiles = ((pixels + 31) / 32) * ((C + 31) / 32);
+  const int64_t cap2 = (int64_t)sm_count(device) * 8;
+  bn_bwd_apply_kernel<<<(int)(tiles < cap2 ? tiles : cap2), 256, 0, s>>>(
+      (const __nv_bfloat16*)x_nhwc, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, pixels, C, gamma, save_mean, save_rstd,
+      relu, dgamma, dbeta, (__nv_bfloat16*)dx, (__nv_bfloat16*)dx_t, ld_t, (__nv_bfloat16*)d_residual);
   P2PFL_LAUNCH_OK();
   return 0;
 }

@@ -258,6 +258,18 @@ int p2pfl_bn_bwd(int device, void* stream, const void* x_nhwc, const void* y, co
                  int64_t pixels, int C, const float* gamma, const float* save_mean,
                  const float* save_rstd, int relu, void* dx, void* d_residual /* nullable */,
                  float* dgamma, float* dbeta);
+/* same, additionally writing dx transposed ([C, ld_t]) for the conv weight-gradient GEMM */
+int p2pfl_bn_bwd_t(int device, void* stream, const void* x_nhwc, const void* y, const void* dy,
+                   int64_t pixels, int C, const float* gamma, const float* save_mean,
+                   const float* save_rstd, int relu, void* dx, void* dx_t /* nullable */, int64_t ld_t,
+                   void* d_residual /* nullable */, float* dgamma, float* dbeta);
+/* inference-mode BatchNorm (running statistics) (+ residual, + ReLU) */
+int p2pfl_bn_infer(int device, void* stream, const void* x_nhwc, int64_t pixels, int C,
+                   const float* gamma, const float* beta, const float* running_mean,
+                   const float* running_var, float eps, int relu, const void* residual, void* y);
+/* col2im that also adds `extra` (same shape as dx; e.g. the gradient of a residual branch) */
+int p2pfl_col2im_add(int device, void* stream, const void* dcol, int ld_col, int B, int H, int W,
+                     int C, int kh, int kw, int stride, int pad, void* dx_nhwc, const void* extra);
 /* global average pool over HW: [B, HW, C] -> [B, C] (+ transpose), and its backward */
 int p2pfl_avgpool_fwd(int device, void* stream, const void* x_nhwc, int B, int HW, int C, void* y,
                       void* y_t /* nullable */, int ld_t);

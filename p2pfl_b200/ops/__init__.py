@@ -376,11 +376,12 @@ def im2col(x, B: int, H: int, W: int, Cc: int, kh: int, kw: int, stride: int, pa
     _count()
 
 
-def col2im(dcol, ld_col: int, B: int, H: int, W: int, Cc: int, kh: int, kw: int, stride: int, pad: int, dx) -> None:
+def col2im(dcol, ld_col: int, B: int, H: int, W: int, Cc: int, kh: int, kw: int, stride: int, pad: int, dx, extra=None) -> None:
+    """dx = col2im(dcol) (+ extra, e.g. the gradient arriving through a residual branch)."""
     _check(
-        lib().p2pfl_col2im(
+        lib().p2pfl_col2im_add(
             _dev(dcol), _stream(), _p(dcol), C.c_int(ld_col), C.c_int(B), C.c_int(H), C.c_int(W), C.c_int(Cc),
-            C.c_int(kh), C.c_int(kw), C.c_int(stride), C.c_int(pad), _p(dx),
+            C.c_int(kh), C.c_int(kw), C.c_int(stride), C.c_int(pad), _p(dx), _p(extra),
         )
     )  # fmt: skip
     _count()
@@ -422,14 +423,24 @@ def bn_fwd(x, pixels: int, Cc: int, gamma, beta, running_mean, running_var, mome
             C.c_float(momentum), C.c_float(eps), C.c_int(int(relu)), _p(residual), _p(y), _p(save_mean), _p(save_rstd),
         )
     )  # fmt: skip
-    _count()
+    _count(3)
 
 
-def bn_bwd(x, y, dy, pixels: int, Cc: int, gamma, save_mean, save_rstd, relu: bool, dx, d_residual, dgamma, dbeta) -> None:
+def bn_bwd(x, y, dy, pixels: int, Cc: int, gamma, save_mean, save_rstd, relu: bool, dx, d_residual, dgamma, dbeta, dx_t=None, ld_t: int = 0) -> None:
     _check(
-        lib().p2pfl_bn_bwd(
+        lib().p2pfl_bn_bwd_t(
             _dev(x), _stream(), _p(x), _p(y), _p(dy), C.c_int64(pixels), C.c_int(Cc), _p(gamma), _p(save_mean), _p(save_rstd),
-            C.c_int(int(relu)), _p(dx), _p(d_residual), _p(dgamma), _p(dbeta),
+            C.c_int(int(relu)), _p(dx), _p(dx_t), C.c_int64(ld_t), _p(d_residual), _p(dgamma), _p(dbeta),
+        )
+    )  # fmt: skip
+    _count(2)
+
+
+def bn_infer(x, pixels: int, Cc: int, gamma, beta, running_mean, running_var, eps: float, relu: bool, residual, y) -> None:
+    _check(
+        lib().p2pfl_bn_infer(
+            _dev(x), _stream(), _p(x), C.c_int64(pixels), C.c_int(Cc), _p(gamma), _p(beta), _p(running_mean), _p(running_var),
+            C.c_float(eps), C.c_int(int(relu)), _p(residual), _p(y),
         )
     )  # fmt: skip
     _count()

@@ -136,7 +136,9 @@ def test_batchnorm_fwd_bwd(ops, relu, res):
     dx = torch.zeros_like(y)
     dres = torch.zeros_like(y) if res else None
     dg, dbt = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
-    ops.bn_bwd(_nhwc(x), y, _nhwc(dy), pixels, C, bn.weight.detach(), sm, sr, relu, dx, dres, dg, dbt)
+    dxT = torch.zeros(C, pixels, device=DEV, dtype=torch.bfloat16)
+    ops.bn_bwd(_nhwc(x), y, _nhwc(dy), pixels, C, bn.weight.detach(), sm, sr, relu, dx, dres, dg, dbt, dxT, pixels)
+    assert torch.equal(dxT, dx.view(pixels, C).t())
     # the ReLU mask is taken from the bf16 output: elements within rounding of zero may flip
     rel = (dx.float().permute(0, 3, 1, 2) - xr.grad).norm() / xr.grad.norm()
     assert rel < 5e-2, float(rel)
@@ -144,6 +146,33 @@ def test_batchnorm_fwd_bwd(ops, relu, res):
     assert (dbt - bn.bias.grad).norm() / bn.bias.grad.norm() < 5e-2
     if res:
         assert (dres.float().permute(0, 3, 1, 2) - rr.grad).norm() / rr.grad.norm() < 5e-2
+
+
+def test_batchnorm_inference(ops):
+    B, C, H = 4, 40, 5
+    x = torch.randn(B, C, H, H, device=DEV).to(torch.bfloat16).float()
+    bn = torch.nn.BatchNorm2d(C).to(DEV).eval()
+    with torch.no_grad():
+        bn.running_mean.uniform_(-1, 1)
+        bn.running_var.uniform_(0.5, 2)
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.5, 0.5)
+        ref = F.relu(bn(x))
+    y = torch.zeros(B, H, H, C, device=DEV, dtype=torch.bfloat16)
+    ops.bn_infer(_nhwc(x), B * H * H, C, bn.weight.detach(), bn.bias.detach(), bn.running_mean, bn.running_var, 1e-5, True, None, y)
+    assert torch.allclose(y.float().permute(0, 3, 1, 2), ref, atol=3e-2, rtol=3e-2)
+
+
+def test_col2im_adds_the_residual_gradient(ops):
+    B, C, H, k = 2, 8, 6, 3
+    K = C * k * k
+    dcol = torch.randn(B * H * H, K, device=DEV).to(torch.bfloat16)
+    extra = torch.randn(B, H, H, C, device=DEV).to(torch.bfloat16)
+    a = torch.zeros(B, H, H, C, device=DEV, dtype=torch.bfloat16)
+    b = torch.zeros_like(a)
+    ops.col2im(dcol, K, B, H, H, C, k, k, 1, 1, a)
+    ops.col2im(dcol, K, B, H, H, C, k, k, 1, 1, b, extra)
+    assert torch.allclose(b.float(), a.float() + extra.float(), atol=3e-2, rtol=2e-2)
 
 
 def test_global_avgpool(ops):
