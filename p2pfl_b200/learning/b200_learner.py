@@ -123,6 +123,16 @@ class B200Learner(TorchLearner):
                 self._tdescs, self.wT16 = plan.tdescs, plan.wT16
                 self.fused = True
             return
+        if getattr(self.model, "fused_spec", None) == "resnet18":
+            from p2pfl_b200.learning.b200_resnet import ResNetPlan
+
+            plan = ResNetPlan(self)
+            if plan.ok:
+                self.cnn = plan  # same plan interface as the CNN (alloc / forward_eval / train_step / refresh)
+                self._feat, self._ncls = plan.feat, plan.ncls
+                self._tdescs, self.wT16 = plan.tdescs, plan.wT16
+                self.fused = True
+            return
         if getattr(self.model, "fused_spec", None) != "mlp":
             return
         linears = [(n, m) for n, m in self.model.named_children() if isinstance(m, nn.Linear)]
@@ -235,17 +245,23 @@ class B200Learner(TorchLearner):
     # ------------------------------------------------------------------ data
     def _upload(self, split: str) -> Tuple[torch.Tensor, torch.Tensor]:
         x, y = self.data.pinned_tensors(split) if hasattr(self.data, "pinned_tensors") else self.data.tensors(split)
-        xd = x.reshape(x.shape[0], -1).to(self.device, non_blocking=True)
+        xd = self._rows(x.to(self.device, non_blocking=True))
         yd = y.to(self.device, non_blocking=True).to(torch.int32)  # int64 travels, the cast is on the device
         self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
         return xd, yd
+
+    def _rows(self, x_dev: torch.Tensor) -> torch.Tensor:
+        """[n, ...] device tensor -> [n, feat] rows; channels-last for plans that consume NHWC."""
+        if x_dev.dim() == 4 and x_dev.shape[1] > 1 and getattr(self.cnn, "nhwc_input", False):
+            x_dev = x_dev.permute(0, 2, 3, 1)
+        return x_dev.reshape(x_dev.shape[0], -1).contiguous()
 
     def _train_data(self) -> Tuple[torch.Tensor, torch.Tensor]:
         if self.data_mode == "stream" or self._train_dev is None:
             if self._train_dev is not None and self.data_mode == "stream":
                 # same device buffers every round so captured graphs stay valid
                 x, y = self.data.pinned_tensors("train")
-                self._train_dev[0].copy_(x.reshape(x.shape[0], -1), non_blocking=True)
+                self._train_dev[0].copy_(self._rows(x.to(self.device, non_blocking=True)))
                 self._train_dev[1].copy_(y.to(self.device, non_blocking=True))
                 self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
             else:
@@ -258,7 +274,7 @@ class B200Learner(TorchLearner):
             self._eval_dev[split] = cur = self._upload(split)
         elif self.data_mode == "stream":
             x, y = self.data.pinned_tensors(split)
-            cur[0].copy_(x.reshape(x.shape[0], -1), non_blocking=True)
+            cur[0].copy_(self._rows(x.to(self.device, non_blocking=True)))
             cur[1].copy_(y.to(self.device, non_blocking=True))
             self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
         return cur
@@ -388,7 +404,7 @@ class B200Learner(TorchLearner):
         B = x.shape[0]
         feat = self._feat
         with torch.cuda.stream(self._s()):
-            xf = x.reshape(B, -1).to(self.device, torch.float32).contiguous()
+            xf = self._rows(x.to(self.device, torch.float32))
             yi = y.to(self.device).to(torch.int32)
             xs = torch.zeros(B, feat, dtype=torch.bfloat16, device=self.device)
             xsT = torch.zeros(1, feat, _pad8(B), dtype=torch.bfloat16, device=self.device)

@@ -148,12 +148,59 @@ def test_cnn_fused_fit_and_evaluate():
     learner.close()
 
 
+def test_resnet18_fused_step_matches_autograd():
+    """Implicit-GEMM convolutions + fused BatchNorm/residual kernels vs eager fp32 autograd."""
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.learning.data import Cifar10FederatedDM
+    from p2pfl_b200.models import ResNet18
+
+    torch.manual_seed(0)
+    model = ResNet18(seed=0)
+    ref = copy.deepcopy(model).to(DEV).train()
+    dm = Cifar10FederatedDM(0, 1, n_train=160, n_test=64)
+    learner = B200Learner(model, dm, "r", epochs=1, device=DEV)
+    assert learner.fused and learner.cnn is not None
+    x, y = dm.tensors("train")
+    x, y = x[:32], y[:32]
+    loss = learner.debug_single_step(x, y)
+    out = ref(x.to(DEV))
+    ref_loss = F.cross_entropy(out, y.to(DEV))
+    ref_loss.backward()
+    assert abs(loss - float(ref_loss.detach())) < 0.1 * max(1.0, float(ref_loss.detach())), (loss, float(ref_loss))
+    views = learner.layout.views(learner.grads)
+    errs = {n: float((views[n] - p.grad).norm() / (p.grad.norm() + 1e-12)) for n, p in ref.named_parameters()}
+    head = {k: v for k, v in errs.items() if k.startswith(("fc.", "layer4.1"))}
+    assert max(head.values()) < 0.12, head
+    # eighteen bf16 layers deep, the relative error grows towards the input
+    assert max(errs.values()) < 0.6, {k: round(v, 3) for k, v in errs.items() if v > 0.3}
+    # running statistics were updated in the arena
+    rm = learner.layout.views(learner.flat)["bn1.running_mean"]
+    assert torch.allclose(rm, ref.bn1.running_mean, atol=2e-2)
+    learner.close()
+
+
+def test_resnet18_fused_fit_and_evaluate():
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.learning.data import Cifar10FederatedDM
+    from p2pfl_b200.models import ResNet18
+
+    dm = Cifar10FederatedDM(0, 1, n_train=720, n_test=300, noise=3.0)
+    learner = B200Learner(ResNet18(seed=1), dm, "r", epochs=2, device=DEV)
+    r0 = learner.evaluate()
+    learner.fit()
+    r1 = learner.evaluate()
+    assert r1["test_loss"] < r0["test_loss"], (r0, r1)
+    assert r1["test_metric"] > 0.5, r1
+    learner.close()
+
+
 def test_non_fused_model_falls_back_to_autograd():
     from p2pfl_b200.learning.b200_learner import B200Learner
-    from p2pfl_b200.models import ResNet18 as CNN
+    from p2pfl_b200.learning.data import TokenFederatedDM
+    from p2pfl_b200.models import gpt2_tiny
 
-    dm = __import__("p2pfl_b200.learning.data", fromlist=["Cifar10FederatedDM"]).Cifar10FederatedDM(0, 1, n_train=160, n_test=64)
-    learner = B200Learner(CNN(seed=0), dm, "c", epochs=1, device=DEV)
+    dm = TokenFederatedDM(0, 1, batch_size=4, seq_len=16, vocab=256, n_train=16, n_test=8)
+    learner = B200Learner(gpt2_tiny(seed=0), dm, "c", epochs=1, device=DEV)
     assert not learner.fused
     r0 = learner.evaluate()
     learner.fit()
