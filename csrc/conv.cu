@@ -48,7 +48,30 @@ im2col_kernel(const __nv_bfloat16* __restrict__ x, int B, int H, int W, int C, i
     __nv_bfloat16 v = __float2bfloat16_rn(0.f);
     if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((int64_t)b * H + h) * W + w) * C + c];
     col[pix * ld_col + k] = v;
-    if (col_t) col_t[(int64_t)k * ld_t + pix] = v;
+  }
+}
+
+// The transpose col_t[k, pix] is produced by its own pass with pix as the fastest index, so
+// that the (much larger) writes are coalesced; the scattered side is the cached reads of x.
+__global__ void __launch_bounds__(kThreads)
+im2col_t_kernel(const __nv_bfloat16* __restrict__ x, int B, int H, int W, int C, int kh, int kw, int stride, int pad,
+                int Ho, int Wo, __nv_bfloat16* __restrict__ col_t, int64_t ld_t) {
+  const int K = C * kh * kw;
+  const int64_t npix = (int64_t)B * Ho * Wo;
+  const int64_t total = npix * K;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t pix = idx % npix;
+    const int k = (int)(idx / npix);
+    const int wo = (int)(pix % Wo);
+    const int ho = (int)((pix / Wo) % Ho);
+    const int b = (int)(pix / ((int64_t)Wo * Ho));
+    const int c = k / (kh * kw);
+    const int ij = k - c * kh * kw;
+    const int i = ij / kw, j = ij - i * kw;
+    const int h = ho * stride + i - pad, w = wo * stride + j - pad;
+    __nv_bfloat16 v = __float2bfloat16_rn(0.f);
+    if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((int64_t)b * H + h) * W + w) * C + c];
+    col_t[(int64_t)k * ld_t + pix] = v;
   }
 }
 
@@ -81,6 +104,114 @@ col2im_kernel(const __nv_bfloat16* __restrict__ dcol, int ld_col, int B, int H, 
     }
     if (extra) acc += __bfloat162float(extra[idx]);  // e.g. the residual branch's gradient
     dx[idx] = __float2bfloat16_rn(acc);
+  }
+}
+
+
+// ----------------------------------------------- tap-major ("kc") conv layout
+// For C % 8 == 0 the K axis of the implicit GEMM is ordered (i, j, c) - tap-major, channel
+// fastest - instead of PyTorch's (c, i, j).  With NHWC activations every (pixel, tap) is then
+// one contiguous run of C channels, so im2col / col2im move 16-byte vectors and the column
+// matrix is written as one dense stream.  The weights are repacked to the same order once per
+// optimizer step (conv_pack_kernel), the weight gradient is unpacked back (conv_unpack_kernel).
+__global__ void __launch_bounds__(kThreads)
+im2col_kc_kernel(const uint4* __restrict__ x, int B, int H, int W, int C8, int kh, int kw, int stride, int pad, int Ho,
+                 int Wo, uint4* __restrict__ col, int ld8) {
+  const int taps = kh * kw;
+  const int64_t total = (int64_t)B * Ho * Wo * taps * C8;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(idx % C8);
+    const int64_t r = idx / C8;
+    const int tap = (int)(r % taps);
+    const int64_t pix = r / taps;
+    const int wo = (int)(pix % Wo);
+    const int ho = (int)((pix / Wo) % Ho);
+    const int b = (int)(pix / ((int64_t)Wo * Ho));
+    const int i = tap / kw, j = tap - i * kw;
+    const int h = ho * stride + i - pad, w = wo * stride + j - pad;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((int64_t)b * H + h) * W + w) * C8 + c8];
+    col[pix * ld8 + (int64_t)tap * C8 + c8] = v;
+  }
+}
+
+__device__ __forceinline__ void acc_bf16x8(float (&a)[8], const uint4& v) {
+  const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    a[2 * k] += __uint_as_float(u[k] << 16);
+    a[2 * k + 1] += __uint_as_float(u[k] & 0xFFFF0000u);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+col2im_kc_kernel(const uint4* __restrict__ dcol, int ld8, int B, int H, int W, int C8, int kh, int kw, int stride, int pad,
+                 int Ho, int Wo, uint4* __restrict__ dx, const uint4* __restrict__ extra) {
+  const int64_t total = (int64_t)B * H * W * C8;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(idx % C8);
+    const int w = (int)((idx / C8) % W);
+    const int h = (int)((idx / ((int64_t)C8 * W)) % H);
+    const int b = (int)(idx / ((int64_t)C8 * W * H));
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int i = 0; i < kh; ++i) {
+      const int hn = h + pad - i;
+      if (hn < 0 || hn % stride) continue;
+      const int ho = hn / stride;
+      if (ho >= Ho) continue;
+      for (int j = 0; j < kw; ++j) {
+        const int wn = w + pad - j;
+        if (wn < 0 || wn % stride) continue;
+        const int wo = wn / stride;
+        if (wo >= Wo) continue;
+        const int64_t pix = ((int64_t)b * Ho + ho) * Wo + wo;
+        acc_bf16x8(acc, dcol[pix * ld8 + (int64_t)(i * kw + j) * C8 + c8]);
+      }
+    }
+    if (extra) acc_bf16x8(acc, extra[idx]);
+    uint4 o;
+    o.x = pack_bf16x2(acc[0], acc[1]);
+    o.y = pack_bf16x2(acc[2], acc[3]);
+    o.z = pack_bf16x2(acc[4], acc[5]);
+    o.w = pack_bf16x2(acc[6], acc[7]);
+    dx[idx] = o;
+  }
+}
+
+// One launch for every convolution of a network; blockIdx.y picks the row of `table`:
+//   {flat offset of the PyTorch weight [cout, cin*taps], offset in the packed buffer [cout, ldk],
+//    cout, cin, taps, ldk, tap_major (1: k = tap*cin + c, 0: k = c*taps + tap), unused}
+constexpr int kConvTableCols = 8;
+__global__ void __launch_bounds__(kThreads)
+conv_pack_kernel(const float* __restrict__ flat, __nv_bfloat16* __restrict__ packed, const int64_t* __restrict__ table) {
+  const int64_t* t = table + (int64_t)blockIdx.y * kConvTableCols;
+  const float* src = flat + t[0];
+  __nv_bfloat16* dst = packed + t[1];
+  const int cout = (int)t[2], cin = (int)t[3], taps = (int)t[4], ldk = (int)t[5], tap_major = (int)t[6];
+  const int K = cin * taps;
+  const int64_t total = (int64_t)cout * K;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int kd = (int)(idx % K);
+    const int co = (int)(idx / K);
+    const int ks = tap_major ? (kd % cin) * taps + kd / cin : kd;
+    dst[(int64_t)co * ldk + kd] = __float2bfloat16_rn(src[(int64_t)co * K + ks]);
+  }
+}
+
+// gradient of the packed weight (fp32 [cout, ldk], what the wgrad GEMM accumulates) -> PyTorch order
+__global__ void __launch_bounds__(kThreads)
+conv_unpack_kernel(const float* __restrict__ packed, float* __restrict__ flat, const int64_t* __restrict__ table) {
+  const int64_t* t = table + (int64_t)blockIdx.y * kConvTableCols;
+  float* dst = flat + t[0];
+  const float* src = packed + t[1];
+  const int cout = (int)t[2], cin = (int)t[3], taps = (int)t[4], ldk = (int)t[5], tap_major = (int)t[6];
+  const int K = cin * taps;
+  const int64_t total = (int64_t)cout * K;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int ks = (int)(idx % K);
+    const int co = (int)(idx / K);
+    const int kd = tap_major ? (ks % taps) * cin + ks / taps : ks;
+    dst[idx] = src[(int64_t)co * ldk + kd];
   }
 }
 
@@ -378,8 +509,13 @@ int p2pfl_im2col(int device, void* stream, const void* x_nhwc, int B, int H, int
   const int64_t total = (int64_t)B * Ho * Wo * C * kh * kw;
   im2col_kernel<<<grid_for(total, device), kThreads, 0, as_stream(stream)>>>(
       (const __nv_bfloat16*)x_nhwc, B, H, W, C, kh, kw, stride, pad, Ho, Wo, (__nv_bfloat16*)col, ld_col,
-      (__nv_bfloat16*)col_t, ld_t);
+      (__nv_bfloat16*)nullptr, ld_t);
   P2PFL_LAUNCH_OK();
+  if (col_t) {
+    im2col_t_kernel<<<grid_for(total, device), kThreads, 0, as_stream(stream)>>>(
+        (const __nv_bfloat16*)x_nhwc, B, H, W, C, kh, kw, stride, pad, Ho, Wo, (__nv_bfloat16*)col_t, ld_t);
+    P2PFL_LAUNCH_OK();
+  }
   return 0;
 }
 
@@ -396,6 +532,56 @@ int p2pfl_col2im_add(int device, void* stream, const void* dcol, int ld_col, int
   col2im_kernel<<<grid_for((int64_t)B * H * W * C, device), kThreads, 0, as_stream(stream)>>>(
       (const __nv_bfloat16*)dcol, ld_col, B, H, W, C, kh, kw, stride, pad, Ho, Wo, (__nv_bfloat16*)dx_nhwc,
       (const __nv_bfloat16*)extra);
+  P2PFL_LAUNCH_OK();
+  return 0;
+}
+
+int p2pfl_im2col_kc(int device, void* stream, const void* x_nhwc, int B, int H, int W, int C, int kh, int kw, int stride,
+                    int pad, void* col, int ld_col) {
+  P2PFL_REQUIRE(x_nhwc && col && C > 0 && (C % 8) == 0 && (ld_col % 8) == 0 && ld_col >= C * kh * kw,
+                "p2pfl_im2col_kc needs C and ld_col to be multiples of 8");
+  P2PFL_REQUIRE(((reinterpret_cast<uintptr_t>(x_nhwc) | reinterpret_cast<uintptr_t>(col)) & 15) == 0,
+                "p2pfl_im2col_kc needs 16-byte aligned buffers");
+  const int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  const int64_t total = (int64_t)B * Ho * Wo * kh * kw * (C / 8);
+  im2col_kc_kernel<<<grid_for(total, device), kThreads, 0, as_stream(stream)>>>(
+      (const uint4*)x_nhwc, B, H, W, C / 8, kh, kw, stride, pad, Ho, Wo, (uint4*)col, ld_col / 8);
+  P2PFL_LAUNCH_OK();
+  return 0;
+}
+
+int p2pfl_col2im_kc(int device, void* stream, const void* dcol, int ld_col, int B, int H, int W, int C, int kh, int kw,
+                    int stride, int pad, void* dx_nhwc, const void* extra) {
+  P2PFL_REQUIRE(dcol && dx_nhwc && C > 0 && (C % 8) == 0 && (ld_col % 8) == 0, "p2pfl_col2im_kc needs C and ld_col to be multiples of 8");
+  P2PFL_REQUIRE(((reinterpret_cast<uintptr_t>(dcol) | reinterpret_cast<uintptr_t>(dx_nhwc) | reinterpret_cast<uintptr_t>(extra)) & 15) == 0,
+                "p2pfl_col2im_kc needs 16-byte aligned buffers");
+  const int Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  col2im_kc_kernel<<<grid_for((int64_t)B * H * W * (C / 8), device), kThreads, 0, as_stream(stream)>>>(
+      (const uint4*)dcol, ld_col / 8, B, H, W, C / 8, kh, kw, stride, pad, Ho, Wo, (uint4*)dx_nhwc, (const uint4*)extra);
+  P2PFL_LAUNCH_OK();
+  return 0;
+}
+
+int p2pfl_conv_pack(int device, void* stream, const float* flat, void* packed_bf16, const int64_t* table_dev, int n_conv,
+                    int64_t max_elems) {
+  P2PFL_REQUIRE(flat && packed_bf16 && table_dev && n_conv > 0 && n_conv <= 65535, "bad arguments to p2pfl_conv_pack");
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  int gx = grid_for(max_elems, device);
+  gx = gx > 64 ? 64 : gx;
+  conv_pack_kernel<<<dim3(gx, n_conv), kThreads, 0, as_stream(stream)>>>(flat, (__nv_bfloat16*)packed_bf16, table_dev);
+  P2PFL_LAUNCH_OK();
+  return 0;
+}
+
+int p2pfl_conv_unpack(int device, void* stream, const float* packed_f32, float* flat, const int64_t* table_dev, int n_conv,
+                      int64_t max_elems) {
+  P2PFL_REQUIRE(flat && packed_f32 && table_dev && n_conv > 0 && n_conv <= 65535, "bad arguments to p2pfl_conv_unpack");
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  int gx = grid_for(max_elems, device);
+  gx = gx > 64 ? 64 : gx;
+  conv_unpack_kernel<<<dim3(gx, n_conv), kThreads, 0, as_stream(stream)>>>(packed_f32, flat, table_dev);
   P2PFL_LAUNCH_OK();
   return 0;
 }

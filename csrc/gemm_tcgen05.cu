@@ -44,6 +44,7 @@ struct Epilogue {
   float alpha;
   int32_t ld_mask, ld_f32, ld_bf16, ld_f32_t, ld_bf16_t;
   int32_t bias_per_row, relu;
+  int32_t atomic;  // split-K: out_f32 is accumulated with red.global.add (caller zero-fills it)
 };
 
 // ------------------------------------------------------------------ PTX glue
@@ -142,9 +143,24 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
   return d;
 }
 
-// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=bn
-__device__ __forceinline__ uint32_t make_idesc(uint32_t bn) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// MN-major operand (stored [K, MN] with MN contiguous), 128B swizzle.  TMA lands it as boxes of
+// 64 MN-elements x BK k-rows: every k-row is one 128-byte swizzle row, 8 k-rows make a 1024-byte
+// atom (SBO), and the next 64 MN-elements start one whole box later (LBO = BK * 128 bytes).
+constexpr uint32_t kMnBoxBytes = BK * 128;
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(kMnBoxBytes >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, M=128, N=bn; bit 15 / 16 = A / B is MN-major
+__device__ __forceinline__ uint32_t make_idesc(uint32_t bn, uint32_t mn = 0) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((mn & 1u) << 15) | (((mn >> 1) & 1u) << 16) | ((bn >> 3) << 17) |
+         ((uint32_t)(BM >> 4) << 24);
 }
 
 // Drain one 128 x bn accumulator tile: TMEM -> registers -> fused epilogue -> global.
@@ -185,7 +201,12 @@ __device__ __forceinline__ void epilogue_tile(const Epilogue& ep, int M, int N, 
         else atomicAdd(ep.rowsum + m, s);
       }
       // direct ([M, ld]) outputs: each thread writes its row's 32 contiguous values
-      if (ep.out_f32) {
+      if (ep.out_f32 && ep.atomic) {
+        float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < valid) atomicAdd(o + j, x[j]);
+      } else if (ep.out_f32) {
         float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
         if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
@@ -240,6 +261,8 @@ struct GroupedArgs {
   CUtensorMap mb[kMaxGroup];
   Epilogue ep[kMaxGroup];
   int32_t M[kMaxGroup], N[kMaxGroup], K[kMaxGroup], bn[kMaxGroup];
+  int32_t split[kMaxGroup];  // K slices per output tile (>= 1); slices accumulate atomically
+  int32_t mn[kMaxGroup];     // bit 0: A is MN-major ([K, lda]), bit 1: B is MN-major ([K, ldb])
   int32_t count;
 };
 
@@ -249,9 +272,16 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
   const int prob = blockIdx.z;
   const int M = g.M[prob], N = g.N[prob], K = g.K[prob];
   const uint32_t bn = (uint32_t)g.bn[prob];
-  const int m0 = blockIdx.x * BM;
+  const int split = g.split[prob];
+  const uint32_t mn = (uint32_t)g.mn[prob];
+  const int m0 = (int)(blockIdx.x / split) * BM;
   const int n0 = blockIdx.y * (int)bn;
   if (m0 >= M || n0 >= N) return;  // grid is the union of the problems' tile grids
+  // this CTA's slice of the K loop
+  const int kb_all = (K + BK - 1) / BK;
+  const int kb_per = (kb_all + split - 1) / split;
+  const int kb0 = (int)(blockIdx.x % split) * kb_per;
+  if (kb0 >= kb_all) return;
   const CUtensorMap* tma_a = &g.ma[prob];
   const CUtensorMap* tma_b = &g.mb[prob];
   const Epilogue& ep = g.ep[prob];
@@ -272,7 +302,7 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_kb = (K + BK - 1) / BK;
+  const int num_kb = (kb_all - kb0) < kb_per ? (kb_all - kb0) : kb_per;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tma_a)) : "memory");
@@ -302,13 +332,26 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
         const uint32_t bar = smem_u32(&full_bar[s]);
         mbar_expect_tx(bar, stage_tx);
         const uint32_t a_dst = smem_u32(smem + (size_t)s * stage_bytes);
-        tma_load_2d(tma_a, bar, a_dst, kb * BK, m0);
-        tma_load_2d(tma_b, bar, a_dst + kTileABytes, kb * BK, n0);
+        const int k_crd = (kb0 + kb) * BK;
+        if (mn & 1u) {
+          for (int j = 0; j < BM / 64; ++j) tma_load_2d(tma_a, bar, a_dst + j * kMnBoxBytes, m0 + j * 64, k_crd);
+        } else {
+          tma_load_2d(tma_a, bar, a_dst, k_crd, m0);
+        }
+        if (mn & 2u) {
+          for (int j = 0; j < (int)bn / 64; ++j)
+            tma_load_2d(tma_b, bar, a_dst + kTileABytes + j * kMnBoxBytes, n0 + j * 64, k_crd);
+        } else {
+          tma_load_2d(tma_b, bar, a_dst + kTileABytes, k_crd, n0);
+        }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    const uint32_t idesc = make_idesc(bn);
+    const uint32_t idesc = make_idesc(bn, mn);
+    // bytes >> 4 per 16-element K step: 32 B inside a K-major swizzle row, two 1024 B atoms MN-major
+    const uint64_t a_step = (mn & 1u) ? (2048 >> 4) : 2;
+    const uint64_t b_step = (mn & 2u) ? (2048 >> 4) : 2;
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % n_stages;
       const uint32_t phase = (uint32_t)(kb / n_stages) & 1u;
@@ -316,12 +359,12 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
       tc_fence_after();
       if (elect_one()) {
         const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
-        const uint64_t da = make_smem_desc(a_addr);
-        const uint64_t db = make_smem_desc(a_addr + kTileABytes);
+        const uint64_t da = (mn & 1u) ? make_smem_desc_mn(a_addr) : make_smem_desc(a_addr);
+        const uint64_t db = (mn & 2u) ? make_smem_desc_mn(a_addr + kTileABytes) : make_smem_desc(a_addr + kTileABytes);
 #pragma unroll
         for (int k = 0; k < BK / 16; ++k) {
-          // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in the (addr >> 4) field
-          umma_bf16(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+          // advance 16 bf16 along K: a_step / b_step in the (addr >> 4) field
+          umma_bf16(tmem_base, da + a_step * (uint64_t)k, db + b_step * (uint64_t)k, idesc, (kb | k) != 0 ? 1u : 0u);
         }
         umma_commit(smem_u32(&empty_bar[s]));  // smem stage reusable once these MMAs retire
         if (kb == num_kb - 1) umma_commit(smem_u32(&tmem_full_bar));
@@ -332,7 +375,6 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
     // ===================== epilogue (warps 2..5) =====================
     // a warp may only touch the TMEM lane quarter given by (warp id % 4)
     const int q = warp & 3;
-    const int m = m0 + q * 32 + lane;
     mbar_wait(smem_u32(&tmem_full_bar), 0);
     tc_fence_after();
     epilogue_tile(ep, M, N, m0, n0, bn, tmem_base, q, lane, gridDim.y == 1 || (int)bn >= N);
@@ -497,6 +539,28 @@ int make_map(CUtensorMap* map, const void* base, int rows, int cols, int ld, int
   return 0;
 }
 
+// bf16 [k_rows, ld] row-major holding an MN-major operand: logical width `mn_cols`; box = 64 MN
+// elements (one 128-byte swizzle row) x BK k-rows
+int make_map_mn(CUtensorMap* map, const void* base, int k_rows, int mn_cols, int ld) {
+  EncodeTiledFn enc = get_encode_fn();
+  P2PFL_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  P2PFL_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "GEMM operands must be 16-byte aligned");
+  P2PFL_REQUIRE(((size_t)ld * 2) % 16 == 0, "GEMM operand leading dimensions must be multiples of 8 elements");
+  cuuint64_t gdim[2] = {(cuuint64_t)mn_cols, (cuuint64_t)k_rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {64u, (cuuint32_t)BK};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (MN-major, k_rows=%d cols=%d ld=%d)", (int)r, k_rows,
+              mn_cols, ld);
+    return -2;
+  }
+  return 0;
+}
+
 // N-tile width: the widest that fits, but narrow it while the grid would leave most SMs
 // idle - small-K problems (wgrad of a small batch) are bound by the epilogue stores, which
 // spread over more SMs with narrower tiles.
@@ -510,10 +574,40 @@ int pick_bn(int M, int N) {
 int fill_problem(GroupedArgs& g, int idx, const p2pfl_gemm_args& a) {
   P2PFL_REQUIRE(a.A && a.B && a.M > 0 && a.N > 0 && a.K > 0, "bad GEMM shape or operands");
   P2PFL_REQUIRE(a.out_f32 || a.out_bf16 || a.out_f32_t || a.out_bf16_t || a.rowsum, "GEMM needs an output");
-  const int bn = pick_bn(a.M, a.N);
-  if (int rc = make_map(&g.ma[idx], a.A, a.M, a.K, a.lda, BM)) return rc;
-  if (int rc = make_map(&g.mb[idx], a.B, a.N, a.K, a.ldb, bn)) return rc;
+  const int mn = a.mn_major & 3;
+  const int tiles_m = (a.M + BM - 1) / BM;
+  const int kb_all = (a.K + BK - 1) / BK;
+  int bn, split = 1;
+  if (a.split_k != 0 && a.split_k != 1) {
+    // split-K problems (weight gradients: small output, long reduction): widest tile, then
+    // enough K slices to fill the machine, at least four k-blocks each
+    bn = a.N <= 32 ? 32 : a.N <= 64 ? 64 : a.N <= 128 ? 128 : 256;
+    const int tiles = tiles_m * ((a.N + bn - 1) / bn);
+    split = a.split_k > 1 ? a.split_k : (2 * 148 + tiles - 1) / tiles;
+    if (split > kb_all / 4) split = kb_all / 4;
+    if (split < 1) split = 1;
+  } else {
+    bn = pick_bn(a.M, a.N);
+  }
+  if ((mn & 2) && bn < 64) bn = 64;  // an MN-major B tile is made of 64-column boxes
+  if (split > 1) {
+    P2PFL_REQUIRE(a.out_f32 && !a.out_bf16 && !a.out_f32_t && !a.out_bf16_t && !a.rowsum && !a.bias && !a.relu && !a.mask,
+                  "a split-K GEMM accumulates into out_f32 only (zero-filled by the caller), without bias / ReLU / mask");
+  }
+  if (mn & 1) {
+    if (int rc = make_map_mn(&g.ma[idx], a.A, a.K, a.M, a.lda)) return rc;
+  } else {
+    if (int rc = make_map(&g.ma[idx], a.A, a.M, a.K, a.lda, BM)) return rc;
+  }
+  if (mn & 2) {
+    if (int rc = make_map_mn(&g.mb[idx], a.B, a.K, a.N, a.ldb)) return rc;
+  } else {
+    if (int rc = make_map(&g.mb[idx], a.B, a.N, a.K, a.ldb, bn)) return rc;
+  }
+  g.split[idx] = split;
+  g.mn[idx] = mn;
   Epilogue& ep = g.ep[idx];
+  ep.atomic = split > 1;
   ep.bias = a.bias;
   ep.mask = reinterpret_cast<const __nv_bfloat16*>(a.mask);
   ep.out_f32 = a.out_f32;
@@ -545,10 +639,11 @@ int launch_group(int device, cudaStream_t stream, const p2pfl_gemm_args* args, i
   int gx = 0, gy = 0;
   for (int i = 0; i < count; ++i) {
     if (int rc = fill_problem(g, i, args[i])) return rc;
-    const int tx = (args[i].M + BM - 1) / BM, ty = (args[i].N + g.bn[i] - 1) / g.bn[i];
+    const int tx = (args[i].M + BM - 1) / BM * g.split[i], ty = (args[i].N + g.bn[i] - 1) / g.bn[i];
     gx = tx > gx ? tx : gx;
     gy = ty > gy ? ty : gy;
   }
+  const bool plain = g.split[0] == 1 && g.mn[0] == 0;
   constexpr size_t smem = (size_t)kRingBytes + 1024;
   static bool attr_set[64] = {false};
   if (device >= 0 && device < 64 && !attr_set[device]) {
@@ -556,7 +651,7 @@ int launch_group(int device, cudaStream_t stream, const p2pfl_gemm_args* args, i
     attr_set[device] = true;
   }
   const int sms = sm_count(device);
-  if (count == 1 && gx * gy >= 2 * sms) {
+  if (count == 1 && plain && gx * gy >= 2 * sms) {
     // many more tiles than SMs: persistent CTAs with double-buffered accumulators
     static bool pattr_set[64] = {false};
     if (device >= 0 && device < 64 && !pattr_set[device]) {
@@ -787,6 +882,7 @@ extern "C" int p2pfl_gemm_chain(int device, void* stream, const p2pfl_gemm_args*
   for (int i = 0; i < n_gemm; ++i) {
     const p2pfl_gemm_args& a = gemms[i];
     P2PFL_REQUIRE(a.A && a.B && a.M > 0 && a.N > 0 && a.K > 0, "bad GEMM shape or operands");
+    P2PFL_REQUIRE((a.split_k == 0 || a.split_k == 1) && a.mn_major == 0, "chain links are plain K-major GEMMs without split-K");
     memset(&tmp, 0, sizeof(tmp));
     if (int rc = fill_problem(tmp, 0, a)) return rc;
     g.ma[i] = tmp.ma[0];

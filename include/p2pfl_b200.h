@@ -202,6 +202,15 @@ typedef struct {
   void*  out_bf16_t; int32_t ld_bf16_t; /* [N, ld_bf16_t] (transposed) */
   float* rowsum;                        /* [M], atomically accumulated */
   float alpha;                          /* scales the accumulator before the epilogue */
+  /* 0/1: one CTA per output tile.  -1 (pick) or n > 1: the K loop is cut in slices that
+   * accumulate into out_f32 with atomics - the caller zero-fills out_f32, and bias / ReLU /
+   * mask / the other outputs are not available.  For weight gradients (small D, long K). */
+  int32_t split_k;
+  /* bit 0: A is stored [K, lda] with M contiguous; bit 1: B is stored [K, ldb] with N
+   * contiguous (MN-major tcgen05 operands), so D = A^T-stored . B-stored needs no transposed
+   * copies: wgrad = dZ[pix, Cout]^T . col[pix, K], dgrad = dZ . W[Cout, K].
+   * p2pfl_gemm_tn / _grouped only. */
+  int32_t mn_major;
 } p2pfl_gemm_args;
 int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* args);
 /* Up to 4 independent GEMMs in ONE launch (e.g. a layer's wgrad and dgrad, which
@@ -274,6 +283,26 @@ int p2pfl_col2im_add(int device, void* stream, const void* dcol, int ld_col, int
 int p2pfl_avgpool_fwd(int device, void* stream, const void* x_nhwc, int B, int HW, int C, void* y,
                       void* y_t /* nullable */, int ld_t);
 int p2pfl_avgpool_bwd(int device, void* stream, const void* dy, int B, int HW, int C, void* dx_nhwc);
+
+/* Tap-major ("kc") convolution layout, for C % 8 == 0: the K axis of the implicit GEMM is
+ * ordered (i, j, c) - channel fastest - so with NHWC activations im2col / col2im move
+ * 16-byte channel vectors and the column matrix is one dense stream.
+ *   col[(b,ho,wo), (i*kw + j)*C + c] = x[b, ho*s+i-p, wo*s+j-p, c]
+ * The weights are repacked to the same K order (p2pfl_conv_pack, all convolutions of a
+ * network in ONE launch, fp32 -> bf16 [cout, ldk]); the weight gradient the wgrad GEMM
+ * accumulates in packed order is put back with p2pfl_conv_unpack.  `table_dev`: int64
+ * [n_conv, 8] on the device, rows {flat offset, packed offset, cout, cin, taps, ldk,
+ * tap_major (0 keeps PyTorch's (c,i,j) order: the C = 3 stem), 0}; `max_elems` = the
+ * largest cout*cin*taps. */
+int p2pfl_im2col_kc(int device, void* stream, const void* x_nhwc, int B, int H, int W, int C,
+                    int kh, int kw, int stride, int pad, void* col, int ld_col);
+int p2pfl_col2im_kc(int device, void* stream, const void* dcol, int ld_col, int B, int H, int W,
+                    int C, int kh, int kw, int stride, int pad, void* dx_nhwc,
+                    const void* extra /* nullable, added */);
+int p2pfl_conv_pack(int device, void* stream, const float* flat, void* packed_bf16,
+                    const int64_t* table_dev, int n_conv, int64_t max_elems);
+int p2pfl_conv_unpack(int device, void* stream, const float* packed_f32, float* flat,
+                      const int64_t* table_dev, int n_conv, int64_t max_elems);
 
 /* ------------------------------------------------------------ data movement
  * K11/N8: device-resident dataset; gather a shuffled epoch in bf16, both as

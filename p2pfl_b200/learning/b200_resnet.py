@@ -1,11 +1,15 @@
 """Fused sm_100a train step of the CIFAR-shaped ResNet-18 (BASELINE.json config 3).
 
-Every convolution is an implicit GEMM on the tcgen05 kernel (``im2col`` -> ``ops.gemm_tn``,
-weight gradient ``dZ^T . col`` with K = pixel count, data gradient ``dZ . W`` + ``col2im``),
-every BatchNorm (+ residual add, + ReLU) is the coalesced stats / apply kernel pair, the
-head is global average pool + a swap-AB Linear + the fused softmax-cross-entropy.  Activations
-are NHWC bf16; parameters, BatchNorm running statistics, gradients and Adam state live in the
-learner's flat arena, so ``state_dict`` and the gossip data plane are unchanged.
+Every convolution is a GEMM on the tcgen05 kernel over a tap-major column matrix
+(``im2col_kc``: K ordered (i, j, c), so NHWC activations move as 16-byte channel vectors).
+The backward GEMMs read the SAME buffers as MN-major tensor-core operands, so nothing is
+transposed: weight gradient ``dZ[pix, Cout]^T . col[pix, K]`` (split over K = pixel count, the
+slices accumulate atomically), data gradient ``dZ . W[Cout, K]`` + ``col2im_kc``.  Every
+BatchNorm (+ residual add, + ReLU) is the coalesced stats / apply kernel pair, the head is
+global average pool + a swap-AB Linear + the fused softmax-cross-entropy.  Activations are
+NHWC bf16; parameters, BatchNorm running statistics, gradients and Adam state live in the
+learner's flat arena (PyTorch weight order - the tap-major bf16 copies are repacked by one
+launch per step), so ``state_dict`` and the gossip data plane are unchanged.
 
 Not part of the reference (it ships only the MLP and the small CNN); built for the
 "CIFAR-10-shaped ResNet-18, ring, bf16" configuration.
@@ -39,9 +43,8 @@ class _Conv:
         self.w_off = lay[name + ".weight"].offset
         self.g_off, self.b_off = lay[bn + ".weight"].offset, lay[bn + ".bias"].offset
         self.rm_off, self.rv_off = lay[bn + ".running_mean"].offset, lay[bn + ".running_var"].offset
-        self.padded = self.K % 8 != 0  # first layer: K = 27 needs a padded bf16 copy (16-byte row pitch)
-        self.wpad: Optional[torch.Tensor] = None
-        self.wt_off = -1
+        self.kc = self.cin % 8 == 0  # tap-major K order; the 3-channel stem keeps PyTorch's (c, i, j)
+        self.pk_off = -1  # offset of this conv in the packed weight / packed gradient buffers
 
 
 class _Block:
@@ -90,32 +93,37 @@ class ResNetPlan:
         lay = learner.layout.by_name
         self.fcw_off, self.fcb_off = lay["fc.weight"].offset, lay["fc.bias"].offset
         dev = learner.device
-        # bf16 transposed copies W^T [K, Cout] (dgrad operands) + the head's W^T [clast, ncls]
-        off = 0
-        self.tdescs = []
-        for c in self.convs[1:]:  # the stem needs no data gradient
-            c.wt_off = off
-            self.tdescs.append((c.w_off, off, c.cout, c.K, _pad8(c.cout)))
-            off += c.K * _pad8(c.cout)
-        self.t_fc = off
-        self.tdescs.append((self.fcw_off, off, self.ncls, self.clast, _pad8(self.ncls)))
-        off += self.clast * _pad8(self.ncls)
-        self.wT16 = torch.zeros(off, dtype=torch.bfloat16, device=dev)
+        # packed bf16 conv weights [cout, ldk] (and, same offsets, the fp32 gradients the wgrad
+        # GEMMs accumulate); `table` drives the one-launch pack / unpack kernels
+        off, rows = 0, []
         for c in self.convs:
-            if c.padded:
-                c.wpad = torch.zeros(c.cout, c.ldk, dtype=torch.bfloat16, device=dev)
+            c.pk_off = off
+            rows.append([c.w_off, off, c.cout, c.cin, c.k * c.k, c.ldk, int(c.kc), 0])
+            off += (c.cout * c.ldk + 63) // 64 * 64
+        self.wk = torch.zeros(off, dtype=torch.bfloat16, device=dev)
+        self.gw = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.table = torch.tensor(rows, dtype=torch.int64, device=dev)
+        self.max_w = max(c.cout * c.K for c in self.convs)
+        # the head's W^T [clast, ncls] (dgrad operand of the swap-AB Linear)
+        self.t_fc = 0
+        self.tdescs = [(self.fcw_off, 0, self.ncls, self.clast, _pad8(self.ncls))]
+        self.wT16 = torch.zeros(self.clast * _pad8(self.ncls), dtype=torch.bfloat16, device=dev)
         self.ok = True
 
     # ------------------------------------------------------------------ copies
     def refresh(self) -> None:
         L = self.lr
+        ops.conv_pack(L.flat, self.wk, self.table, len(self.convs), self.max_w)
         ops.transpose_cast(L.flat, self.wT16, self.tdescs)
-        for c in self.convs:
-            if c.padded:
-                ops.pad_cast(L.flat[c.w_off :], c.cout, c.K, c.wpad, c.ldk)
 
     def _w(self, c: _Conv) -> torch.Tensor:
-        return c.wpad if c.padded else self.lr.w16[c.w_off :]
+        return self.wk[c.pk_off :]
+
+    def _im2col(self, c: _Conv, x: torch.Tensor, bsz: int, col: torch.Tensor) -> None:
+        if c.kc:
+            ops.im2col_kc(x, bsz, c.Hin, c.Hin, c.cin, c.k, c.k, c.stride, c.pad, col, c.ldk)
+        else:
+            ops.im2col(x, bsz, c.Hin, c.Hin, c.cin, c.k, c.k, c.stride, c.pad, col, c.ldk)
 
     # ----------------------------------------------------------------- buffers
     def alloc(self, B: int, train: bool) -> Dict[str, Any]:
@@ -127,7 +135,6 @@ class ResNetPlan:
             pix = B * c.Hout * c.Hout
             d = {"col": z(pix, c.ldk), "z": z(pix, c.cout), "y": z(pix, c.cout)}
             if train:
-                d["colT"] = z(c.K, pix)
                 d["sm"] = z(c.cout, dt=torch.float32)
                 d["sr"] = z(c.cout, dt=torch.float32)
             a["conv"][c.name] = d
@@ -141,7 +148,7 @@ class ResNetPlan:
             a["dZT"] = z(self.ncls, a["ldB"])
             a["df"] = z(B, self.clast)
             # gradient scratch, sized for the widest layer and reused down the network
-            for k in ("g0", "g1", "g2", "g3", "dz", "dzT"):
+            for k in ("g0", "g1", "g2", "g3", "dz"):
                 a[k] = z(max_act)
             a["dcol"] = z(max_col)
         return a
@@ -152,9 +159,7 @@ class ResNetPlan:
         """y = [relu](bn(conv(x)) [+ residual]); x NHWC bf16 [bsz, Hin, Hin, cin]."""
         L, d = self.lr, a["conv"][c.name]
         pix = bsz * c.Hout * c.Hout
-        pix_alloc = a["B"] * c.Hout * c.Hout
-        ops.im2col(x, bsz, c.Hin, c.Hin, c.cin, c.k, c.k, c.stride, c.pad, d["col"], c.ldk,
-                   d["colT"] if train else None, pix_alloc)  # fmt: skip
+        self._im2col(c, x, bsz, d["col"])
         ops.gemm_tn(d["col"], c.ldk, self._w(c), c.ldk, pix, c.cout, c.K, out_bf16=d["z"], ld_bf16=c.cout)
         f = L.flat
         if train:
@@ -193,21 +198,24 @@ class ResNetPlan:
         ``dx_out`` (optional) receives the gradient w.r.t. the conv input (+ ``extra``)."""
         L, d, g = self.lr, a["conv"][c.name], self.lr.grads
         pix = bsz * c.Hout * c.Hout
-        pix_alloc = a["B"] * c.Hout * c.Hout
         f = L.flat
         ops.bn_bwd(d["z"], d["y"], dy, pix, c.cout, f[c.g_off :], d["sm"], d["sr"], relu, a["dz"], d_res,
-                   g[c.g_off :], g[c.b_off :], a["dzT"], pix_alloc)  # fmt: skip
-        probs = [ops.gemm_args(a["dzT"], pix_alloc, d["colT"], pix_alloc, c.cout, c.K, pix, out_f32=g[c.w_off :], ld_f32=c.K)]
+                   g[c.g_off :], g[c.b_off :])  # fmt: skip
+        # dW[cout, K] = dz[pix, cout]^T . col[pix, K]: both operands MN-major, the pixel axis split
+        probs = [ops.gemm_args(a["dz"], c.cout, d["col"], c.ldk, c.cout, c.K, pix, out_f32=self.gw[c.pk_off :], ld_f32=c.ldk,
+                               split_k=-1, a_mn=True, b_mn=True)]  # fmt: skip
         if dx_out is not None:
-            probs.append(ops.gemm_args(a["dz"], c.cout, self.wT16[c.wt_off :], _pad8(c.cout), pix, c.K, c.cout,
-                                       out_bf16=a["dcol"], ld_bf16=c.ldk))  # fmt: skip
+            # dcol[pix, K] = dz[pix, cout] . W[cout, K]: the packed weight is the MN-major B operand
+            probs.append(ops.gemm_args(a["dz"], c.cout, self._w(c), c.ldk, pix, c.K, c.cout, out_bf16=a["dcol"],
+                                       ld_bf16=c.ldk, b_mn=True))  # fmt: skip
         ops.gemm_tn_grouped(L.device, probs)
         if dx_out is not None:
-            ops.col2im(a["dcol"], c.ldk, bsz, c.Hin, c.Hin, c.cin, c.k, c.k, c.stride, c.pad, dx_out, extra)
+            ops.col2im_kc(a["dcol"], c.ldk, bsz, c.Hin, c.Hin, c.cin, c.k, c.k, c.stride, c.pad, dx_out, extra)
 
     def train_step(self, x16, y, bsz: int, a: Dict[str, Any], loss_slot, step_offset: int, lr: float) -> None:
         L, g = self.lr, self.lr.grads
         ldB = a["ldB"]
+        self.gw.zero_()  # the split-K weight gradients accumulate
         self.forward(x16, bsz, a, train=True)
         ops.softmax_xent(a["logits"], a["ld_logits"], y, bsz, self.ncls, a["dZ"], _pad8(self.ncls), a["dZT"], ldB,
                          g[self.fcb_off :], loss_slot)  # fmt: skip
@@ -235,5 +243,6 @@ class ResNetPlan:
                 self._bn_conv_bwd(b.c1, x_in, a["g3"], bsz, a, True, None, spare, dcur)
             dcur, spare = spare, dcur
         self._bn_conv_bwd(self.stem, x16, dcur, bsz, a, True, None, None, None)
+        ops.conv_unpack(self.gw, g, self.table, len(self.convs), self.max_w)
         ops.adam_step(L.flat, g, L.adam_m, L.adam_v, L.w16, lr, L.adam_step, step_offset)
         self.refresh()

@@ -45,6 +45,7 @@ class GemmArgs(C.Structure):
         ("out_bf16_t", C.c_void_p), ("ld_bf16_t", C.c_int32),
         ("rowsum", C.c_void_p),
         ("alpha", C.c_float),
+        ("split_k", C.c_int32), ("mn_major", C.c_int32),
     ]  # fmt: skip
 
 
@@ -301,8 +302,12 @@ def gemm_args(
     out_f32_t: Optional[torch.Tensor] = None, ld_f32_t: int = 0,
     out_bf16_t: Optional[torch.Tensor] = None, ld_bf16_t: int = 0,
     rowsum: Optional[torch.Tensor] = None, alpha: float = 1.0,
+    split_k: int = 0, a_mn: bool = False, b_mn: bool = False,
 ) -> GemmArgs:  # fmt: skip
-    """Describe D[M,N] = alpha * A[M,K] @ B[N,K]^T with its fused epilogue."""
+    """Describe D[M,N] = alpha * A[M,K] @ B[N,K]^T with its fused epilogue.
+
+    ``a_mn`` / ``b_mn``: that operand is stored ``[K, ld]`` (M resp. N contiguous) instead.
+    ``split_k`` (-1 = pick, n > 1 = n slices): K slices accumulate into a zero-filled ``out_f32``."""
     return GemmArgs(
         A.data_ptr(), lda, B.data_ptr(), ldb, M, N, K,
         0 if bias is None else bias.data_ptr(), int(bias_per_row), int(relu),
@@ -312,6 +317,7 @@ def gemm_args(
         0 if out_f32_t is None else out_f32_t.data_ptr(), ld_f32_t,
         0 if out_bf16_t is None else out_bf16_t.data_ptr(), ld_bf16_t,
         0 if rowsum is None else rowsum.data_ptr(), alpha,
+        split_k, int(a_mn) | (int(b_mn) << 1),
     )  # fmt: skip
 
 
@@ -413,6 +419,39 @@ def pad_cast(src, rows: int, cols: int, dst, ld: int) -> None:
 
 def nchw_to_nhwc(x, B: int, Cc: int, H: int, W: int, y) -> None:
     _check(lib().p2pfl_nchw_to_nhwc(_dev(x), _stream(), _p(x), C.c_int(B), C.c_int(Cc), C.c_int(H), C.c_int(W), _p(y)))
+    _count()
+
+
+def im2col_kc(x, B: int, H: int, W: int, Cc: int, kh: int, kw: int, stride: int, pad: int, col, ld_col: int) -> None:
+    """Tap-major im2col (K ordered (i, j, c)), 16-byte channel vectors; needs ``Cc % 8 == 0``."""
+    _check(
+        lib().p2pfl_im2col_kc(
+            _dev(x), _stream(), _p(x), C.c_int(B), C.c_int(H), C.c_int(W), C.c_int(Cc), C.c_int(kh), C.c_int(kw),
+            C.c_int(stride), C.c_int(pad), _p(col), C.c_int(ld_col),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def col2im_kc(dcol, ld_col: int, B: int, H: int, W: int, Cc: int, kh: int, kw: int, stride: int, pad: int, dx, extra=None) -> None:
+    _check(
+        lib().p2pfl_col2im_kc(
+            _dev(dcol), _stream(), _p(dcol), C.c_int(ld_col), C.c_int(B), C.c_int(H), C.c_int(W), C.c_int(Cc), C.c_int(kh),
+            C.c_int(kw), C.c_int(stride), C.c_int(pad), _p(dx), _p(extra),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def conv_pack(flat, packed, table, n_conv: int, max_elems: int) -> None:
+    """fp32 PyTorch-order conv weights in ``flat`` -> bf16 packed ``[cout, ldk]`` copies, one launch."""
+    _check(lib().p2pfl_conv_pack(_dev(flat), _stream(), _p(flat), _p(packed), _p(table), C.c_int(n_conv), C.c_int64(max_elems)))
+    _count()
+
+
+def conv_unpack(packed_f32, flat, table, n_conv: int, max_elems: int) -> None:
+    """Packed-order fp32 weight gradients -> PyTorch order inside ``flat``, one launch."""
+    _check(lib().p2pfl_conv_unpack(_dev(flat), _stream(), _p(packed_f32), _p(flat), _p(table), C.c_int(n_conv), C.c_int64(max_elems)))
     _count()
 
 

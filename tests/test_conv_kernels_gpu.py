@@ -194,3 +194,76 @@ def test_nchw_to_nhwc(ops):
     y = torch.zeros(3, 4, 6, 5, device=DEV, dtype=torch.bfloat16)
     ops.nchw_to_nhwc(x, 3, 5, 4, 6, y)
     assert torch.equal(y, _nhwc(x))
+
+
+# ------------------------------------------------------- tap-major ("kc") path
+@pytest.mark.parametrize("B,C,H,k,stride,pad,Cout", [(4, 64, 16, 3, 1, 1, 64), (3, 64, 16, 3, 2, 1, 128), (2, 128, 8, 1, 2, 0, 256), (5, 8, 6, 3, 1, 1, 16)])
+def test_conv_tap_major_fwd_wgrad_dgrad(ops, B, C, H, k, stride, pad, Cout):
+    """The ResNet conv path: vectorised im2col, packed weights, MN-major backward GEMMs
+    (no transposed copies), split-K wgrad, vectorised col2im (+ residual), unpacked gradient."""
+    torch.manual_seed(1)
+    x = torch.randn(B, C, H, H, device=DEV).to(torch.bfloat16).float()
+    w = (torch.randn(Cout, C, k, k, device=DEV) / (C * k * k) ** 0.5).to(torch.bfloat16).float()
+    Ho = ops.conv_out(H, k, stride, pad)
+    pix, K, taps = B * Ho * Ho, C * k * k, k * k
+    xn = _nhwc(x)
+    col = torch.full((pix, K), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.im2col_kc(xn, B, H, H, C, k, k, stride, pad, col, K)
+    ref_col = F.unfold(x, k, padding=pad, stride=stride).transpose(1, 2).reshape(pix, C, taps)
+    assert torch.equal(col.float().view(pix, taps, C), ref_col.permute(0, 2, 1))
+    # packed weights: flat fp32 (PyTorch order, at an offset) -> bf16 [Cout, K] tap-major
+    off = 40
+    flat = torch.zeros(off + Cout * K, device=DEV)
+    flat[off:] = w.reshape(-1)
+    table = torch.tensor([[off, 64, Cout, C, taps, K, 1, 0]], dtype=torch.int64, device=DEV)
+    wk = torch.zeros(64 + Cout * K, device=DEV, dtype=torch.bfloat16)
+    ops.conv_pack(flat, wk, table, 1, Cout * K)
+    assert torch.equal(wk[64:].float().view(Cout, taps, C), w.view(Cout, C, taps).permute(0, 2, 1))
+    wmat = wk[64:]
+    out = torch.zeros(pix, Cout, device=DEV, dtype=torch.bfloat16)
+    ops.gemm_tn(col, K, wmat, K, pix, Cout, K, out_bf16=out, ld_bf16=Cout)
+    ref = F.conv2d(x, w, None, stride=stride, padding=pad)
+    assert torch.allclose(out.float().view(B, Ho, Ho, Cout).permute(0, 3, 1, 2), ref, atol=3e-2, rtol=3e-2)
+    # backward: both GEMMs in one launch, reading dout / col / wk in place
+    dout = torch.randn(pix, Cout, device=DEV).to(torch.bfloat16)
+    gw = torch.zeros(64 + Cout * K, device=DEV)
+    dcol = torch.zeros(pix, K, device=DEV, dtype=torch.bfloat16)
+    ops.gemm_tn_grouped(
+        torch.device(DEV),
+        [
+            ops.gemm_args(dout, Cout, col, K, Cout, K, pix, out_f32=gw[64:], ld_f32=K, split_k=-1, a_mn=True, b_mn=True),
+            ops.gemm_args(dout, Cout, wmat, K, pix, K, Cout, out_bf16=dcol, ld_bf16=K, b_mn=True),
+        ],
+    )
+    grads = torch.zeros_like(flat)
+    ops.conv_unpack(gw, grads, table, 1, Cout * K)
+    extra = torch.randn(B, H, H, C, device=DEV).to(torch.bfloat16)
+    dx = torch.zeros(B, H, H, C, device=DEV, dtype=torch.bfloat16)
+    ops.col2im_kc(dcol, K, B, H, H, C, k, k, stride, pad, dx, extra)
+    xr = x.clone().requires_grad_(True)
+    wr = w.clone().requires_grad_(True)
+    y = F.conv2d(xr, wr, None, stride=stride, padding=pad)
+    y.backward(dout.float().view(B, Ho, Ho, Cout).permute(0, 3, 1, 2))
+    rel = (grads[off:].view_as(wr.grad) - wr.grad).norm() / wr.grad.norm()
+    assert rel < 2e-2, float(rel)
+    assert float(grads[:off].abs().max()) == 0.0
+    ref_dx = xr.grad.permute(0, 2, 3, 1) + extra.float()
+    rel = (dx.float() - ref_dx).norm() / ref_dx.norm()
+    assert rel < 2e-2, float(rel)
+
+
+def test_conv_pack_keeps_pytorch_order_for_the_stem(ops):
+    """tap_major = 0 rows (3 input channels) are a plain padded cast; several rows per launch."""
+    torch.manual_seed(2)
+    w0 = torch.randn(64, 3, 3, 3, device=DEV)
+    w1 = torch.randn(16, 8, 3, 3, device=DEV)
+    flat = torch.cat([w0.reshape(-1), w1.reshape(-1)])
+    table = torch.tensor([[0, 0, 64, 3, 9, 32, 0, 0], [w0.numel(), 64 * 32, 16, 8, 9, 72, 1, 0]], dtype=torch.int64, device=DEV)
+    wk = torch.zeros(64 * 32 + 16 * 72, device=DEV, dtype=torch.bfloat16)
+    ops.conv_pack(flat, wk, table, 2, max(w0.numel(), w1.numel()))
+    a = wk[: 64 * 32].view(64, 32)
+    assert torch.equal(a[:, :27], w0.reshape(64, 27).to(torch.bfloat16)) and float(a[:, 27:].abs().max()) == 0.0
+    assert torch.equal(wk[64 * 32 :].view(16, 9, 8), w1.view(16, 8, 9).permute(0, 2, 1).to(torch.bfloat16))
+    g = torch.zeros_like(flat)
+    ops.conv_unpack(wk.float(), g, table, 2, max(w0.numel(), w1.numel()))
+    assert torch.equal(g, flat.to(torch.bfloat16).float())

@@ -403,3 +403,88 @@ def test_softmax_xent_overwrites_dbias(ops):
         db = torch.full((Cn,), 123.0, device=DEV)
         ops.softmax_xent(lg, 16, lb, Bb, Cn, d, 16, None, 0, db, None)
         assert torch.allclose(db, d[:, :Cn].float().sum(0), atol=1e-4), big
+
+
+# ----------------------------------------------- MN-major operands and split-K
+@pytest.mark.parametrize("a_mn,b_mn", [(True, True), (False, True), (True, False)])
+@pytest.mark.parametrize("M,N,K", [(64, 576, 4096), (128, 27, 1000), (512, 4608, 1024), (200, 136, 64), (64, 64, 65536)])
+def test_gemm_mn_major_operands(ops, M, N, K, a_mn, b_mn):
+    """Operands stored [K, MN] (MN contiguous) are read in place: no transposed copies."""
+    torch.manual_seed(M + N + K)
+    A = (torch.randn(M, K, device=DEV) / math.sqrt(K)).to(torch.bfloat16)
+    B = torch.randn(N, K, device=DEV).to(torch.bfloat16)
+    ref = A.float() @ B.float().t()
+    ldm, ldn, ldk = (M + 7) // 8 * 8, (N + 7) // 8 * 8, (K + 7) // 8 * 8
+    if a_mn:
+        a_op = torch.zeros(K, ldm, device=DEV, dtype=torch.bfloat16)
+        a_op[:, :M] = A.t()
+        lda = ldm
+    else:
+        a_op = torch.zeros(M, ldk, device=DEV, dtype=torch.bfloat16)
+        a_op[:, :K] = A
+        lda = ldk
+    if b_mn:
+        b_op = torch.zeros(K, ldn, device=DEV, dtype=torch.bfloat16)
+        b_op[:, :N] = B.t()
+        ldb = ldn
+    else:
+        b_op = torch.zeros(N, ldk, device=DEV, dtype=torch.bfloat16)
+        b_op[:, :K] = B
+        ldb = ldk
+    out = torch.full((M, N), float("nan"), device=DEV)
+    ops.gemm_tn(a_op, lda, b_op, ldb, M, N, K, out_f32=out, ld_f32=N, a_mn=a_mn, b_mn=b_mn)
+    torch.cuda.synchronize()
+    err = (out - ref).abs().max().item()
+    assert torch.allclose(out, ref, atol=3e-3, rtol=3e-3), f"max abs err {err}"
+
+
+@pytest.mark.parametrize("split", [-1, 3, 16])
+@pytest.mark.parametrize("M,N,K,mn", [(64, 576, 65536, True), (64, 27, 8192, True), (128, 256, 4096, False), (512, 4608, 1024, True)])
+def test_gemm_split_k_accumulates(ops, M, N, K, mn, split):
+    """Weight-gradient shape: small output, long reduction, K slices add up atomically."""
+    torch.manual_seed(split + M)
+    A = (torch.randn(M, K, device=DEV) / math.sqrt(K)).to(torch.bfloat16)
+    B = torch.randn(N, K, device=DEV).to(torch.bfloat16)
+    ref = A.float() @ B.float().t()
+    ld = (N + 7) // 8 * 8
+    out = torch.zeros(M, ld, device=DEV)
+    if mn:
+        a_op, b_op = A.t().contiguous(), torch.zeros(K, ld, device=DEV, dtype=torch.bfloat16)
+        b_op[:, :N] = B.t()
+        ops.gemm_tn(a_op, M, b_op, ld, M, N, K, out_f32=out, ld_f32=ld, split_k=split, a_mn=True, b_mn=True)
+    else:
+        ops.gemm_tn(A, K, B, K, M, N, K, out_f32=out, ld_f32=ld, split_k=split)
+    torch.cuda.synchronize()
+    err = (out[:, :N] - ref).abs().max().item()
+    assert torch.allclose(out[:, :N], ref, atol=3e-3, rtol=3e-3), f"max abs err {err}"
+    assert float(out[:, N:].abs().max()) == 0.0 if ld > N else True
+
+
+def test_gemm_split_k_rejects_fused_epilogue(ops):
+    A = torch.zeros(64, 4096, device=DEV, dtype=torch.bfloat16)
+    out = torch.zeros(64, 64, device=DEV, dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError, match="split-K"):
+        ops.gemm_tn(A, 4096, A, 4096, 64, 64, 4096, out_bf16=out, ld_bf16=64, split_k=4)
+
+
+def test_gemm_grouped_conv_backward_pair(ops):
+    """The ResNet backward launch: split-K MN-major wgrad + MN-major-B dgrad in one grid."""
+    torch.manual_seed(3)
+    pix, cout, Kc = 4096, 128, 1152
+    dz = (torch.randn(pix, cout, device=DEV) / 16).to(torch.bfloat16)
+    col = torch.randn(pix, Kc, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(cout, Kc, device=DEV) / 32).to(torch.bfloat16)
+    gw = torch.zeros(cout, Kc, device=DEV)
+    dcol = torch.zeros(pix, Kc, device=DEV, dtype=torch.bfloat16)
+    ops.gemm_tn_grouped(
+        torch.device(DEV),
+        [
+            ops.gemm_args(dz, cout, col, Kc, cout, Kc, pix, out_f32=gw, ld_f32=Kc, split_k=-1, a_mn=True, b_mn=True),
+            ops.gemm_args(dz, cout, w, Kc, pix, Kc, cout, out_bf16=dcol, ld_bf16=Kc, b_mn=True),
+        ],
+    )
+    torch.cuda.synchronize()
+    ref_w = dz.float().t() @ col.float()
+    ref_d = dz.float() @ w.float()
+    assert torch.allclose(gw, ref_w, atol=2e-2, rtol=1e-2), (gw - ref_w).abs().max().item()
+    assert torch.allclose(dcol.float(), ref_d, atol=2e-2, rtol=2e-2), (dcol.float() - ref_d).abs().max().item()

@@ -25,6 +25,24 @@ if what in ("all", "step"):
     learner.fit()
     print("eval", learner.evaluate())
     torch.cuda.synchronize()
+if what == "resnet":
+    # the graph build runs every kernel of the step once outside capture, so a launch list
+    # under ncu shows the whole fused ResNet-18 step
+    from p2pfl_b200.learning.data import Cifar10FederatedDM  # noqa: E402
+    from p2pfl_b200.models import ResNet18  # noqa: E402
+
+    dm = Cifar10FederatedDM(0, 1, n_train=640, n_test=64, batch_size=64)
+    learner = B200Learner(ResNet18(seed=0), dm, "prof", epochs=1, device="cuda:0")
+    learner.fit()
+    ev0 = torch.cuda.Event(enable_timing=True)
+    ev1 = torch.cuda.Event(enable_timing=True)
+    ev0.record(learner.stream)
+    for _ in range(5):
+        learner.fit()
+    ev1.record(learner.stream)
+    torch.cuda.synchronize()
+    print("resnet ms/fit", ev0.elapsed_time(ev1) / 5, "steps/fit", learner._round_steps,
+          "launches/epoch", learner.kernel_launches_per_epoch)
 if what in ("all", "gossip"):
     n, tile = 124_441_344, 16384
     a = DeviceArena(n, slots=2, tile=tile, wire_bf16=True, device=0)
