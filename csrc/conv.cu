@@ -182,6 +182,8 @@ col2im_kc_kernel(const uint4* __restrict__ dcol, int ld8, int B, int H, int W, i
 //   {flat offset of the PyTorch weight [cout, cin*taps], offset in the packed buffer [cout, ldk],
 //    cout, cin, taps, ldk, tap_major (1: k = tap*cin + c, 0: k = c*taps + tap), unused}
 constexpr int kConvTableCols = 8;
+// One thread per (cout, cin) pair walks the taps: its fp32 side is `taps` consecutive floats,
+// its packed side is coalesced across the warp (consecutive c) - both directions stream.
 __global__ void __launch_bounds__(kThreads)
 conv_pack_kernel(const float* __restrict__ flat, __nv_bfloat16* __restrict__ packed, const int64_t* __restrict__ table) {
   const int64_t* t = table + (int64_t)blockIdx.y * kConvTableCols;
@@ -189,12 +191,13 @@ conv_pack_kernel(const float* __restrict__ flat, __nv_bfloat16* __restrict__ pac
   __nv_bfloat16* dst = packed + t[1];
   const int cout = (int)t[2], cin = (int)t[3], taps = (int)t[4], ldk = (int)t[5], tap_major = (int)t[6];
   const int K = cin * taps;
-  const int64_t total = (int64_t)cout * K;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
-    const int kd = (int)(idx % K);
-    const int co = (int)(idx / K);
-    const int ks = tap_major ? (kd % cin) * taps + kd / cin : kd;
-    dst[(int64_t)co * ldk + kd] = __float2bfloat16_rn(src[(int64_t)co * K + ks]);
+  const int total = cout * cin;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int c = idx % cin;
+    const int co = idx / cin;
+    const float* s = src + (int64_t)co * K + c * taps;
+    __nv_bfloat16* d = dst + (int64_t)co * ldk;
+    for (int tap = 0; tap < taps; ++tap) d[tap_major ? tap * cin + c : c * taps + tap] = __float2bfloat16_rn(s[tap]);
   }
 }
 
@@ -206,12 +209,13 @@ conv_unpack_kernel(const float* __restrict__ packed, float* __restrict__ flat, c
   const float* src = packed + t[1];
   const int cout = (int)t[2], cin = (int)t[3], taps = (int)t[4], ldk = (int)t[5], tap_major = (int)t[6];
   const int K = cin * taps;
-  const int64_t total = (int64_t)cout * K;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
-    const int ks = (int)(idx % K);
-    const int co = (int)(idx / K);
-    const int kd = tap_major ? (ks % taps) * cin + ks / taps : ks;
-    dst[idx] = src[(int64_t)co * ldk + kd];
+  const int total = cout * cin;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int c = idx % cin;
+    const int co = idx / cin;
+    float* d = dst + (int64_t)co * K + c * taps;
+    const float* s = src + (int64_t)co * ldk;
+    for (int tap = 0; tap < taps; ++tap) d[tap] = s[tap_major ? tap * cin + c : c * taps + tap];
   }
 }
 
@@ -568,8 +572,8 @@ int p2pfl_conv_pack(int device, void* stream, const float* flat, void* packed_bf
                     int64_t max_elems) {
   P2PFL_REQUIRE(flat && packed_bf16 && table_dev && n_conv > 0 && n_conv <= 65535, "bad arguments to p2pfl_conv_pack");
   P2PFL_CUDA_OK(cudaSetDevice(device));
-  int gx = grid_for(max_elems, device);
-  gx = gx > 64 ? 64 : gx;
+  int gx = grid_for(max_elems / 9 + 1, device);
+  gx = gx > 256 ? 256 : gx;
   conv_pack_kernel<<<dim3(gx, n_conv), kThreads, 0, as_stream(stream)>>>(flat, (__nv_bfloat16*)packed_bf16, table_dev);
   P2PFL_LAUNCH_OK();
   return 0;
@@ -579,8 +583,8 @@ int p2pfl_conv_unpack(int device, void* stream, const float* packed_f32, float* 
                       int64_t max_elems) {
   P2PFL_REQUIRE(flat && packed_f32 && table_dev && n_conv > 0 && n_conv <= 65535, "bad arguments to p2pfl_conv_unpack");
   P2PFL_CUDA_OK(cudaSetDevice(device));
-  int gx = grid_for(max_elems, device);
-  gx = gx > 64 ? 64 : gx;
+  int gx = grid_for(max_elems / 9 + 1, device);
+  gx = gx > 256 ? 256 : gx;
   conv_unpack_kernel<<<dim3(gx, n_conv), kThreads, 0, as_stream(stream)>>>(packed_f32, flat, table_dev);
   P2PFL_LAUNCH_OK();
   return 0;

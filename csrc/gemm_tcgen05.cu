@@ -202,10 +202,19 @@ __device__ __forceinline__ void epilogue_tile(const Epilogue& ep, int M, int N, 
       }
       // direct ([M, ld]) outputs: each thread writes its row's 32 contiguous values
       if (ep.out_f32 && ep.atomic) {
+        // L2 retires a fixed number of reductions per clock whatever their width: use 16-byte ones
         float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
+        if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (j < valid) atomicAdd(o + j, x[j]);
+          for (int j = 0; j < 32; j += 4)
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j), "f"(x[j]), "f"(x[j + 1]),
+                         "f"(x[j + 2]), "f"(x[j + 3])
+                         : "memory");
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < valid) atomicAdd(o + j, x[j]);
+        }
       } else if (ep.out_f32) {
         float* o = ep.out_f32 + (size_t)m * ep.ld_f32 + nb;
         if (valid == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
@@ -263,6 +272,7 @@ struct GroupedArgs {
   int32_t M[kMaxGroup], N[kMaxGroup], K[kMaxGroup], bn[kMaxGroup];
   int32_t split[kMaxGroup];  // K slices per output tile (>= 1); slices accumulate atomically
   int32_t mn[kMaxGroup];     // bit 0: A is MN-major ([K, lda]), bit 1: B is MN-major ([K, ldb])
+  int32_t ring_bytes;        // dynamic shared memory given to the stage ring of the one-shot kernel
   int32_t count;
 };
 
@@ -289,7 +299,9 @@ gemm_tn_kernel(const __grid_constant__ GroupedArgs g) {
   // narrow tiles get a deeper ring out of the same shared memory: the small-batch GEMMs of
   // the train step are latency bound, and more loads in flight shorten their K loop
   const uint32_t stage_bytes = stage_tx;
-  int n_stages = (int)(kRingBytes / stage_bytes);
+  // the launch sizes the ring for the longest K loop of its problems: short loops take little
+  // shared memory, so several CTAs share an SM and hide each other's load and drain latency
+  int n_stages = (int)((uint32_t)g.ring_bytes / stage_bytes);
   n_stages = n_stages > kMaxStages ? kMaxStages : n_stages;
 
   extern __shared__ uint8_t smem_raw[];
@@ -398,6 +410,7 @@ __global__ void __launch_bounds__(kThreadsGemm, 1)
 gemm_tn_persistent_kernel(const __grid_constant__ GroupedArgs g) {
   const int M = g.M[0], N = g.N[0], K = g.K[0];
   const uint32_t bn = (uint32_t)g.bn[0];
+  const uint32_t mn = (uint32_t)g.mn[0];
   const CUtensorMap* tma_a = &g.ma[0];
   const CUtensorMap* tma_b = &g.mb[0];
   const Epilogue& ep = g.ep[0];
@@ -450,13 +463,24 @@ gemm_tn_persistent_kernel(const __grid_constant__ GroupedArgs g) {
           const uint32_t bar = smem_u32(&full_bar[s]);
           mbar_expect_tx(bar, stage_bytes);
           const uint32_t dst = smem_u32(smem + (size_t)s * stage_bytes);
-          tma_load_2d(tma_a, bar, dst, kb * BK, m0);
-          tma_load_2d(tma_b, bar, dst + kTileABytes, kb * BK, n0);
+          if (mn & 1u) {
+            for (int j = 0; j < BM / 64; ++j) tma_load_2d(tma_a, bar, dst + j * kMnBoxBytes, m0 + j * 64, kb * BK);
+          } else {
+            tma_load_2d(tma_a, bar, dst, kb * BK, m0);
+          }
+          if (mn & 2u) {
+            for (int j = 0; j < (int)bn / 64; ++j)
+              tma_load_2d(tma_b, bar, dst + kTileABytes + j * kMnBoxBytes, n0 + j * 64, kb * BK);
+          } else {
+            tma_load_2d(tma_b, bar, dst + kTileABytes, kb * BK, n0);
+          }
         }
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc = make_idesc(bn);
+    const uint32_t idesc = make_idesc(bn, mn);
+    const uint64_t a_step = (mn & 1u) ? (2048 >> 4) : 2;
+    const uint64_t b_step = (mn & 2u) ? (2048 >> 4) : 2;
     uint32_t it = 0, tile_it = 0;
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tile_it) {
       const uint32_t acc = tile_it & 1u, aph = (tile_it >> 1) & 1u;
@@ -468,11 +492,11 @@ gemm_tn_persistent_kernel(const __grid_constant__ GroupedArgs g) {
         tc_fence_after();
         if (elect_one()) {
           const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
-          const uint64_t da = make_smem_desc(a_addr);
-          const uint64_t db = make_smem_desc(a_addr + kTileABytes);
+          const uint64_t da = (mn & 1u) ? make_smem_desc_mn(a_addr) : make_smem_desc(a_addr);
+          const uint64_t db = (mn & 2u) ? make_smem_desc_mn(a_addr + kTileABytes) : make_smem_desc(a_addr + kTileABytes);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
-            umma_bf16(tmem_base + acc * bn, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_bf16(tmem_base + acc * bn, da + a_step * (uint64_t)k, db + b_step * (uint64_t)k, idesc, (kb | k) != 0 ? 1u : 0u);
           umma_commit(smem_u32(&empty_bar[s]));
           if (kb == num_kb - 1) umma_commit(smem_u32(&tmem_full_bar[acc]));
         }
@@ -583,7 +607,8 @@ int fill_problem(GroupedArgs& g, int idx, const p2pfl_gemm_args& a) {
     // enough K slices to fill the machine, at least four k-blocks each
     bn = a.N <= 32 ? 32 : a.N <= 64 ? 64 : a.N <= 128 ? 128 : 256;
     const int tiles = tiles_m * ((a.N + bn - 1) / bn);
-    split = a.split_k > 1 ? a.split_k : (2 * 148 + tiles - 1) / tiles;
+    // one wave of CTAs: every extra slice costs another pass of reductions over D
+    split = a.split_k > 1 ? a.split_k : (148 + tiles - 1) / tiles;
     if (split > kb_all / 4) split = kb_all / 4;
     if (split < 1) split = 1;
   } else {
@@ -642,8 +667,14 @@ int launch_group(int device, cudaStream_t stream, const p2pfl_gemm_args* args, i
     const int tx = (args[i].M + BM - 1) / BM * g.split[i], ty = (args[i].N + g.bn[i] - 1) / g.bn[i];
     gx = tx > gx ? tx : gx;
     gy = ty > gy ? ty : gy;
+    const int stage = (int)kTileABytes + g.bn[i] * BK * 2;
+    const int kb_cta = ((args[i].K + BK - 1) / BK + g.split[i] - 1) / g.split[i];
+    int stages = (int)kRingBytes / stage;
+    stages = stages > kMaxStages ? kMaxStages : stages;
+    stages = stages > kb_cta ? kb_cta : stages;
+    g.ring_bytes = g.ring_bytes > stages * stage ? g.ring_bytes : stages * stage;
   }
-  const bool plain = g.split[0] == 1 && g.mn[0] == 0;
+  const bool plain = g.split[0] == 1;
   constexpr size_t smem = (size_t)kRingBytes + 1024;
   static bool attr_set[64] = {false};
   if (device >= 0 && device < 64 && !attr_set[device]) {
@@ -661,7 +692,7 @@ int launch_group(int device, cudaStream_t stream, const p2pfl_gemm_args* args, i
     P2PFL_CUDA_OK(launch_pdl(gemm_tn_persistent_kernel, dim3(sms), dim3(kThreadsGemm), smem, stream, g));
     return 0;
   }
-  P2PFL_CUDA_OK(launch_pdl(gemm_tn_kernel, dim3(gx, gy, count), dim3(kThreadsGemm), smem, stream, g));
+  P2PFL_CUDA_OK(launch_pdl(gemm_tn_kernel, dim3(gx, gy, count), dim3(kThreadsGemm), (size_t)g.ring_bytes + 1024, stream, g));
   return 0;
 }
 

@@ -26,6 +26,26 @@ REFERENCE_COMMANDS = frozenset(
 )  # fmt: skip
 
 
+# Engine-level envelope for several control messages to one extended neighbour (never sent to a
+# reference node; no counterpart in the reference): args = [pack_bundled(m), ...].
+BUNDLE_CMD = "bundle"
+
+
+def pack_bundled(msg: Any) -> str:
+    import json
+
+    return json.dumps([msg.cmd, int(msg.round), int(msg.ttl), int(msg.hash), [str(a) for a in msg.args]])
+
+
+def unpack_bundled(source: str, packed: str) -> Any:
+    import json
+
+    from p2pfl_b200.communication.messages import Message
+
+    cmd, rnd, ttl, h, args = json.loads(packed)
+    return Message(source=source, cmd=str(cmd), args=[str(a) for a in args], round=int(rnd), ttl=int(ttl), hash=int(h))
+
+
 class HeartbeatCommand(Command):
     """``beat [time]`` (reference: commands/heartbeat_command.py:39-52)."""
 

@@ -38,6 +38,10 @@ class Gossiper(threading.Thread):
         self._pending: Deque[Tuple[Message, List[str]]] = collections.deque()
         self._cv = threading.Condition()
         self._stop_flag = False
+        # lazily queued broadcasts wait here (at most BUNDLE_LINGER) for the next ordinary one
+        self._lazy: List[Tuple[Message, Any]] = []
+        self._lazy_deadline = 0.0
+        self.bundle_fn: Optional[Callable[[List[Message]], None]] = None
         # duplicate filter: ring + set for O(1) membership
         self._seen_ring: Deque[int] = collections.deque()
         self._seen: Set[int] = set()
@@ -62,11 +66,25 @@ class Gossiper(threading.Thread):
             return True
 
     # ---------------------------------------------------------- relay queue
-    def add_broadcast(self, msg: Message, broadcast_fn: Callable[[Message], None]) -> None:
-        """Queue a whole broadcast (performed with overlapped round trips by ``broadcast_fn``)."""
+    def add_broadcast(self, msg: Message, broadcast_fn: Callable[[Message], None], lazy: bool = False) -> None:
+        """Queue a whole broadcast (performed with overlapped round trips by ``broadcast_fn``).
+        ``lazy``: nobody is waiting for it - hold it until the next ordinary broadcast (or
+        ``BUNDLE_LINGER``) so that both can travel in one message."""
         with self._cv:
+            if lazy and self.bundle_fn is not None and Settings.BUNDLE_BOOKKEEPING:
+                if not self._lazy:
+                    self._lazy_deadline = time.time() + Settings.BUNDLE_LINGER
+                self._lazy.append((msg, broadcast_fn))
+                self._cv.notify()  # the relay thread re-arms its timeout
+                return
+            self._flush_lazy_locked()
             self._pending.append((msg, broadcast_fn))  # type: ignore[arg-type]
             self._cv.notify()
+
+    def _flush_lazy_locked(self) -> None:
+        if self._lazy:
+            self._pending.extend(self._lazy)  # type: ignore[arg-type]
+            self._lazy = []
 
     def add_message(self, msg: Message, pending_neis: List[str]) -> None:
         if not pending_neis:
@@ -79,7 +97,14 @@ class Gossiper(threading.Thread):
         while True:
             with self._cv:
                 while not self._pending and not self._stop_flag:
-                    self._cv.wait()
+                    if self._lazy:
+                        rest = self._lazy_deadline - time.time()
+                        if rest <= 0:
+                            self._flush_lazy_locked()
+                            break
+                        self._cv.wait(rest)
+                    else:
+                        self._cv.wait()
                 if self._stop_flag:
                     return
                 budget = max(1, Settings.GOSSIP_MESSAGES_PER_PERIOD)
@@ -98,6 +123,14 @@ class Gossiper(threading.Thread):
                     if not neis:
                         self._pending.popleft()
             t0 = time.time()
+            bcasts = [m for m, n in batch if callable(n)]
+            if len(bcasts) >= 2 and self.bundle_fn is not None and Settings.BUNDLE_BOOKKEEPING:
+                # several whole broadcasts drained together: one message per neighbour
+                try:
+                    self.bundle_fn(bcasts)
+                except Exception as e:
+                    logger.debug(self._addr, f"bundled broadcast failed: {e}")
+                batch = [(m, n) for m, n in batch if not callable(n)]
             for msg, nei in batch:
                 try:
                     if callable(nei):

@@ -160,6 +160,7 @@ class BaseProtocol(CommunicationProtocol):
             self.addr, transport.open_link, transport.close_link, on_change=self._neighbors_changed
         )
         self._gossiper = Gossiper(self.addr, self.send)
+        self._gossiper.bundle_fn = self._broadcast_bundle
         self._heartbeater = Heartbeater(self.addr, self._neighbors, self._broadcast_beat)
         self._server = _ServerHandle(transport)
         from p2pfl_b200.commands.control import HeartbeatCommand, NeighborsHintCommand
@@ -298,15 +299,42 @@ class BaseProtocol(CommunicationProtocol):
             logger.info(self.addr, f"send of '{msg.cmd}' to {nei} failed ({res}); removing neighbour")
             self._neighbors.remove(nei, disconnect_msg=True)
 
-    def broadcast_async(self, msg: Message) -> None:
+    def broadcast_async(self, msg: Message, lazy: bool = False) -> None:
         """Fire-and-forget broadcast: queued to the gossiper thread, which performs the
-        (overlapped) sends and evicts neighbours that fail, exactly like :meth:`broadcast`."""
+        (overlapped) sends and evicts neighbours that fail, exactly like :meth:`broadcast`.
+        ``lazy`` broadcasts may wait ``Settings.BUNDLE_LINGER`` for the next ordinary one;
+        broadcasts that leave together are bundled (:meth:`_broadcast_bundle`)."""
         if not Settings.ASYNC_BOOKKEEPING:
             self.broadcast(msg)
             return
         targets = list(self._neighbors.get_all(only_direct=True))
         if targets:
-            self._gossiper.add_broadcast(msg, self.broadcast)
+            self._gossiper.add_broadcast(msg, self.broadcast, lazy=lazy)
+
+    def _broadcast_bundle(self, msgs: List[Message]) -> None:
+        """Several broadcasts at once: extended neighbours get ONE ``bundle`` message (ttl 1)
+        whose arguments are the packed messages - each is then handled, relayed and
+        de-duplicated by the receiver as if it had arrived alone; reference neighbours get the
+        messages one by one (they would evict us for a command they do not know)."""
+        from p2pfl_b200.commands.control import BUNDLE_CMD, REFERENCE_COMMANDS, pack_bundled
+
+        direct = self._neighbors.get_all(only_direct=True)
+        ext = [(n, direct[n].link) for n in direct if n in self._extended]
+        plain = [n for n in direct if n not in self._extended]
+        failed: Dict[str, str] = {}
+        if ext:
+            bundle = self.build_msg(BUNDLE_CMD, [pack_bundled(m) for m in msgs])
+            bundle.ttl = 1
+            for (nei, _), res in zip(ext, self._transport.deliver_many(ext, bundle)):
+                if res is not None:
+                    failed[nei] = res
+        if plain:
+            for m in msgs:
+                if m.cmd in REFERENCE_COMMANDS:
+                    self.broadcast(m, node_list=plain)
+        for nei, res in failed.items():
+            logger.info(self.addr, f"send of a bundle to {nei} failed ({res}); removing neighbour")
+            self._neighbors.remove(nei, disconnect_msg=True)
 
     def _beat_msg(self, now: float) -> Message:
         from p2pfl_b200.commands.control import EXTENDED_MARK
@@ -376,6 +404,16 @@ class BaseProtocol(CommunicationProtocol):
             return "node not running"
         if not self._gossiper.check_and_set_processed(msg.hash):
             return None
+        if msg.cmd == "bundle":
+            from p2pfl_b200.commands.control import unpack_bundled
+
+            err = None
+            for packed in msg.args:
+                try:
+                    err = self.on_message(unpack_bundled(msg.source, packed)) or err
+                except Exception as e:
+                    err = f"bad bundled message: {e}"
+            return err
         if msg.ttl > 1:
             # flood to my direct neighbours, except the originator and - topology-aware
             # pruning - those the originator advertises it reaches directly

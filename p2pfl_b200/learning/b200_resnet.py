@@ -208,7 +208,13 @@ class ResNetPlan:
             # dcol[pix, K] = dz[pix, cout] . W[cout, K]: the packed weight is the MN-major B operand
             probs.append(ops.gemm_args(a["dz"], c.cout, self._w(c), c.ldk, pix, c.K, c.cout, out_bf16=a["dcol"],
                                        ld_bf16=c.ldk, b_mn=True))  # fmt: skip
-        ops.gemm_tn_grouped(L.device, probs)
+        if len(probs) == 2 and ((pix + 127) // 128) * ((c.K + 255) // 256) >= 296:
+            # a data gradient with many more tiles than SMs runs on the persistent kernel (its
+            # epilogue overlaps the next tile); the split-K weight gradient gets its own launch
+            for pr in probs:
+                ops.gemm_tn_grouped(L.device, [pr])
+        else:
+            ops.gemm_tn_grouped(L.device, probs)
         if dx_out is not None:
             ops.col2im_kc(a["dcol"], c.ldk, bsz, c.Hin, c.Hin, c.cin, c.k, c.k, c.stride, c.pad, dx_out, extra)
 

@@ -10,6 +10,7 @@ from p2pfl_b200.exceptions import NoModelsToAggregateError
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.settings import Settings
 from p2pfl_b200.stages.common import pack_model
+from p2pfl_b200.stages.common import send_async
 from p2pfl_b200.stages.stage import LearningContext, Stage
 from p2pfl_b200.stages.stage_factory import StageFactory
 
@@ -36,7 +37,14 @@ class GossipModelStage(Stage):
             return None
         st.learner.set_parameters(params)
         contributors = agg.get_aggregated_models()
-        getattr(proto, "broadcast_async", proto.broadcast)(proto.build_msg("models_ready", [], round=st.round))
+        # after a complete fused exchange nobody waits for this round's models_ready: it may ride
+        # with the next round's metrics / pre-vote bundle
+        lazy = (
+            getattr(st, "fused_complete_round", None) == st.round
+            and st.total_rounds is not None
+            and st.round + 1 < st.total_rounds
+        )
+        send_async(proto, proto.build_msg("models_ready", [], round=st.round), lazy)
         t1 = time.time()
         GossipModelStage._diffuse(ctx, params, contributors, t1)
         ctx.timings["aggregate"] = ctx.timings.get("aggregate", 0.0) + t1 - t0

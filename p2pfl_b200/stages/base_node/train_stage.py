@@ -32,12 +32,16 @@ class TrainStage(Stage):
         agg.set_nodes_to_aggregate(st.train_set)
         TrainStage.replay_early_models(ctx)
         st.learner.begin_round(st.round)
-        TrainStage.prevote(ctx)
         ctx.timings["arm"] = ctx.timings.get("arm", 0.0) + time.time() - t0
 
         if ctx.early_stopping_fn():
             return None
-        evaluate_and_share(ctx)
+        # the metrics wait (lazily queued) for the pre-vote that follows the evaluation: the two
+        # - and last round's models_ready - reach each neighbour as one bundled message
+        will_prevote = TrainStage.will_prevote(ctx)
+        evaluate_and_share(ctx, lazy=will_prevote)
+        if will_prevote:
+            TrainStage.prevote(ctx)
         t1 = time.time()
 
         if ctx.early_stopping_fn():
@@ -75,14 +79,19 @@ class TrainStage(Stage):
         return StageFactory.get_stage("GossipModelStage")
 
     @staticmethod
-    def prevote(ctx: LearningContext) -> None:
-        """Cast next round's ballot now, so that it travels while this round trains."""
+    def will_prevote(ctx: LearningContext) -> bool:
         from p2pfl_b200.settings import Settings
 
         st = ctx.state
         if not (Settings.PREVOTE and Settings.VOTE_EVERY_ROUND):
-            return
-        if st.round is None or st.total_rounds is None or st.round + 1 >= st.total_rounds:
+            return False
+        return not (st.round is None or st.total_rounds is None or st.round + 1 >= st.total_rounds)
+
+    @staticmethod
+    def prevote(ctx: LearningContext) -> None:
+        """Cast next round's ballot now, so that it travels while this round trains."""
+        st = ctx.state
+        if not TrainStage.will_prevote(ctx):
             return
         from p2pfl_b200.stages.base_node.vote_train_set_stage import VoteTrainSetStage
 

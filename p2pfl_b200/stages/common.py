@@ -16,19 +16,34 @@ def pack_model(protocol: Any, learner: Any, params: Any) -> Any:
     return learner.encode_parameters(params=params if params is not None else learner.export_model())
 
 
-def broadcast_metrics(protocol: Any, state: Any, results: Dict[str, float]) -> None:
+def broadcast_metrics(protocol: Any, state: Any, results: Dict[str, float], lazy: bool = False) -> None:
     """Share evaluation results with every node
-    (reference: stages/base_node/train_stage.py:103-112)."""
+    (reference: stages/base_node/train_stage.py:103-112).  ``lazy``: another broadcast
+    follows shortly (the pre-vote) and the two may share one message per neighbour."""
     if not results:
         return
     flat: List[str] = []
     for k, v in results.items():
         flat += [str(k), str(v)]
     msg = protocol.build_msg("metrics", flat, round=state.round)
-    getattr(protocol, "broadcast_async", protocol.broadcast)(msg)  # nobody waits on metrics
+    send_async(protocol, msg, lazy)  # nobody waits on metrics
 
 
-def evaluate_and_share(ctx: Any) -> None:
+def send_async(protocol: Any, msg: Any, lazy: bool = False) -> None:
+    """Fire-and-forget broadcast where the protocol has one (plain broadcast otherwise)."""
+    fn = getattr(protocol, "broadcast_async", None)
+    if fn is None:
+        protocol.broadcast(msg)
+    elif lazy:
+        try:
+            fn(msg, lazy=True)
+        except TypeError:  # a protocol without lazy queueing
+            fn(msg)
+    else:
+        fn(msg)
+
+
+def evaluate_and_share(ctx: Any, lazy: bool = False) -> None:
     st = ctx.state
     if st.learner is None:
         return
@@ -39,4 +54,4 @@ def evaluate_and_share(ctx: Any) -> None:
     results = st.learner.evaluate()
     ctx.timings["evaluate_learner"] = ctx.timings.get("evaluate_learner", 0.0) + _t.time() - t0
     logger.debug(st.addr, f"evaluated: {results}")
-    broadcast_metrics(ctx.communication_protocol, st, results)
+    broadcast_metrics(ctx.communication_protocol, st, results, lazy)

@@ -253,3 +253,72 @@ def test_relay_pruning_in_a_clique_and_reach_on_a_line():
                 assert len(deliveries) == 3, deliveries  # no redundant relays
         finally:
             _stop(nodes)
+
+
+@pytest.mark.parametrize("protocol", PROTOCOLS)
+def test_bookkeeping_broadcasts_are_bundled(protocol):
+    """A lazily queued broadcast waits for the next ordinary one; together they reach an extended
+    neighbour as ONE message, a neighbour that has not shown the capability mark one by one."""
+    nodes = _nodes(3, protocol)
+    got = {1: [], 2: []}
+    try:
+        from p2pfl_b200.commands.command import Command
+
+        class Metrics(Command):
+            def __init__(self, who):
+                self.who = who
+
+            @staticmethod
+            def get_name():
+                return "metrics"
+
+            def execute(self, source, round, *args, **kw):
+                got[self.who].append(("metrics", round, args))
+
+        class Ready(Metrics):
+            @staticmethod
+            def get_name():
+                return "models_ready"
+
+            def execute(self, source, round, *args, **kw):
+                got[self.who].append(("models_ready", round, args))
+
+        for i in (1, 2):
+            nodes[i]._communication_protocol.add_command([Metrics(i), Ready(i)])
+        nodes[0].connect(nodes[1].addr)
+        nodes[0].connect(nodes[2].addr)
+        wait_convergence(nodes[:1], 2, only_direct=True)
+        proto = nodes[0]._communication_protocol
+        deadline = time.time() + 5
+        while len(proto._extended) < 2 and time.time() < deadline:
+            time.sleep(0.01)
+        proto._extended.discard(nodes[2].addr)  # node 2 plays a reference node
+        sent = []
+        real = proto._transport.deliver_many
+
+        def spy(targets, env):
+            sent.extend((t[0], env.cmd) for t in targets)
+            return real(targets, env)
+
+        proto._transport.deliver_many = spy
+        proto.broadcast_async(proto.build_msg("models_ready", [], round=4), lazy=True)
+        proto.broadcast_async(proto.build_msg("metrics", ["test_loss", "0.5"], round=5), lazy=True)
+        time.sleep(Settings.BUNDLE_LINGER / 4)
+        assert not got[1] and not got[2]  # still waiting for company
+        proto.broadcast_async(proto.build_msg("metrics", ["test_metric", "0.9"], round=5))
+        deadline = time.time() + 5
+        while (len(got[1]) < 3 or len(got[2]) < 3) and time.time() < deadline:
+            time.sleep(0.01)
+        want = [("models_ready", 4, ()), ("metrics", 5, ("test_loss", "0.5")), ("metrics", 5, ("test_metric", "0.9"))]
+        assert got[1] == want and got[2] == want
+        mine = [c for n, c in sent if c != "beat" and c != "neighbors_hint"]
+        assert sorted(c for n, c in sent if n == nodes[1].addr and c in mine) == ["bundle"]
+        assert sorted(c for n, c in sent if n == nodes[2].addr and c in mine) == ["metrics", "metrics", "models_ready"]
+        # a lone lazy broadcast leaves by itself after the linger
+        proto.broadcast_async(proto.build_msg("models_ready", [], round=6), lazy=True)
+        deadline = time.time() + 5
+        while len(got[1]) < 4 and time.time() < deadline:
+            time.sleep(0.01)
+        assert got[1][-1] == ("models_ready", 6, ())
+    finally:
+        _stop(nodes)

@@ -488,3 +488,18 @@ def test_gemm_grouped_conv_backward_pair(ops):
     ref_d = dz.float() @ w.float()
     assert torch.allclose(gw, ref_w, atol=2e-2, rtol=1e-2), (gw - ref_w).abs().max().item()
     assert torch.allclose(dcol.float(), ref_d, atol=2e-2, rtol=2e-2), (dcol.float() - ref_d).abs().max().item()
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True)])
+def test_gemm_persistent_with_mn_major_operands(ops, a_mn, b_mn):
+    """Many more tiles than SMs (the layer-1 data gradient: M = pixels, K = Cout = 64)."""
+    torch.manual_seed(9)
+    M, N, K = 65536, 576, 64
+    A = (torch.randn(M, K, device=DEV) / 8).to(torch.bfloat16)
+    W = torch.randn(K, N, device=DEV).to(torch.bfloat16)  # [K, N]: MN-major B
+    a_op, lda = (A.t().contiguous(), M) if a_mn else (A, K)
+    out = torch.zeros(M, N, device=DEV, dtype=torch.bfloat16)
+    ops.gemm_tn(a_op, lda, W, N, M, N, K, out_bf16=out, ld_bf16=N, a_mn=a_mn, b_mn=b_mn)
+    torch.cuda.synchronize()
+    ref = A.float() @ W.float()
+    assert torch.allclose(out.float(), ref, atol=3e-2, rtol=2e-2), (out.float() - ref).abs().max().item()
