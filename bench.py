@@ -199,6 +199,8 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
                 marks["launch0"] = ops.launch_count()
                 lr = node.state.learner
                 marks["h2d0"], marks["d2h0"] = lr.h2d_bytes, lr.d2h_bytes
+                marks["tim0"] = dict(node.live_timings)
+                marks["ht0"] = dict(getattr(node.state.learner, "host_seconds", {}))
                 marks["t0"] = time.perf_counter()
                 marks["e0"] = torch.cuda.Event(enable_timing=True)
                 marks["e0"].record(torch.cuda.current_stream())
@@ -209,6 +211,8 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
                 marks["e1"].record(torch.cuda.current_stream())
                 torch.cuda.synchronize()
                 marks["t1"] = time.perf_counter()
+                marks["tim1"] = dict(node.live_timings)
+                marks["ht1"] = dict(getattr(lr, "host_seconds", {}))
                 marks["launch1"] = ops.launch_count()
                 marks["h2d1"], marks["d2h1"] = lr.h2d_bytes, lr.d2h_bytes
                 if world > 1:
@@ -237,10 +241,19 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        trace_dir = os.environ.get("P2PFL_BENCH_TRACE")
+        if trace_dir:
+            # per-rank host timeline of the timed region (ms per round), for scaling analysis
+            os.makedirs(trace_dir, exist_ok=True)
+            per = {k: round((v - marks.get("tim0", {}).get(k, 0.0)) * 1e3 / K, 3) for k, v in marks.get("tim1", {}).items()}
+            per.update({k: round((v - marks.get("ht0", {}).get(k, 0.0)) * 1e3 / K, 3) for k, v in marks.get("ht1", {}).items()})
+            per["device_ms_per_round"] = round(ms / K, 3)
+            with open(os.path.join(trace_dir, f"stage_{data_mode}_rank{rank}.json"), "w") as fh:
+                json.dump(per, fh)
         return {
             "ms": float(t[0]), "wall_ms": float(t[1]), "launches": int(cnt[0]),
             "h2d": float(cnt[1]), "d2h": float(cnt[2]), "clocks": marks.get("clocks"),
-            "timings": dict(node.last_timings),
+            "timings": {k: v - marks.get("tim0", {}).get(k, 0.0) for k, v in marks.get("tim1", {}).items()},
         }  # fmt: skip
 
     dev = measure("resident")
@@ -293,7 +306,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         },
         "gpu_launches": dev["launches"],
         "wall_ms_per_step": dev["wall_ms"] / K,
-        "stage_seconds_rank0": {k: round(v, 4) for k, v in dev["timings"].items() if not k.startswith("stage:")},
+        "stage_ms_per_step_rank0": {k: round(v * 1e3 / K, 3) for k, v in dev["timings"].items()},
     }
     if world > 1:
         dist.barrier()

@@ -21,6 +21,7 @@ Models without a fused spec fall back to eager autograd for forward/backward
 from __future__ import annotations
 
 import threading
+import time
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -112,6 +113,7 @@ class B200Learner(TorchLearner):
         self.fused = False
         self._layers = []
         self.cnn = None
+        self.host_seconds: Dict[str, float] = {}  # where the host thread spends a fit (perm upload / launch / sync)
         self._tdescs = []
         if getattr(self.model, "fused_spec", None) == "cnn":
             from p2pfl_b200.learning.b200_cnn import CnnPlan
@@ -427,6 +429,7 @@ class B200Learner(TorchLearner):
         ep: Dict[str, Any] = {"n": n, "B": B, "nb": nb}
         ep["perm"] = torch.arange(n, dtype=torch.int32, device=dev)
         ep["perm_host"] = torch.empty(n, dtype=torch.int32).pin_memory()
+        ep["perm_host2"] = torch.empty(n, dtype=torch.int32).pin_memory()
         ep["xs"] = torch.zeros(nb * B, feat, dtype=torch.bfloat16, device=dev)
         # the MLP's first wgrad GEMM wants each batch transposed as well; the CNN does not
         need_t = self.cnn is None
@@ -489,14 +492,33 @@ class B200Learner(TorchLearner):
                     break
                 # host RNG: the CUDA generator cannot be used while another node's
                 # thread captures a graph on this device
-                ep["perm_host"].copy_(torch.randperm(n, dtype=torch.int32))
+                ta = time.perf_counter()
+                if not ep.get("perm_ready"):
+                    ep["perm_host"].copy_(torch.randperm(n, dtype=torch.int32))
                 ep["perm"].copy_(ep["perm_host"], non_blocking=True)
+                up = torch.cuda.Event()
+                up.record()
                 self.h2d_bytes += n * 4
+                tb = time.perf_counter()
                 ep["graph"].replay()
                 ops.add_launches(ep["launches"])
                 self.kernel_launches_per_epoch = ep["launches"]
+                # the next epoch's shuffle is drawn while the device runs this one (the upload above
+                # is done with the first pinned buffer before anything waits on the stream again)
+                ep["perm_host"], ep["perm_host2"] = ep["perm_host2"], ep["perm_host"]
+                if ep.get("perm_up2") is not None:
+                    ep["perm_up2"].synchronize()  # the upload that last read this buffer (long done)
+                ep["perm_up2"] = up
+                ep["perm_host"].copy_(torch.randperm(n, dtype=torch.int32))
+                ep["perm_ready"] = True
+                tc = time.perf_counter()
                 # per-epoch validation, as Lightning does for the reference (mlp.py:82-91)
                 val = self._eval_split("val")
+                td = time.perf_counter()
+                ht = self.host_seconds
+                ht["fit_perm"] = ht.get("fit_perm", 0.0) + tb - ta
+                ht["fit_replay_call"] = ht.get("fit_replay_call", 0.0) + tc - tb
+                ht["fit_val_sync"] = ht.get("fit_val_sync", 0.0) + td - tc
                 if val is not None:
                     logger.log_metric(self.addr, "val_loss", val[0], step=(e + 1) * ep["nb"])
                     logger.log_metric(self.addr, "val_metric", val[1], step=(e + 1) * ep["nb"])

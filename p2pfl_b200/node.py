@@ -80,6 +80,7 @@ class Node:
         self._learning_thread: Optional[threading.Thread] = None
         self.__running = False
         self.last_timings: Dict[str, float] = {}
+        self.live_timings: Dict[str, float] = {}
 
         self._communication_protocol.add_command(
             [
@@ -228,6 +229,7 @@ class Node:
             early_stopping_fn=lambda: self.state.round is None,
             learner_kwargs=self.learner_kwargs,
         )
+        self.live_timings = ctx.timings  # the running experiment's stage timers (read-only for observers)
         try:
             workflow.run(ctx)
         except Exception as e:
