@@ -18,6 +18,7 @@
 // Operands are both K-major ("TN"); callers keep activations in both
 // orientations instead (see learning/b200_learner.py), which keeps every GEMM
 // of the train step on this one kernel.
+#include <cstdlib>
 #include <cuda.h>
 #include <string.h>
 
@@ -165,31 +166,69 @@ __device__ __forceinline__ uint32_t make_idesc(uint32_t bn, uint32_t mn = 0) {
 
 // Drain one 128 x bn accumulator tile: TMEM -> registers -> fused epilogue -> global.
 // Called by the four epilogue warps; `q` is the warp's TMEM lane quarter.
-__device__ __forceinline__ void epilogue_tile(const Epilogue& ep, int M, int N, int m0, int n0, uint32_t bn,
-                                              uint32_t tmem_base, int q, int lane, bool single_n_tile) {
+__device__ __forceinline__ void epilogue_tile(const Epilogue& ep_mem, int M, int N, int m0, int n0, uint32_t bn,
+                                              uint32_t tmem_base, int q, int lane, bool single_n_tile,
+                                              long long* dbg = nullptr) {
+  // by value: read through the reference (shared or constant memory), every field would be
+  // reloaded after each global store - the stores might alias it as far as the compiler knows
+  const Epilogue ep = ep_mem;
   const int m = m0 + q * 32 + lane;
+#define EPI_STAMP(slot) \
+  if (dbg && lane == 0) dbg[slot] = clock64()
+  EPI_STAMP(0);
   const float bias_row = (ep.bias && ep.bias_per_row && m < M) ? ep.bias[m] : 0.f;
+  if (dbg && bias_row == 123456.f) dbg[7] = 1;  // (forces the load to complete before the next stamp)
+  EPI_STAMP(1);
 #pragma unroll 1
   for (int c = 0; c < (int)bn / 32; ++c) {
     const int nb = n0 + c * 32;
     if (nb >= N) break;
     uint32_t r[32];
     tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), r);
+    EPI_STAMP(2);
+    // the option tests stay OUTSIDE the element loops: inside, each becomes a branch per element
     float x[32];
+    if (ep.bias && !ep.bias_per_row) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      float v = __uint_as_float(r[j]) * ep.alpha;
-      if (ep.bias) v += ep.bias_per_row ? bias_row : ((nb + j < N) ? ep.bias[nb + j] : 0.f);
-      if (ep.relu) v = fmaxf(v, 0.f);
-      x[j] = v;
+      for (int j = 0; j < 32; ++j) x[j] = (nb + j < N) ? __ldg(ep.bias + nb + j) : 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) x[j] = fmaf(__uint_as_float(r[j]), ep.alpha, x[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) x[j] = fmaf(__uint_as_float(r[j]), ep.alpha, bias_row);
+    }
+    if (ep.relu) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
     }
     if (ep.mask && m < M) {
       const __nv_bfloat16* mk = ep.mask + (size_t)m * ep.ld_mask + nb;
+      if ((N - nb) >= 32 && ((reinterpret_cast<uintptr_t>(mk) & 15) == 0)) {
+        // the row's 32 mask values as four 16-byte loads, all in flight together
+        uint4 mv[4];
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (nb + j < N && !(__bfloat162float(mk[j]) > 0.f)) x[j] = 0.f;
+        for (int v = 0; v < 4; ++v) mv[v] = *reinterpret_cast<const uint4*>(mk + v * 8);
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          const uint32_t w[4] = {mv[v].x, mv[v].y, mv[v].z, mv[v].w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            if (!(__uint_as_float(w[k] << 16) > 0.f)) x[v * 8 + 2 * k] = 0.f;
+            if (!(__uint_as_float(w[k] & 0xFFFF0000u) > 0.f)) x[v * 8 + 2 * k + 1] = 0.f;
+          }
+        }
+      } else {
+        float mf[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) mf[j] = (nb + j < N) ? __bfloat162float(mk[j]) : 1.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (!(mf[j] > 0.f)) x[j] = 0.f;
+      }
     }
     const int valid = (N - nb) < 32 ? (N - nb) : 32;
+    if (dbg && x[0] == 123456.f) dbg[7] = 2;
+    EPI_STAMP(3);
     if (m < M) {
       if (ep.rowsum) {
         float s = 0.f;
@@ -244,19 +283,34 @@ __device__ __forceinline__ void epilogue_tile(const Epilogue& ep, int M, int N, 
             if (j < valid) o[j] = __float2bfloat16_rn(x[j]);
         }
       }
+      EPI_STAMP(4);
       // transposed outputs: consecutive lanes hold consecutive m -> coalesced per column
       if (ep.out_f32_t) {
+        float* o = ep.out_f32_t + (size_t)nb * ep.ld_f32_t + m;
+        if (valid == 32) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (j < valid) ep.out_f32_t[(size_t)(nb + j) * ep.ld_f32_t + m] = x[j];
+          for (int j = 0; j < 32; ++j) o[(size_t)j * ep.ld_f32_t] = x[j];
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < valid) o[(size_t)j * ep.ld_f32_t] = x[j];
+        }
       }
       if (ep.out_bf16_t) {
+        __nv_bfloat16* o = ep.out_bf16_t + (size_t)nb * ep.ld_bf16_t + m;
+        if (valid == 32) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (j < valid) ep.out_bf16_t[(size_t)(nb + j) * ep.ld_bf16_t + m] = __float2bfloat16_rn(x[j]);
+          for (int j = 0; j < 32; ++j) o[(size_t)j * ep.ld_bf16_t] = __float2bfloat16_rn(x[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < valid) o[(size_t)j * ep.ld_bf16_t] = __float2bfloat16_rn(x[j]);
+        }
       }
+      EPI_STAMP(5);
     }
   }
+#undef EPI_STAMP
 }
 
 constexpr int kMaxGroup = 4;
@@ -722,49 +776,178 @@ namespace {
 
 constexpr int kChainMaxGemm = 8;
 constexpr int kChainMaxPhases = 12;
+// N-tile width.  The kernel carries a width per GEMM (chain_bn_for), but measured on B200 a
+// 128-wide tile for the weight-gradient link was slower than 32-wide ones (the epilogue's first
+// TMEM load stalled ~3 us behind the next tile's MMAs), so every link uses 32 columns.
 constexpr uint32_t kChainBN = 32;
-constexpr uint32_t kChainStageBytes = kTileABytes + kChainBN * BK * 2;  // 20 KB
+constexpr uint32_t kChainMaxBN = 32;
+constexpr uint32_t kChainStageBytes = kTileABytes + kChainMaxBN * BK * 2;  // 20 KB
 constexpr int kChainStages = 9;
+__host__ __device__ __forceinline__ int chain_bn_for(int N) { return N >= 128 ? (int)kChainMaxBN : (int)kChainBN; }
+
+// Everything but the tensor maps.  The kernel copies this block from the parameter (constant)
+// space to shared memory once, all threads at once: read in place, every first touch of a
+// constant line is a ~0.5 us miss and the links would pay them one after the other.
+struct ChainScalars {
+  Epilogue ep[kChainMaxGemm];
+  int32_t M[kChainMaxGemm], N[kChainMaxGemm], K[kChainMaxGemm];
+  int32_t tiles_n[kChainMaxGemm], tiles[kChainMaxGemm], num_kb[kChainMaxGemm];  // host-computed: no divisions per tile
+  int32_t a_rows[kChainMaxGemm];  // rows of the A box: min(128, M rounded up to 8) - TMA time is per row, valid or not
+  int32_t kind[kChainMaxPhases];  // 0 = GEMM(s), 1 = softmax cross-entropy
+  int32_t idx[kChainMaxPhases];
+  int32_t cnt[kChainMaxPhases];   // GEMM link: idx .. idx+cnt-1 are independent and share the link
+  int32_t n_phases;
+  p2pfl_ce_args ce;
+  long long* stamps;  // bring-up aid (nullable): [link][8] SM-clock stamps of CTA 0, see p2pfl_gemm_chain_set_stamps
+};
+static_assert(sizeof(ChainScalars) % 4 == 0, "copied word by word");
 
 struct ChainArgs {
   CUtensorMap ma[kChainMaxGemm];
   CUtensorMap mb[kChainMaxGemm];
-  Epilogue ep[kChainMaxGemm];
-  int32_t M[kChainMaxGemm], N[kChainMaxGemm], K[kChainMaxGemm];
-  int32_t kind[kChainMaxPhases];  // 0 = GEMM, 1 = softmax cross-entropy
-  int32_t idx[kChainMaxPhases];
-  int32_t n_phases;
-  p2pfl_ce_args ce;
+  ChainScalars sc;
 };
 
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_release_acquire() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// tile `t` of a link that spans GEMMs gi0 .. gi0+cnt-1 -> (GEMM, m0, n0, its k-block count)
+struct ChainTile {
+  int gi, m0, n0, num_kb, bn, a_rows;
+};
+__device__ __forceinline__ int chain_tiles_of(const ChainScalars& g, int gi) { return g.tiles[gi]; }
+__device__ __forceinline__ ChainTile chain_locate(const ChainScalars& g, int gi0, int cnt, int t) {
+  int gi = gi0;
+  for (int j = 0; j + 1 < cnt; ++j) {
+    const int n = chain_tiles_of(g, gi);
+    if (t < n) break;
+    t -= n;
+    ++gi;
+  }
+  const int bn = chain_bn_for(g.N[gi]);
+  const int tiles_n = g.tiles_n[gi];
+  const int tm = tiles_n == 1 ? t : t / tiles_n;
+  ChainTile ct;
+  ct.gi = gi;
+  ct.bn = bn;
+  ct.m0 = tm * BM;
+  ct.n0 = (t - tm * tiles_n) * bn;
+  ct.num_kb = g.num_kb[gi];
+  ct.a_rows = g.a_rows[gi];
+  return ct;
+}
+
 // log-softmax + cross-entropy forward/backward by the 128 epilogue threads (one warp per row)
-__device__ void chain_ce(const p2pfl_ce_args& a, int ewarp, int lane, float* s_db) {
+// `scratch`: idle shared memory (the stage ring between links) for B * (C + 1) words, or null.
+// Staging the logits there costs ONE round trip to L2; read in place, every row pays three.
+__device__ void chain_ce(const p2pfl_ce_args& a_mem, int ewarp, int lane, float* s_db, float* scratch, bool small,
+                         long long* dbg = nullptr) {
+#define CE_STAMP(slot) \
+  if (dbg && ewarp == 0 && lane == 0) dbg[slot] = clock64()
+  CE_STAMP(0);
+  const p2pfl_ce_args a = a_mem;  // by value, for the same reason as in epilogue_tile
   const int et = ewarp * 32 + lane;
   const int C = a.C, B = a.B;
   for (int c = et; c < C; c += 128) s_db[c] = 0.f;
+  int* s_lab = reinterpret_cast<int*>(scratch + (size_t)B * C);
+  if (scratch && !small) {
+    for (int i = et; i < B * C; i += 128) scratch[i] = __ldcg(a.logits + (size_t)(i / C) * a.ld_logits + (i % C));
+    for (int i = et; i < B; i += 128) s_lab[i] = a.labels[i];
+  }
   asm volatile("bar.sync 1, 128;" ::: "memory");
   const float inv_b = 1.f / (float)B;
   float wloss = 0.f;
   __nv_bfloat16* dl = reinterpret_cast<__nv_bfloat16*>(a.dlogits_bf16);
   __nv_bfloat16* dlt = reinterpret_cast<__nv_bfloat16*>(a.dlogits_t_bf16);
+  if (scratch && small) {
+    // few classes, at most 128 rows.  Three short phases, each with all the parallelism there is:
+    //   (1) all 128 threads stage logits + labels in shared memory (one trip to L2),
+    //   (2) one thread per row: max / sum-exp over its C classes -> log-sum-exp, loss,
+    //   (3) all threads: one gradient element each (both orientations + a staged copy),
+    // then C threads sum the staged gradients into the bias gradient.
+    float* xs = scratch;                                   // [B, C]
+    int* lab = reinterpret_cast<int*>(scratch + B * C);    // [B]
+    float* s_lse = scratch + B * C + B;                    // [B]
+    float* gs = s_lse + B;                                 // [B, C]
+    for (int i = et; i < B * C; i += 128) xs[i] = __ldcg(a.logits + (size_t)(i / C) * a.ld_logits + (i % C));
+    for (int i = et; i < B; i += 128) lab[i] = a.labels[i];
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    CE_STAMP(1);
+    float loss_row = 0.f;
+    if (et < B) {
+      const float* xr = xs + et * C;
+      float mx = -INFINITY;
+      for (int c = 0; c < C; ++c) mx = fmaxf(mx, xr[c]);
+      float se = 0.f;
+      for (int c = 0; c < C; ++c) se += __expf(xr[c] - mx);
+      const float lse = mx + __logf(se);
+      s_lse[et] = lse;
+      const int y = lab[et];
+      if (y >= 0 && y < C) loss_row = lse - xr[y];
+    }
+    loss_row = warp_sum(loss_row);
+    if (a.loss_sum && lane == 0 && loss_row != 0.f) atomicAdd(a.loss_sum, loss_row);
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    CE_STAMP(2);
+    for (int i = et; i < B * C; i += 128) {
+      const int row = i / C, c = i - row * C;
+      const __nv_bfloat16 gb = __float2bfloat16_rn((__expf(xs[i] - s_lse[row]) - (c == lab[row] ? 1.f : 0.f)) * inv_b);
+      if (dl) dl[(size_t)row * a.ld_d + c] = gb;
+      if (dlt) dlt[(size_t)c * a.ld_dt + row] = gb;
+      gs[i] = __bfloat162float(gb);
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    CE_STAMP(3);
+    if (a.dbias)
+      for (int c = et; c < C; c += 128) {
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int r2 = 0;
+        for (; r2 + 4 <= B; r2 += 4) {
+          s0 += gs[(r2 + 0) * C + c];
+          s1 += gs[(r2 + 1) * C + c];
+          s2 += gs[(r2 + 2) * C + c];
+          s3 += gs[(r2 + 3) * C + c];
+        }
+        for (; r2 < B; ++r2) s0 += gs[r2 * C + c];
+        a.dbias[c] = (s0 + s1) + (s2 + s3);
+      }
+    CE_STAMP(4);
+    return;
+  }
+#undef CE_STAMP
   for (int row = ewarp; row < B; row += 4) {
-    const float* x = a.logits + (size_t)row * a.ld_logits;
+    // the logits may have been stored by another CTA of the cluster: never through L1
+    const float* xg = a.logits + (size_t)row * a.ld_logits;
+    const float* xs = scratch + (size_t)row * C;
+    auto X = [&](int c) { return scratch ? xs[c] : __ldcg(xg + c); };
     float mx = -INFINITY;
-    for (int c = lane; c < C; c += 32) mx = fmaxf(mx, x[c]);
+    for (int c = lane; c < C; c += 32) mx = fmaxf(mx, X(c));
     mx = warp_max(mx);
     float se = 0.f;
-    for (int c = lane; c < C; c += 32) se += __expf(x[c] - mx);
+    for (int c = lane; c < C; c += 32) se += __expf(X(c) - mx);
     se = warp_sum(se);
     const float lse = mx + __logf(se);
-    const int y = a.labels[row];
+    const int y = scratch ? s_lab[row] : a.labels[row];
     for (int c = lane; c < C; c += 32) {
-      const float g = (__expf(x[c] - lse) - (c == y ? 1.f : 0.f)) * inv_b;
+      const float g = (__expf(X(c) - lse) - (c == y ? 1.f : 0.f)) * inv_b;
       const __nv_bfloat16 gb = __float2bfloat16_rn(g);
       if (dl) dl[(size_t)row * a.ld_d + c] = gb;
       if (dlt) dlt[(size_t)c * a.ld_dt + row] = gb;
       atomicAdd(s_db + c, __bfloat162float(gb));
     }
-    if (lane == 0 && y >= 0 && y < C) wloss += lse - x[y];
+    if (lane == 0 && y >= 0 && y < C) wloss += lse - X(y);
   }
   asm volatile("bar.sync 1, 128;" ::: "memory");
   if (a.dbias)
@@ -773,7 +956,13 @@ __device__ void chain_ce(const p2pfl_ce_args& a, int ewarp, int lane, float* s_d
 }
 
 __global__ void __launch_bounds__(kThreadsGemm, 1)
-gemm_chain_kernel(const __grid_constant__ ChainArgs g) {
+gemm_chain_kernel(const __grid_constant__ ChainArgs ga) {
+  __shared__ ChainScalars g;  // see ChainScalars: one parallel copy instead of serial constant misses
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&ga.sc);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&g);
+    for (int i = threadIdx.x; i < (int)(sizeof(ChainScalars) / 4); i += kThreadsGemm) dst[i] = src[i];
+  }
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   __shared__ __align__(8) uint64_t full_bar[kChainStages];
@@ -787,10 +976,10 @@ gemm_chain_kernel(const __grid_constant__ ChainArgs g) {
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
-    for (int p = 0; p < g.n_phases; ++p)
-      if (g.kind[p] == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&g.ma[g.idx[p]])) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&g.mb[g.idx[p]])) : "memory");
+    for (int i = 0; i < kChainMaxGemm; ++i)
+      if (ga.sc.M[i] > 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&ga.ma[i])) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&ga.mb[i])) : "memory");
       }
     for (int s = 0; s < kChainStages; ++s) {
       mbar_init(smem_u32(&full_bar[s]), 1);
@@ -802,7 +991,7 @@ gemm_chain_kernel(const __grid_constant__ ChainArgs g) {
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), 64);
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), 2 * kChainMaxBN);
   pdl_launch_dependents();
   tc_fence_before();
   __syncthreads();
@@ -812,97 +1001,137 @@ gemm_chain_kernel(const __grid_constant__ ChainArgs g) {
 
   uint32_t it = 0;       // k-block counter over the whole chain (smem ring position)
   uint32_t tile_it = 0;  // output-tile counter over the whole chain (TMEM accumulator position)
-  const uint32_t idesc = make_idesc(kChainBN);
+  // launched as ONE thread-block cluster: the tiles of a link are dealt round-robin to the CTAs,
+  // links are separated by the hardware cluster barrier (release / acquire)
+  const int crank = (int)cluster_ctarank(), csize = (int)cluster_nctarank();
 
+  long long* const stamps = (g.stamps && crank == 0) ? g.stamps : nullptr;
+#define CHAIN_STAMP(slot) \
+  if (stamps && lane == 0) stamps[p * 8 + (slot)] = clock64()
   for (int p = 0; p < g.n_phases; ++p) {
+    if (threadIdx.x == 0) CHAIN_STAMP(0);
     if (g.kind[p] == 0) {
-      const int gi = g.idx[p];
-      const int M = g.M[gi], N = g.N[gi], K = g.K[gi];
-      const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + (int)kChainBN - 1) / (int)kChainBN;
-      const int num_kb = (K + BK - 1) / BK;
-      const int n_tiles = tiles_m * tiles_n;
+      const int gi0 = g.idx[p], cnt = g.cnt[p] > 0 ? g.cnt[p] : 1;
+      int n_tiles = 0;
+      for (int j = 0; j < cnt; ++j) n_tiles += chain_tiles_of(g, gi0 + j);
+      // what this CTA will do in this link (every role advances the ring / accumulator counters alike)
+      uint32_t my_tiles = 0, my_kb = 0;
+      for (int t = crank; t < n_tiles; t += csize) {
+        ++my_tiles;
+        my_kb += (uint32_t)chain_locate(g, gi0, cnt, t).num_kb;
+      }
       if (warp == 0) {
         // ---------------- TMA producer ----------------
         if (elect_one()) {
-          uint32_t lit = it;  // every lane of the warp advances `it` below, whoever is elected
-          for (int t = 0; t < n_tiles; ++t) {
-            const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * (int)kChainBN;
-            for (int kb = 0; kb < num_kb; ++kb, ++lit) {
+          uint32_t lit = it;
+          for (int t = crank; t < n_tiles; t += csize) {
+            const ChainTile ct = chain_locate(g, gi0, cnt, t);
+            for (int kb = 0; kb < ct.num_kb; ++kb, ++lit) {
               const uint32_t s = lit % kChainStages, ph = (lit / kChainStages) & 1u;
               mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
               const uint32_t bar = smem_u32(&full_bar[s]);
-              mbar_expect_tx(bar, kChainStageBytes);
+              mbar_expect_tx(bar, (uint32_t)(ct.a_rows + ct.bn) * BK * 2);
               const uint32_t dst = smem_u32(smem + (size_t)s * kChainStageBytes);
-              tma_load_2d(&g.ma[gi], bar, dst, kb * BK, m0);
-              tma_load_2d(&g.mb[gi], bar, dst + kTileABytes, kb * BK, n0);
+              tma_load_2d(&ga.ma[ct.gi], bar, dst, kb * BK, ct.m0);
+              tma_load_2d(&ga.mb[ct.gi], bar, dst + kTileABytes, kb * BK, ct.n0);
             }
           }
         }
         __syncwarp();
       } else if (warp == 1) {
         // ---------------- MMA issuer ----------------
-        for (int t = 0; t < n_tiles; ++t, ++tile_it) {
-          const uint32_t acc = tile_it & 1u, aph = (tile_it >> 1) & 1u;
+        uint32_t lit = it, ltile = tile_it;
+        for (int t = crank; t < n_tiles; t += csize, ++ltile) {
+          const ChainTile ct = chain_locate(g, gi0, cnt, t);
+          const uint32_t idesc = make_idesc((uint32_t)ct.bn);
+          const uint32_t acc = ltile & 1u, aph = (ltile >> 1) & 1u;
           mbar_wait(smem_u32(&tmem_empty_bar[acc]), aph ^ 1u);  // epilogue drained this accumulator
           tc_fence_after();
-          for (int kb = 0; kb < num_kb; ++kb, ++it) {
-            const uint32_t s = it % kChainStages, ph = (it / kChainStages) & 1u;
+          for (int kb = 0; kb < ct.num_kb; ++kb, ++lit) {
+            const uint32_t s = lit % kChainStages, ph = (lit / kChainStages) & 1u;
             mbar_wait(smem_u32(&full_bar[s]), ph);
             tc_fence_after();
+            if (kb == 0 && t == crank) CHAIN_STAMP(1);  // first operands landed
             if (elect_one()) {
               const uint32_t a_addr = smem_u32(smem + (size_t)s * kChainStageBytes);
               const uint64_t da = make_smem_desc(a_addr);
               const uint64_t db = make_smem_desc(a_addr + kTileABytes);
 #pragma unroll
               for (int k = 0; k < BK / 16; ++k)
-                umma_bf16(tmem_base + acc * kChainBN, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                umma_bf16(tmem_base + acc * kChainMaxBN, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
                           (kb | k) != 0 ? 1u : 0u);
               umma_commit(smem_u32(&empty_bar[s]));
-              if (kb == num_kb - 1) umma_commit(smem_u32(&tmem_full_bar[acc]));
+              if (kb == ct.num_kb - 1) umma_commit(smem_u32(&tmem_full_bar[acc]));
             }
             __syncwarp();
           }
+          CHAIN_STAMP(2);  // this tile's MMAs issued
         }
       } else {
         // ---------------- epilogue ----------------
         const int q = warp & 3;
-        for (int t = 0; t < n_tiles; ++t, ++tile_it) {
-          const uint32_t acc = tile_it & 1u, aph = (tile_it >> 1) & 1u;
-          const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * (int)kChainBN;
+        uint32_t ltile = tile_it;
+        for (int t = crank; t < n_tiles; t += csize, ++ltile) {
+          const ChainTile ct = chain_locate(g, gi0, cnt, t);
+          const uint32_t acc = ltile & 1u, aph = (ltile >> 1) & 1u;
           mbar_wait(smem_u32(&tmem_full_bar[acc]), aph);
           tc_fence_after();
-          epilogue_tile(g.ep[gi], M, N, m0, n0, kChainBN, tmem_base + acc * kChainBN, q, lane, tiles_n == 1);
+          if (warp == 2 && t == crank) CHAIN_STAMP(3);  // first accumulator complete
+          epilogue_tile(g.ep[ct.gi], g.M[ct.gi], g.N[ct.gi], ct.m0, ct.n0, (uint32_t)ct.bn, tmem_base + acc * kChainMaxBN, q,
+                        lane, g.N[ct.gi] <= ct.bn, (stamps && warp == 2 && t == crank) ? stamps + 96 + p * 8 : nullptr);
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(smem_u32(&tmem_empty_bar[acc]));
         }
+        if (warp == 2) CHAIN_STAMP(4);  // stores issued
       }
-      // the roles that did not iterate still advance the shared counters
-      if (warp == 0) tile_it += n_tiles;
-      if (warp != 1) it += (uint32_t)(n_tiles * num_kb);
-    } else if (warp >= 2) {
-      chain_ce(g.ce, warp - 2, lane, s_db);
+      tile_it += my_tiles;
+      it += my_kb;
+    } else if (warp >= 2 && crank == 0) {
+      const bool fits = (size_t)g.ce.B * (2 * g.ce.C + 2) * 4 <= (size_t)kChainStages * kChainStageBytes;
+      chain_ce(g.ce, warp - 2, lane, s_db, fits ? reinterpret_cast<float*>(smem) : nullptr, g.ce.B <= 128 && g.ce.C <= 64,
+               stamps ? stamps + 96 + p * 8 : nullptr);
     }
-    // ---- link boundary: this link's global stores (generic proxy) must be visible to the
-    // next link's TMA loads (async proxy) and to its plain loads
-    __threadfence();
-    asm volatile("fence.proxy.async;" ::: "memory");
-    __syncthreads();
+    // ---- link boundary: this link's global stores (generic proxy, possibly another CTA's) must
+    // be visible to the next link's TMA loads (async proxy) and to its plain loads
+    // (the cluster barrier's release / acquire pair orders the stores at cluster scope itself)
+    if (csize == 1) __threadfence();
+    if (warp >= 2) asm volatile("fence.proxy.async.global;" ::: "memory");  // the threads that stored
+    if (warp == 2) CHAIN_STAMP(5);  // fences done
+    if (csize > 1) cluster_sync_release_acquire();
+    else __syncthreads();
+    if (warp == 0) asm volatile("fence.proxy.async.global;" ::: "memory");  // the thread that issues TMA loads
+    if (warp == 2) CHAIN_STAMP(6);  // barrier passed
   }
+#undef CHAIN_STAMP
 
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 64);
+    tmem_dealloc(tmem_base, 2 * kChainMaxBN);
   }
 }
 
 }  // namespace
 
+static long long* g_chain_stamps = nullptr;
+extern "C" int p2pfl_gemm_chain_set_stamps(void* device_buffer) {
+  g_chain_stamps = reinterpret_cast<long long*>(device_buffer);
+  return 0;
+}
+
 extern "C" int p2pfl_gemm_chain(int device, void* stream, const p2pfl_gemm_args* gemms, int n_gemm,
                                 const int32_t* phase_kind, const int32_t* phase_idx, int n_phases,
                                 const p2pfl_ce_args* ce) {
+  return p2pfl_gemm_chain_cluster(device, stream, gemms, n_gemm, phase_kind, phase_idx, nullptr, n_phases, ce, 1);
+}
+
+extern "C" int p2pfl_gemm_chain_cluster(int device, void* stream, const p2pfl_gemm_args* gemms, int n_gemm,
+                                        const int32_t* phase_kind, const int32_t* phase_idx, const int32_t* phase_cnt,
+                                        int n_phases, const p2pfl_ce_args* ce, int cluster_ctas) {
+  P2PFL_REQUIRE(cluster_ctas >= 1 && cluster_ctas <= 16 && (cluster_ctas & (cluster_ctas - 1)) == 0,
+                "the chain runs as one cluster of 1, 2, 4, 8 or 16 CTAs");
   P2PFL_REQUIRE(n_gemm >= 0 && n_gemm <= kChainMaxGemm && n_phases >= 1 && n_phases <= kChainMaxPhases,
                 "a GEMM chain takes at most 8 GEMMs in at most 12 links");
   P2PFL_REQUIRE(phase_kind && phase_idx, "null phase list");
@@ -916,25 +1145,36 @@ extern "C" int p2pfl_gemm_chain(int device, void* stream, const p2pfl_gemm_args*
     P2PFL_REQUIRE((a.split_k == 0 || a.split_k == 1) && a.mn_major == 0, "chain links are plain K-major GEMMs without split-K");
     memset(&tmp, 0, sizeof(tmp));
     if (int rc = fill_problem(tmp, 0, a)) return rc;
-    g.ma[i] = tmp.ma[0];
-    if (int rc = make_map(&g.mb[i], a.B, a.N, a.K, a.ldb, (int)kChainBN)) return rc;  // chain tiles N by 32
-    g.ep[i] = tmp.ep[0];
-    g.M[i] = a.M;
-    g.N[i] = a.N;
-    g.K[i] = a.K;
+    // a batch-major link has M = batch rows: fetch only those (the MMA still multiplies 128 rows, the
+    // rest of the tile holds whatever was there and lands in accumulator rows nobody stores)
+    const int a_rows = a.M >= BM ? BM : (a.M + 7) / 8 * 8;
+    g.sc.a_rows[i] = a_rows;
+    if (int rc = make_map(&g.ma[i], a.A, a.M, a.K, a.lda, a_rows)) return rc;
+    if (int rc = make_map(&g.mb[i], a.B, a.N, a.K, a.ldb, chain_bn_for(a.N))) return rc;  // the chain's own N tiling
+    g.sc.ep[i] = tmp.ep[0];
+    g.sc.M[i] = a.M;
+    g.sc.N[i] = a.N;
+    g.sc.K[i] = a.K;
+    const int cbn = chain_bn_for(a.N);
+    g.sc.tiles_n[i] = (a.N + cbn - 1) / cbn;
+    g.sc.tiles[i] = ((a.M + BM - 1) / BM) * g.sc.tiles_n[i];
+    g.sc.num_kb[i] = (a.K + BK - 1) / BK;
   }
   bool has_ce = false;
   for (int p = 0; p < n_phases; ++p) {
     P2PFL_REQUIRE(phase_kind[p] == 0 || phase_kind[p] == 1, "unknown link kind");
-    P2PFL_REQUIRE(phase_kind[p] == 1 || (phase_idx[p] >= 0 && phase_idx[p] < n_gemm), "link refers to a missing GEMM");
-    g.kind[p] = phase_kind[p];
-    g.idx[p] = phase_idx[p];
+    const int cnt = (phase_cnt && phase_kind[p] == 0 && phase_cnt[p] > 0) ? phase_cnt[p] : 1;
+    P2PFL_REQUIRE(phase_kind[p] == 1 || (phase_idx[p] >= 0 && phase_idx[p] + cnt <= n_gemm), "link refers to a missing GEMM");
+    g.sc.kind[p] = phase_kind[p];
+    g.sc.idx[p] = phase_idx[p];
+    g.sc.cnt[p] = cnt;
     has_ce |= phase_kind[p] == 1;
   }
-  g.n_phases = n_phases;
+  g.sc.n_phases = n_phases;
+  g.sc.stamps = g_chain_stamps;
   if (has_ce) {
     P2PFL_REQUIRE(ce && ce->logits && ce->labels && ce->B > 0 && ce->C > 0 && ce->C <= 256, "bad cross-entropy link");
-    g.ce = *ce;
+    g.sc.ce = *ce;
   }
   constexpr size_t smem = (size_t)kChainStages * kChainStageBytes + 1024;
   static bool attr_set[64] = {false};
@@ -942,6 +1182,31 @@ extern "C" int p2pfl_gemm_chain(int device, void* stream, const p2pfl_gemm_args*
     P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set[device] = true;
   }
-  P2PFL_CUDA_OK(launch_pdl(gemm_chain_kernel, dim3(1), dim3(kThreadsGemm), smem, as_stream(stream), g));
+  if (cluster_ctas > 8) {
+    static bool np_set[64] = {false};
+    if (device >= 0 && device < 64 && !np_set[device]) {
+      P2PFL_CUDA_OK(cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      np_set[device] = true;
+    }
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cluster_ctas);
+  cfg.blockDim = dim3(kThreadsGemm);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = as_stream(stream);
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)cluster_ctas;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  P2PFL_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_chain_kernel, g));
+  // bring-up aid: P2PFL_CHAIN_REPEAT=n relaunches the same chain n more times back to back (timing
+  // a warm instruction cache against a cold one); never set outside experiments
+  static const int repeat = [] { const char* e = getenv("P2PFL_CHAIN_REPEAT"); return e ? atoi(e) : 0; }();
+  for (int i = 0; i < repeat; ++i) P2PFL_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_chain_kernel, g));
   return 0;
 }

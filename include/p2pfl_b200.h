@@ -232,6 +232,19 @@ typedef struct {
 int p2pfl_gemm_chain(int device, void* stream, const p2pfl_gemm_args* gemms, int n_gemm,
                      const int32_t* link_kind /* 0 GEMM, 1 cross-entropy */, const int32_t* link_idx,
                      int n_links, const p2pfl_ce_args* ce);
+/* The same chain as ONE thread-block cluster of `cluster_ctas` CTAs (1, 2, 4, 8; 16 where the
+ * device allows it): the 128 x 32 tiles of a link are dealt round-robin to the CTAs and links
+ * are separated by the hardware cluster barrier.  `phase_cnt[p]` > 1 makes link p a group of
+ * independent GEMMs (gemms[idx] .. gemms[idx+cnt-1], e.g. every layer's weight gradient) whose
+ * tiles share the link.  No counterpart in the reference. */
+int p2pfl_gemm_chain_cluster(int device, void* stream, const p2pfl_gemm_args* gemms, int n_gemm,
+                             const int32_t* phase_kind, const int32_t* phase_idx,
+                             const int32_t* phase_cnt /* nullable */, int n_phases,
+                             const p2pfl_ce_args* ce, int cluster_ctas);
+/* Bring-up aid: while `device_buffer` (int64 [12][8], NULL = off) is set, every chain launch
+ * makes CTA 0 record SM-clock stamps per link: 0 link start, 1 first operands landed, 2 MMAs
+ * issued, 3 first accumulator complete, 4 epilogue stores issued, 5 fences done, 6 barrier passed. */
+int p2pfl_gemm_chain_set_stamps(void* device_buffer);
 
 /* ----------------------------------------------------------- convolution path
  * K6/K7 (cnn.py:78-81 Conv2d + ReLU + MaxPool2d through cuDNN/ATen) and the

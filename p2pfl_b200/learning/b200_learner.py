@@ -323,6 +323,9 @@ class B200Learner(TorchLearner):
         feat = Ls[0].in_f
         ldB = act["ldB"]
         C = Ls[-1].out_f
+        if Settings.MLP_CHAIN_CLUSTER > 0 and 3 * nL - 1 <= 8 and C <= 256 and bsz <= 32:
+            self._train_step_chain(x16, xT16, y, bsz, act, loss_slot, step_offset, lr, cluster=Settings.MLP_CHAIN_CLUSTER)
+            return
         if Settings.MLP_CHAIN and 2 * nL - 1 <= 8 and C <= 256:
             self._train_step_chain(x16, xT16, y, bsz, act, loss_slot, step_offset, lr)
             return
@@ -354,10 +357,12 @@ class B200Learner(TorchLearner):
         ops.adam_step_t(self.flat, self.grads, self.adam_m, self.adam_v, self.w16, lr, self.adam_step, step_offset,
                         self.wT16, self._tdescs)  # fmt: skip
 
-    def _train_step_chain(self, x16, xT16, y, bsz: int, act, loss_slot, step_offset: int, lr: float) -> None:
-        """Three launches per step: (1) ONE single-CTA kernel for every dependent link - the
-        forward chain, the loss and the dgrad chain; (2) all weight-gradient GEMMs, which
-        depend only on (1), as one grouped launch; (3) Adam + bf16 refresh + transposes."""
+    def _train_step_chain(self, x16, xT16, y, bsz: int, act, loss_slot, step_offset: int, lr: float, cluster: int = 0) -> None:
+        """``cluster`` = 0, three launches per step: (1) ONE single-CTA kernel for every dependent
+        link - the forward chain, the loss and the dgrad chain; (2) all weight-gradient GEMMs, which
+        depend only on (1), as one grouped launch; (3) Adam + bf16 refresh + transposes.
+        ``cluster`` > 0, two launches: (1) a thread-block cluster walks the same links and then all
+        weight gradients as one more link; (2) Adam."""
         Ls = self._layers
         nL = len(Ls)
         feat = Ls[0].in_f
@@ -370,7 +375,19 @@ class B200Learner(TorchLearner):
             last = li == nL - 1
             Bm, ldb = (x16, feat) if li == 0 else (act["H"][li - 1], _pad8(L.in_f))
             common = dict(bias=self.flat[L.b_off :], bias_per_row=True)
-            if last:
+            if cluster > 0:
+                # batch-major (D[bsz, out] = X . W^T): the N tiles of a link spread over the cluster's CTAs,
+                # and each streams a 32-row slice of W instead of 128 rows - the forward links are bound by
+                # what ONE SM can pull through TMA
+                colb = dict(bias=self.flat[L.b_off :], bias_per_row=False)
+                if last:
+                    gemms.append(ops.gemm_args(Bm, ldb, self.w16[L.w_off :], L.in_f, bsz, L.out_f, L.in_f,
+                                               out_f32=act["logits"], ld_f32=act["ld_logits"], **colb))  # fmt: skip
+                else:
+                    gemms.append(ops.gemm_args(Bm, ldb, self.w16[L.w_off :], L.in_f, bsz, L.out_f, L.in_f, relu=True,
+                                               out_bf16=act["H"][li], ld_bf16=_pad8(L.out_f), out_bf16_t=act["HT"][li],
+                                               ld_bf16_t=ldB, **colb))  # fmt: skip
+            elif last:
                 gemms.append(ops.gemm_args(self.w16[L.w_off :], L.in_f, Bm, ldb, L.out_f, bsz, L.in_f,
                                            out_f32_t=act["logits"], ld_f32_t=act["ld_logits"], **common))  # fmt: skip
             else:
@@ -389,14 +406,18 @@ class B200Learner(TorchLearner):
                 out_bf16_t=act["dZ"][li - 1] if li - 1 > 0 else None, ld_bf16_t=_pad8(P.out_f),
                 rowsum=self.grads[P.b_off :]))  # fmt: skip
             links.append(("gemm", len(gemms) - 1))
-        ops.gemm_chain(self.device, gemms, links, ce)
         wg = []
         for li, L in enumerate(Ls):  # wgrad: dW[out, in] = dZ^T[out, bsz] . (X^T[in, bsz])^T   (K = batch)
             Bm = xT16 if li == 0 else act["HT"][li - 1]
             wg.append(ops.gemm_args(act["dZT"][li], ldB, Bm, ldB, L.out_f, L.in_f, bsz,
                                     out_f32=self.grads[L.w_off :], ld_f32=L.in_f))  # fmt: skip
-        for i in range(0, len(wg), 4):
-            ops.gemm_tn_grouped(self.device, wg[i : i + 4])
+        if cluster > 0:
+            links.append(("group", len(gemms), len(wg)))
+            ops.gemm_chain(self.device, gemms + wg, links, ce, cluster=cluster)
+        else:
+            ops.gemm_chain(self.device, gemms, links, ce)
+            for i in range(0, len(wg), 4):
+                ops.gemm_tn_grouped(self.device, wg[i : i + 4])
         ops.adam_step_t(self.flat, self.grads, self.adam_m, self.adam_v, self.w16, lr, self.adam_step, step_offset,
                         self.wT16, self._tdescs)  # fmt: skip
 

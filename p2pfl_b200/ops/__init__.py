@@ -333,16 +333,21 @@ def ce_args(logits, ld_logits: int, labels, B: int, Cn: int, dlogits, ld_d: int,
     return CeArgs(g(logits), ld_logits, g(labels), B, Cn, g(dlogits), ld_d, g(dlogits_t), ld_dt, g(dbias), g(loss_sum))
 
 
-def gemm_chain(device: torch.device, gemms: Sequence[GemmArgs], links: Sequence[tuple], ce: Optional[CeArgs] = None) -> None:
-    """ONE launch for a list of dependent links: ``("gemm", i)`` runs ``gemms[i]``, ``("ce", 0)`` the
-    softmax-cross-entropy described by ``ce``; each link sees what the previous one stored."""
+def gemm_chain(device: torch.device, gemms: Sequence[GemmArgs], links: Sequence[tuple], ce: Optional[CeArgs] = None,
+               cluster: int = 1) -> None:
+    """ONE launch for a list of dependent links: ``("gemm", i)`` runs ``gemms[i]``, ``("group", i, n)``
+    runs the independent ``gemms[i:i+n]`` side by side, ``("ce", 0)`` the softmax-cross-entropy
+    described by ``ce``; each link sees what the previous ones stored.  ``cluster`` CTAs (one
+    thread-block cluster) share the tiles of every link."""
     arr = (GemmArgs * max(1, len(gemms)))(*gemms)
-    kinds = (C.c_int32 * len(links))(*[0 if k == "gemm" else 1 for k, _ in links])
-    idxs = (C.c_int32 * len(links))(*[i for _, i in links])
+    kinds = (C.c_int32 * len(links))(*[1 if l[0] == "ce" else 0 for l in links])
+    idxs = (C.c_int32 * len(links))(*[l[1] for l in links])
+    cnts = (C.c_int32 * len(links))(*[l[2] if l[0] == "group" else 1 for l in links])
     dev = device.index if device.index is not None else torch.cuda.current_device()
     _check(
-        lib().p2pfl_gemm_chain(
-            dev, _stream(), arr, C.c_int(len(gemms)), kinds, idxs, C.c_int(len(links)), C.byref(ce) if ce is not None else None
+        lib().p2pfl_gemm_chain_cluster(
+            dev, _stream(), arr, C.c_int(len(gemms)), kinds, idxs, cnts, C.c_int(len(links)),
+            C.byref(ce) if ce is not None else None, C.c_int(cluster),
         )
     )
     _count()

@@ -92,6 +92,11 @@ class Settings:
     part of the per-round overhead."""
     BUNDLE_LINGER: float = 0.02
     """Longest a lazily queued broadcast waits for company before it is sent on its own."""
+    MLP_CHAIN_CLUSTER: int = 16
+    """Run the fused MLP step as TWO launches: one thread-block cluster of this many CTAs walks
+    every GEMM link (forward chain, loss, dgrad chain, then all weight gradients side by side),
+    the links separated by the hardware cluster barrier instead of kernel boundaries; then Adam.
+    0 = one launch per link (8 per step)."""
     MLP_CHAIN: bool = False
     """Run the dependent links of the fused MLP step (forward chain, loss, dgrad chain) as
     one single-CTA kernel (``p2pfl_gemm_chain``) instead of one launch per link.  Measured

@@ -269,18 +269,20 @@ def test_pdl_on_and_off_give_identical_training():
     assert torch.equal(flats[0], flats[1])
 
 
-def test_chain_kernel_matches_per_link_launches():
-    """The single-CTA GEMM chain (forward + loss + dgrad links in one launch) must reproduce
-    the per-link launches: same tiles, same MMA order, same epilogues (only the loss sum and
-    the last layer's bias gradient are reduced with atomics, whose order may differ)."""
+@pytest.mark.parametrize("mode", ["chain1", "cluster2", "cluster8", "cluster16"])
+def test_chain_kernel_matches_per_link_launches(mode):
+    """The GEMM chain - one CTA, or one thread-block cluster that also walks the weight-gradient
+    link - must reproduce the per-link launches: same tiles, same MMA order, same epilogues (only
+    the loss sum and the last layer's bias gradient are reduced with atomics, whose order may differ)."""
     from p2pfl_b200.learning.b200_learner import B200Learner
     from p2pfl_b200.models import MLP
     from p2pfl_b200.settings import Settings
 
     results = []
-    default = Settings.MLP_CHAIN
+    default = (Settings.MLP_CHAIN, Settings.MLP_CHAIN_CLUSTER)
     for chain in (True, False):
-        Settings.MLP_CHAIN = chain
+        Settings.MLP_CHAIN = chain and mode == "chain1"
+        Settings.MLP_CHAIN_CLUSTER = int(mode[7:]) if chain and mode.startswith("cluster") else 0
         try:
             dm = _dm(n_train=640, n_test=128)
             learner = B200Learner(MLP(seed=3), dm, "p", epochs=1, device=DEV)
@@ -290,7 +292,7 @@ def test_chain_kernel_matches_per_link_launches():
             results.append((learner.flat.clone(), learner.grads.clone(), losses))
             learner.close()
         finally:
-            Settings.MLP_CHAIN = default
+            Settings.MLP_CHAIN, Settings.MLP_CHAIN_CLUSTER = default
     assert all(abs(a - b) < 1e-5 for a, b in zip(results[0][2], results[1][2])), (results[0][2], results[1][2])
     assert torch.allclose(results[0][1], results[1][1], atol=1e-6, rtol=1e-5)
     assert torch.allclose(results[0][0], results[1][0], atol=1e-5)

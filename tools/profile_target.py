@@ -3,6 +3,7 @@
 evaluation, a FedAvg, and a GPT-2-sized push + reduce on one device.  Run it plain
 first; only then under ncu (B200_PROFILING.md)."""
 
+import ctypes
 import os
 import sys
 
@@ -25,6 +26,32 @@ if what in ("all", "step"):
     learner.fit()
     print("eval", learner.evaluate())
     torch.cuda.synchronize()
+if what == "mlpstep":
+    # the fused MLP step in every launch arrangement (per-link, single-CTA chain, cluster chains)
+    from p2pfl_b200.settings import Settings  # noqa: E402
+
+    dm = MnistFederatedDM(0, 1, n_train=640, n_test=128)
+    x, y = dm.tensors("train")
+    for chain, cluster in ((False, 0), (True, 0), (False, 2), (False, 4), (False, 8), (False, 16)):
+        Settings.MLP_CHAIN, Settings.MLP_CHAIN_CLUSTER = chain, cluster
+        learner = B200Learner(MLP(seed=0), dm, "prof", epochs=1, device="cuda:0")
+        stamps = torch.zeros(24, 8, dtype=torch.int64, device="cuda:0")
+        ops.lib().p2pfl_gemm_chain_set_stamps(ctypes.c_void_p(stamps.data_ptr()))
+        for i in range(3):
+            learner.debug_single_step(x[i * 32 : (i + 1) * 32], y[i * 32 : (i + 1) * 32])
+        torch.cuda.synchronize()
+        ops.lib().p2pfl_gemm_chain_set_stamps(ctypes.c_void_p(0))
+        if chain or cluster:
+            st = stamps.cpu()
+            t0 = int(st[0, 0])
+            print(f"chain={chain} cluster={cluster}: per-link stamps in us (1.9 GHz) relative to link 0 start")
+            for p_ in range(8):
+                if int(st[p_, 0]) == 0:
+                    continue
+                print("  link", p_, [round((int(v) - t0) / 1900.0, 2) if int(v) else None for v in st[p_, :7]],
+                      "epilogue", [round((int(v) - t0) / 1900.0, 2) if int(v) else None for v in st[12 + p_, :6]])
+        learner.close()
+    print("mlpstep ok")
 if what == "resnet":
     # the graph build runs every kernel of the step once outside capture, so a launch list
     # under ncu shows the whole fused ResNet-18 step
