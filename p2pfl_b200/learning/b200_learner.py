@@ -515,7 +515,7 @@ class B200Learner(TorchLearner):
                 # host RNG: the CUDA generator cannot be used while another node's
                 # thread captures a graph on this device
                 ta = time.perf_counter()
-                if not ep.get("perm_ready") or os.environ.get("P2PFL_NO_PERM_PRECOMPUTE"):
+                if not ep.get("perm_ready"):
                     ep["perm_host"].copy_(torch.randperm(n, dtype=torch.int32))
                 ep["perm"].copy_(ep["perm_host"], non_blocking=True)
                 up = torch.cuda.Event()
