@@ -218,7 +218,7 @@ int p2pfl_gemm_tn(int device, void* stream, const p2pfl_gemm_args* args);
 int p2pfl_gemm_tn_grouped(int device, void* stream, const p2pfl_gemm_args* args, int count);
 
 /* The dependent part of a small-batch train step as ONE launch: a single CTA walks a
- * list of links - GEMMs (same arguments as p2pfl_gemm_tn; N tiled by 32) and at most
+ * list of links - GEMMs (same arguments as p2pfl_gemm_tn, K-major, no split-K; N tiled by 32) and at most
  * one softmax-cross-entropy link - each consuming what the previous one stored
  * (mlp.py:57-80 forward chain + loss + autograd dgrad chain). */
 typedef struct {
