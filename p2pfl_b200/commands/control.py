@@ -34,7 +34,8 @@ BUNDLE_CMD = "bundle"
 def pack_bundled(msg: Any) -> str:
     import json
 
-    return json.dumps([msg.cmd, int(msg.round), int(msg.ttl), int(msg.hash), [str(a) for a in msg.args]])
+    # (the source is packed too: a relayed message keeps its originator, not the relayer)
+    return json.dumps([msg.cmd, int(msg.round), int(msg.ttl), int(msg.hash), [str(a) for a in msg.args], msg.source])
 
 
 def unpack_bundled(source: str, packed: str) -> Any:
@@ -42,8 +43,10 @@ def unpack_bundled(source: str, packed: str) -> Any:
 
     from p2pfl_b200.communication.messages import Message
 
-    cmd, rnd, ttl, h, args = json.loads(packed)
-    return Message(source=source, cmd=str(cmd), args=[str(a) for a in args], round=int(rnd), ttl=int(ttl), hash=int(h))
+    fields = json.loads(packed)
+    cmd, rnd, ttl, h, args = fields[:5]
+    origin = str(fields[5]) if len(fields) > 5 else source
+    return Message(source=origin, cmd=str(cmd), args=[str(a) for a in args], round=int(rnd), ttl=int(ttl), hash=int(h))
 
 
 class HeartbeatCommand(Command):

@@ -42,6 +42,8 @@ class Gossiper(threading.Thread):
         self._lazy: List[Tuple[Message, Any]] = []
         self._lazy_deadline = 0.0
         self.bundle_fn: Optional[Callable[[List[Message]], None]] = None
+        # several relayed messages for the same neighbour in one drain -> one message (set by the engine)
+        self.bundle_to_fn: Optional[Callable[[str, List[Message]], None]] = None
         # duplicate filter: ring + set for O(1) membership
         self._seen_ring: Deque[int] = collections.deque()
         self._seen: Set[int] = set()
@@ -131,6 +133,21 @@ class Gossiper(threading.Thread):
                 except Exception as e:
                     logger.debug(self._addr, f"bundled broadcast failed: {e}")
                 batch = [(m, n) for m, n in batch if not callable(n)]
+            if self.bundle_to_fn is not None and Settings.BUNDLE_BOOKKEEPING:
+                # relays: everything this drain holds for one neighbour travels together (on a line or
+                # a ring a node forwards nearly every broadcast to the same one or two neighbours)
+                per_nei: dict = {}
+                for msg, nei in batch:
+                    if not callable(nei):
+                        per_nei.setdefault(nei, []).append(msg)
+                grouped = {n for n, ms in per_nei.items() if len(ms) >= 2}
+                for nei in grouped:
+                    try:
+                        self.bundle_to_fn(nei, per_nei[nei])
+                    except Exception as e:
+                        logger.debug(self._addr, f"bundled relay to {nei} failed: {e}")
+                if grouped:
+                    batch = [(m, n) for m, n in batch if callable(n) or n not in grouped]
             for msg, nei in batch:
                 try:
                     if callable(nei):

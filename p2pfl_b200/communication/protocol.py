@@ -161,6 +161,7 @@ class BaseProtocol(CommunicationProtocol):
         )
         self._gossiper = Gossiper(self.addr, self.send)
         self._gossiper.bundle_fn = self._broadcast_bundle
+        self._gossiper.bundle_to_fn = self._send_bundle_to
         self._heartbeater = Heartbeater(self.addr, self._neighbors, self._broadcast_beat)
         self._server = _ServerHandle(transport)
         from p2pfl_b200.commands.control import HeartbeatCommand, NeighborsHintCommand
@@ -310,6 +311,18 @@ class BaseProtocol(CommunicationProtocol):
         targets = list(self._neighbors.get_all(only_direct=True))
         if targets:
             self._gossiper.add_broadcast(msg, self.broadcast, lazy=lazy)
+
+    def _send_bundle_to(self, nei: str, msgs: List[Message]) -> None:
+        """Several (relayed) messages for ONE neighbour: a single ``bundle`` if it is extended."""
+        from p2pfl_b200.commands.control import BUNDLE_CMD, pack_bundled
+
+        if nei in self._extended and len(msgs) > 1:
+            bundle = self.build_msg(BUNDLE_CMD, [pack_bundled(m) for m in msgs])
+            bundle.ttl = 1
+            self.send(nei, bundle)
+        else:
+            for m in msgs:
+                self.send(nei, m)
 
     def _broadcast_bundle(self, msgs: List[Message]) -> None:
         """Several broadcasts at once: extended neighbours get ONE ``bundle`` message (ttl 1)

@@ -322,3 +322,35 @@ def test_bookkeeping_broadcasts_are_bundled(protocol):
         assert got[1][-1] == ("models_ready", 6, ())
     finally:
         _stop(nodes)
+
+
+def test_bundled_relays_keep_their_originator():
+    """A relayer forwards several messages to one neighbour as one bundle; the receiver must see
+    each with its original source, TTL and id (and drop the ones it already has)."""
+    nodes = _nodes(3, InMemoryCommunicationProtocol)
+    got = []
+    try:
+        from p2pfl_b200.commands.command import Command
+
+        class Probe(Command):
+            @staticmethod
+            def get_name():
+                return "probe"
+
+            def execute(self, source, round, *args, **kw):
+                got.append((source, round, args))
+
+        nodes[2]._communication_protocol.add_command(Probe())
+        nodes[1].connect(nodes[2].addr)
+        wait_convergence(nodes[1:], 1, only_direct=True)
+        relayer = nodes[1]._communication_protocol
+        deadline = time.time() + 5
+        while nodes[2].addr not in relayer._extended and time.time() < deadline:
+            time.sleep(0.01)
+        origin = nodes[0]._communication_protocol
+        msgs = [origin.build_msg("probe", [str(i)], round=i) for i in range(3)]
+        relayer._send_bundle_to(nodes[2].addr, [m.relay_copy() for m in msgs])
+        relayer._send_bundle_to(nodes[2].addr, [m.relay_copy() for m in msgs[:2]])  # duplicates: dropped
+        assert got == [(nodes[0].addr, i, (str(i),)) for i in range(3)]
+    finally:
+        _stop(nodes)

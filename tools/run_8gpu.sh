@@ -1,4 +1,3 @@
 mkdir -p gpurun_out
-export P2PFL_BENCH_TRACE=gpurun_out/trace8b
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29611 bench.py --gpus 8 --steps 10 --warmup 3 > gpurun_out/bench8_v5.log 2>&1 || true
-tail -1 gpurun_out/bench8_v5.log | cut -c1-300
+timeout 130 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29661 bench/run_config.py --config 4 --rounds 3 --timeout 100 > gpurun_out/cfg4_8gpu_64.log 2>&1 || true
+tail -2 gpurun_out/cfg4_8gpu_64.log | cut -c1-600
