@@ -23,34 +23,48 @@ class Settings:
     LOG_LEVEL: str = "INFO"
     """DEBUG also makes the learning thread re-raise instead of stopping the node."""
     LOG_DIR: str = "logs"
+    """Directory of the optional log file."""
     LOG_TO_FILE: bool = False
     """The reference always writes logs/p2pfl.log; here it is opt-in."""
 
     # ---- heartbeats ----------------------------------------------------
     HEARTBEAT_PERIOD: float = 2.0
+    """Seconds between two beats to the direct neighbours (also the eviction sweep period)."""
     HEARTBEAT_TIMEOUT: float = 5.0
+    """A neighbour whose last beat is older than this is dropped."""
 
     # ---- control-message gossip ---------------------------------------
     GOSSIP_PERIOD: float = 0.1
+    """Pacing of the relay thread: at most GOSSIP_MESSAGES_PER_PERIOD sends per period (0 = unpaced)."""
     TTL: int = 10
+    """Hops a flooded control message may travel."""
     GOSSIP_MESSAGES_PER_PERIOD: int = 100
+    """Send budget of the relay thread per GOSSIP_PERIOD."""
     AMOUNT_LAST_MESSAGES_SAVED: int = 100
+    """Size of the ring of message ids used to drop duplicates."""
 
     # ---- model gossip --------------------------------------------------
     GOSSIP_MODELS_PERIOD: float = 1.0
     """Upper bound on the pause between two model-gossip ticks.  The loop is
     event driven: it wakes as soon as node state changes (SURVEY Appendix C.6)."""
     GOSSIP_MODELS_PER_ROUND: int = 2
+    """Peers that get a model per gossip tick."""
     GOSSIP_EXIT_ON_X_EQUAL_ROUNDS: int = 10
+    """Model gossip gives up after this many ticks without any change in what the peers hold."""
 
     # ---- learning ------------------------------------------------------
     TRAIN_SET_SIZE: int = 4
+    """Nodes elected to train each round."""
     VOTE_TIMEOUT: float = 60.0
+    """Longest wait for the ballots of a round; the tally then uses what arrived."""
     AGGREGATION_TIMEOUT: float = 300.0
+    """Longest wait for the models of a round; the aggregate then uses what arrived."""
     WAIT_HEARTBEATS_CONVERGENCE: float = 0.2 * HEARTBEAT_TIMEOUT
+    """Pause after start_learning so that beats reach every node before the vote."""
 
     # ---- monitoring ----------------------------------------------------
     RESOURCE_MONITOR_PERIOD: float = 1.0
+    """Sampling period of the node monitor (CPU / RAM / network, GPU through NVML)."""
 
     # ===== additions (not in the reference) =============================
     VOTE_EVERY_ROUND: bool = True
@@ -63,6 +77,7 @@ class Settings:
     GRPC_MAX_MESSAGE_BYTES: int = 1 << 30
     """Raised from gRPC's 4 MiB default so >4 MiB models fit (Q9)."""
     GRPC_SERVER_WORKERS: int = 4
+    """Threads of a node's gRPC server pool (the reference uses 2)."""
     WIRE_DTYPE: str = "bf16"
     """Wire dtype of the device data plane: 'bf16' (inbox mode B) or 'fp32'."""
     DEVICE_TILE_ELEMS: int = 16384
@@ -109,6 +124,7 @@ class Settings:
     """A relay skips neighbours the originator reaches directly (it says so in its
     heartbeats): a full mesh then costs N-1 messages per broadcast, not (N-1)^2."""
     RELAY_PRUNING_MAX_LIST: int = 64
+    """A node with more direct neighbours than this does not advertise them (hint size)."""
     FUSED_EXCHANGE: bool = True
     """Use the single-kernel push+FedAvg exchange whenever the whole train set has
     device arenas on distinct GPUs; otherwise models are pulled one by one."""

@@ -354,3 +354,16 @@ def test_bundled_relays_keep_their_originator():
         assert got == [(nodes[0].addr, i, (str(i),)) for i in range(3)]
     finally:
         _stop(nodes)
+
+
+def test_rendered_proto_is_current():
+    """The ``.proto`` text shipped for other languages is rendered from the descriptors in use."""
+    import importlib.util
+    import os
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("render_proto", os.path.join(root, "tools", "render_proto.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    with open(os.path.join(root, "p2pfl_b200", "communication", "grpc", "proto_schema", "node.proto")) as fh:
+        assert fh.read() == mod.render()
