@@ -11,8 +11,21 @@ import time
 from typing import List, Optional, Type
 
 from p2pfl_b200.management.logger import logger
+from p2pfl_b200.settings import Settings
 from p2pfl_b200.stages.stage import LearningContext, Stage
 from p2pfl_b200.stages.stage_factory import StageFactory
+
+
+def _nvtx():
+    """``torch.cuda.nvtx`` when ranges are wanted and a device is there, else None."""
+    if not Settings.NVTX_RANGES:
+        return None
+    try:
+        import torch
+
+        return torch.cuda.nvtx if torch.cuda.is_available() else None
+    except Exception:
+        return None
 
 
 class StageWorkflow:
@@ -27,7 +40,14 @@ class StageWorkflow:
             self.history.append(stage.name())
             logger.debug(ctx.state.addr, f"running stage {stage.name()}")
             t0 = time.time()
-            self.current_stage = stage.execute(ctx)
+            nvtx = _nvtx()
+            if nvtx is not None:  # one range per stage and round, visible in nsys / ncu --nvtx
+                nvtx.range_push(f"{stage.name()}[r{ctx.state.round}]")
+            try:
+                self.current_stage = stage.execute(ctx)
+            finally:
+                if nvtx is not None:
+                    nvtx.range_pop()
             ctx.timings["stage:" + stage.name()] = ctx.timings.get("stage:" + stage.name(), 0.0) + time.time() - t0
         self.finished = True
 
