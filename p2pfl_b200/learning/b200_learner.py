@@ -6,21 +6,24 @@ MNIST-shaped MLP family (mlp.py:53-69):
 
 * parameters live in a peer-mappable device arena (fp32 master) with a bf16
   working copy and a bf16 transposed copy of each weight for the dgrad GEMM;
-* every Linear forward / dgrad / wgrad is the tcgen05 GEMM (``ops.gemm_tn``)
-  in swap-AB form (out-features ride the 128-row MMA dimension, the batch is
-  N), bias + ReLU + ReLU-mask + bias-gradient fused in its epilogue;
-* log-softmax + cross-entropy forward and backward are one kernel; Adam over
-  the whole arena (+ bf16 refresh) is one kernel;
+* every Linear forward / dgrad / wgrad is the tcgen05 GEMM with bias + ReLU +
+  ReLU-mask + bias-gradient fused in its epilogue; by default ONE thread-block
+  cluster walks all of them plus the loss as dependent links of one launch
+  (``ops.gemm_chain(..., cluster=16)``, ``Settings.MLP_CHAIN_CLUSTER``), and
+  Adam over the whole arena (+ bf16 refresh + transposed copies) is the
+  second launch of the step; ``MLP_CHAIN_CLUSTER = 0`` runs one launch per
+  link instead (swap-AB GEMMs, a fused log-softmax + cross-entropy kernel);
+* the CNN and ResNet-18 families get their own plans (``b200_cnn.py``,
+  ``b200_resnet.py``) behind the same learner;
 * the dataset is resident on the device, shuffled by one gather kernel per
   epoch, and a whole epoch is ONE CUDA graph launch (no host work per step).
 
-Models without a fused spec fall back to eager autograd for forward/backward
+Models without a fused plan (GPT-2) fall back to eager autograd for forward/backward
 (``TorchLearner``) but keep the arena, so the gossip data plane is identical.
 """
 
 from __future__ import annotations
 
-import os
 import threading
 import time
 from typing import Any, Dict, List, Optional, Tuple
