@@ -365,5 +365,5 @@ def test_rendered_proto_is_current():
     spec = importlib.util.spec_from_file_location("render_proto", os.path.join(root, "tools", "render_proto.py"))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
-    with open(os.path.join(root, "p2pfl_b200", "communication", "grpc", "proto_schema", "node.proto")) as fh:
+    with open(os.path.join(root, "p2pfl_b200", "communication", "grpc", "proto_schema", "wire_schema.proto")) as fh:
         assert fh.read() == mod.render()
