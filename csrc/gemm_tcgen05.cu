@@ -1115,6 +1115,31 @@ gemm_chain_kernel(const __grid_constant__ ChainArgs ga) {
 
 }  // namespace
 
+// Largest cluster (16, 8, 4, 2, 1) this device can co-schedule for the chain kernel.
+extern "C" int p2pfl_gemm_chain_max_cluster(int device) {
+  if (cudaSetDevice(device) != cudaSuccess) return 1;
+  constexpr size_t smem = (size_t)kChainStages * kChainStageBytes + 1024;
+  cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  for (int c = 16; c > 1; c >>= 1) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(c);
+    cfg.blockDim = dim3(kThreadsGemm);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)c;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_chain_kernel, &cfg) == cudaSuccess && n >= 1) return c;
+    (void)cudaGetLastError();
+  }
+  return 1;
+}
+
 static long long* g_chain_stamps = nullptr;
 extern "C" int p2pfl_gemm_chain_set_stamps(void* device_buffer) {
   g_chain_stamps = reinterpret_cast<long long*>(device_buffer);

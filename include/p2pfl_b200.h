@@ -241,6 +241,8 @@ int p2pfl_gemm_chain_cluster(int device, void* stream, const p2pfl_gemm_args* ge
                              const int32_t* phase_kind, const int32_t* phase_idx,
                              const int32_t* phase_cnt /* nullable */, int n_phases,
                              const p2pfl_ce_args* ce, int cluster_ctas);
+/* Largest cluster_ctas (16, 8, 4, 2 or 1) the device can co-schedule for the chain kernel. */
+int p2pfl_gemm_chain_max_cluster(int device);
 /* Bring-up aid: while `device_buffer` (int64 [12][8], NULL = off) is set, every chain launch
  * makes CTA 0 record SM-clock stamps per link: 0 link start, 1 first operands landed, 2 MMAs
  * issued, 3 first accumulator complete, 4 epilogue stores issued, 5 fences done, 6 barrier passed. */

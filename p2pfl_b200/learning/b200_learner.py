@@ -328,7 +328,8 @@ class B200Learner(TorchLearner):
         ldB = act["ldB"]
         C = Ls[-1].out_f
         if Settings.MLP_CHAIN_CLUSTER > 0 and 3 * nL - 1 <= 8 and C <= 256 and bsz <= 32:
-            self._train_step_chain(x16, xT16, y, bsz, act, loss_slot, step_offset, lr, cluster=Settings.MLP_CHAIN_CLUSTER)
+            cluster = min(Settings.MLP_CHAIN_CLUSTER, ops.gemm_chain_max_cluster(self.device))
+            self._train_step_chain(x16, xT16, y, bsz, act, loss_slot, step_offset, lr, cluster=cluster)
             return
         if Settings.MLP_CHAIN and 2 * nL - 1 <= 8 and C <= 256:
             self._train_step_chain(x16, xT16, y, bsz, act, loss_slot, step_offset, lr)

@@ -353,6 +353,17 @@ def gemm_chain(device: torch.device, gemms: Sequence[GemmArgs], links: Sequence[
     _count()
 
 
+_max_cluster: dict = {}
+
+
+def gemm_chain_max_cluster(device: torch.device) -> int:
+    """Largest cluster size (16, 8, 4, 2, 1) the chain kernel can be launched with on ``device``."""
+    dev = device.index if device.index is not None else torch.cuda.current_device()
+    if dev not in _max_cluster:
+        _max_cluster[dev] = int(lib().p2pfl_gemm_chain_max_cluster(C.c_int(dev)))
+    return _max_cluster[dev]
+
+
 def gemm_tn_grouped(device: torch.device, problems: Sequence[GemmArgs]) -> None:
     """Up to four independent GEMMs in ONE launch."""
     arr = (GemmArgs * len(problems))(*problems)
