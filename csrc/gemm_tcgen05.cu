@@ -797,6 +797,7 @@ struct ChainScalars {
   int32_t idx[kChainMaxPhases];
   int32_t cnt[kChainMaxPhases];   // GEMM link: idx .. idx+cnt-1 are independent and share the link
   int32_t n_phases;
+  int32_t n_iter;  // bring-up aid: walk the whole list this many times in ONE launch (1 = normal)
   p2pfl_ce_args ce;
   long long* stamps;  // bring-up aid (nullable): [link][8] SM-clock stamps of CTA 0, see p2pfl_gemm_chain_set_stamps
 };
@@ -877,25 +878,47 @@ __device__ void chain_ce(const p2pfl_ce_args& a_mem, int ewarp, int lane, float*
     //   (2) one thread per row: max / sum-exp over its C classes -> log-sum-exp, loss,
     //   (3) all threads: one gradient element each (both orientations + a staged copy),
     // then C threads sum the staged gradients into the bias gradient.
-    float* xs = scratch;                                   // [B, C]
-    int* lab = reinterpret_cast<int*>(scratch + B * C);    // [B]
-    float* s_lse = scratch + B * C + B;                    // [B]
-    float* gs = s_lse + B;                                 // [B, C]
-    for (int i = et; i < B * C; i += 128) xs[i] = __ldcg(a.logits + (size_t)(i / C) * a.ld_logits + (i % C));
-    for (int i = et; i < B; i += 128) lab[i] = a.labels[i];
+    // rows padded to a multiple of 4 words (16-byte aligned rows; the padding holds -inf)
+    const int CP = (C + 3) & ~3;
+    float* xs = scratch;                                    // [B, CP]
+    int* lab = reinterpret_cast<int*>(scratch + B * CP);    // [B]
+    float* s_lse = scratch + B * CP + B;                    // [B]
+    float* gs = s_lse + B;                                  // [B, C]
+    // four loads in flight per thread before the first store: one trip to L2, not one per element
+    const int lab_mine = et < B ? a.labels[et] : 0;
+    for (int base = 0; base < B * CP; base += 512) {
+      float v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int i = base + k * 128 + et;
+        const int row = i / CP, c = i - row * CP;
+        v[k] = (i < B * CP && c < C) ? __ldcg(a.logits + (size_t)row * a.ld_logits + c) : -INFINITY;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int i = base + k * 128 + et;
+        if (i < B * CP) xs[i] = v[k];
+      }
+    }
+    if (et < B) lab[et] = lab_mine;
     asm volatile("bar.sync 1, 128;" ::: "memory");
     CE_STAMP(1);
     float loss_row = 0.f;
     if (et < B) {
-      const float* xr = xs + et * C;
+      const float4* xr4 = reinterpret_cast<const float4*>(xs + et * CP);
       float mx = -INFINITY;
-      for (int c = 0; c < C; ++c) mx = fmaxf(mx, xr[c]);
+      for (int c4 = 0; c4 < CP / 4; ++c4) {
+        const float4 q4 = xr4[c4];
+        mx = fmaxf(fmaxf(mx, fmaxf(q4.x, q4.y)), fmaxf(q4.z, q4.w));
+      }
       float se = 0.f;
-      for (int c = 0; c < C; ++c) se += __expf(xr[c] - mx);
+      for (int c4 = 0; c4 < CP / 4; ++c4) {
+        const float4 q4 = xr4[c4];
+        se += (__expf(q4.x - mx) + __expf(q4.y - mx)) + (__expf(q4.z - mx) + __expf(q4.w - mx));  // exp(-inf) = 0
+      }
       const float lse = mx + __logf(se);
       s_lse[et] = lse;
-      const int y = lab[et];
-      if (y >= 0 && y < C) loss_row = lse - xr[y];
+      if (lab_mine >= 0 && lab_mine < C) loss_row = lse - xs[et * CP + lab_mine];
     }
     loss_row = warp_sum(loss_row);
     if (a.loss_sum && lane == 0 && loss_row != 0.f) atomicAdd(a.loss_sum, loss_row);
@@ -903,7 +926,8 @@ __device__ void chain_ce(const p2pfl_ce_args& a_mem, int ewarp, int lane, float*
     CE_STAMP(2);
     for (int i = et; i < B * C; i += 128) {
       const int row = i / C, c = i - row * C;
-      const __nv_bfloat16 gb = __float2bfloat16_rn((__expf(xs[i] - s_lse[row]) - (c == lab[row] ? 1.f : 0.f)) * inv_b);
+      const __nv_bfloat16 gb =
+          __float2bfloat16_rn((__expf(xs[row * CP + c] - s_lse[row]) - (c == lab[row] ? 1.f : 0.f)) * inv_b);
       if (dl) dl[(size_t)row * a.ld_d + c] = gb;
       if (dlt) dlt[(size_t)c * a.ld_dt + row] = gb;
       gs[i] = __bfloat162float(gb);
@@ -1008,6 +1032,7 @@ gemm_chain_kernel(const __grid_constant__ ChainArgs ga) {
   long long* const stamps = (g.stamps && crank == 0) ? g.stamps : nullptr;
 #define CHAIN_STAMP(slot) \
   if (stamps && lane == 0) stamps[p * 8 + (slot)] = clock64()
+  for (int iter = 0; iter < g.n_iter; ++iter)
   for (int p = 0; p < g.n_phases; ++p) {
     if (threadIdx.x == 0) CHAIN_STAMP(0);
     if (g.kind[p] == 0) {
@@ -1088,7 +1113,7 @@ gemm_chain_kernel(const __grid_constant__ ChainArgs ga) {
       tile_it += my_tiles;
       it += my_kb;
     } else if (warp >= 2 && crank == 0) {
-      const bool fits = (size_t)g.ce.B * (2 * g.ce.C + 2) * 4 <= (size_t)kChainStages * kChainStageBytes;
+      const bool fits = (size_t)g.ce.B * (2 * g.ce.C + 6) * 4 <= (size_t)kChainStages * kChainStageBytes;
       chain_ce(g.ce, warp - 2, lane, s_db, fits ? reinterpret_cast<float*>(smem) : nullptr, g.ce.B <= 128 && g.ce.C <= 64,
                stamps ? stamps + 96 + p * 8 : nullptr);
     }
@@ -1197,6 +1222,8 @@ extern "C" int p2pfl_gemm_chain_cluster(int device, void* stream, const p2pfl_ge
   }
   g.sc.n_phases = n_phases;
   g.sc.stamps = g_chain_stamps;
+  static const int n_iter = [] { const char* e = getenv("P2PFL_CHAIN_ITER"); return e && atoi(e) > 0 ? atoi(e) : 1; }();
+  g.sc.n_iter = n_iter;
   if (has_ce) {
     P2PFL_REQUIRE(ce && ce->logits && ce->labels && ce->B > 0 && ce->C > 0 && ce->C <= 256, "bad cross-entropy link");
     g.sc.ce = *ce;
