@@ -423,7 +423,11 @@ class BaseProtocol(CommunicationProtocol):
             err = None
             for packed in msg.args:
                 try:
-                    err = self.on_message(unpack_bundled(msg.source, packed)) or err
+                    inner = unpack_bundled(msg.source, packed)
+                    if inner.cmd == "bundle":  # bundles do not nest
+                        err = "nested bundle"
+                        continue
+                    err = self.on_message(inner) or err
                 except Exception as e:
                     err = f"bad bundled message: {e}"
             return err

@@ -11,6 +11,8 @@ configures the B200 data plane.
 
 from __future__ import annotations
 
+import os
+
 
 class Settings:
     """Mutable class-attribute configuration (no instances)."""
@@ -107,7 +109,7 @@ class Settings:
     part of the per-round overhead."""
     BUNDLE_LINGER: float = 0.02
     """Longest a lazily queued broadcast waits for company before it is sent on its own."""
-    NVTX_RANGES: bool = bool(int(__import__("os").environ.get("P2PFL_NVTX", "0")))
+    NVTX_RANGES: bool = os.environ.get("P2PFL_NVTX", "0") not in ("", "0")
     """Wrap every stage of the workflow in an NVTX range (``P2PFL_NVTX=1``), for timeline tools."""
     MLP_CHAIN_CLUSTER: int = 16
     """Run the fused MLP step as TWO launches: one thread-block cluster of this many CTAs walks
