@@ -39,7 +39,8 @@ class Settings:
     GOSSIP_PERIOD: float = 0.1
     """Pacing of the relay thread: at most GOSSIP_MESSAGES_PER_PERIOD sends per period (0 = unpaced)."""
     TTL: int = 10
-    """Hops a flooded control message may travel."""
+    """Hops a flooded control message may travel.  It also bounds what a long line of nodes can
+    learn about itself (SURVEY Q10): a 64-node line needs ``TTL >= 63``."""
     GOSSIP_MESSAGES_PER_PERIOD: int = 100
     """Send budget of the relay thread per GOSSIP_PERIOD."""
     AMOUNT_LAST_MESSAGES_SAVED: int = 100
