@@ -129,4 +129,6 @@ class AddModelCommand(Command):
             self._stop()
             return
         if held:
-            self._protocol.broadcast(self._protocol.build_msg("models_aggregated", held, round=st.round))
+            from p2pfl_b200.stages.common import announce_aggregated
+
+            announce_aggregated(self._protocol, st, held)

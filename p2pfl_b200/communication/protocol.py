@@ -312,6 +312,26 @@ class BaseProtocol(CommunicationProtocol):
         if targets:
             self._gossiper.add_broadcast(msg, self.broadcast, lazy=lazy)
 
+    def multicast_async(self, msg: Message, names: List[str]) -> None:
+        """Fire-and-forget delivery of ``msg`` to exactly ``names`` (direct neighbours or not), point to
+        point: ttl 1, no flooding.  Links to non-neighbours are the cached temporary ones."""
+        msg.ttl = 1
+        targets = [n for n in names if n != self.addr]
+        if not targets:
+            return
+
+        def deliver(m: Message) -> None:
+            for n in targets:
+                try:
+                    self.send(n, m, create_connection=True)
+                except Exception as e:  # one unreachable peer must not cost the others their copy
+                    logger.debug(self.addr, f"multicast of '{m.cmd}' to {n} failed: {e}")
+
+        if Settings.ASYNC_BOOKKEEPING:
+            self._gossiper.add_broadcast(msg, deliver)
+        else:
+            deliver(msg)
+
     def _send_bundle_to(self, nei: str, msgs: List[Message]) -> None:
         """Several (relayed) messages for ONE neighbour: a single ``bundle`` if it is extended."""
         from p2pfl_b200.commands.control import BUNDLE_CMD, pack_bundled
@@ -410,9 +430,10 @@ class BaseProtocol(CommunicationProtocol):
     def on_disconnect(self, addr: str) -> None:
         self._neighbors.remove(addr, disconnect_msg=False)
 
-    def on_message(self, msg: Message) -> Optional[str]:
+    def on_message(self, msg: Message, via: Optional[str] = None) -> Optional[str]:
         """Flooding gossip: drop duplicates, relay while TTL lasts, dispatch
-        (reference: grpc_server.py:130-166)."""
+        (reference: grpc_server.py:130-166).  ``via``: the neighbour that handed us the message
+        when that is known (bundled relays) - it is not sent back there."""
         if not self._running:
             return "node not running"
         if not self._gossiper.check_and_set_processed(msg.hash):
@@ -427,7 +448,7 @@ class BaseProtocol(CommunicationProtocol):
                     if inner.cmd == "bundle":  # bundles do not nest
                         err = "nested bundle"
                         continue
-                    err = self.on_message(inner) or err
+                    err = self.on_message(inner, via=msg.source) or err
                 except Exception as e:
                     err = f"bad bundled message: {e}"
             return err
@@ -437,7 +458,9 @@ class BaseProtocol(CommunicationProtocol):
             from p2pfl_b200.commands.control import REFERENCE_COMMANDS
 
             covered = self._direct_of.get(msg.source, ()) if Settings.RELAY_PRUNING else ()
-            targets = [n for n in self._neighbors.get_all(only_direct=True) if n != msg.source and n not in covered]
+            targets = [
+                n for n in self._neighbors.get_all(only_direct=True) if n != msg.source and n != via and n not in covered
+            ]
             if msg.cmd not in REFERENCE_COMMANDS:
                 targets = [n for n in targets if n in self._extended]
             if targets:

@@ -108,6 +108,11 @@ class Settings:
     next round's ``metrics`` and the pre-vote cost one round trip per peer instead of three.
     Every RPC costs both ends ~0.1 ms of interpreter time, which at 8 nodes was the main
     part of the per-round overhead."""
+    DIRECT_TRAINSET_STATUS: bool = True
+    """``models_aggregated`` (who holds whose model) only matters to the round's trainers.  When some
+    of them are not direct neighbours it goes to them point to point (over the links the model
+    gossip opens anyway) instead of being flooded through every node: on a 64-node line with 16
+    trainers that was the largest share of all control traffic."""
     BUNDLE_LINGER: float = 0.02
     """Longest a lazily queued broadcast waits for company before it is sent on its own."""
     NVTX_RANGES: bool = os.environ.get("P2PFL_NVTX", "0") not in ("", "0")

@@ -13,7 +13,7 @@ import time
 from typing import Any, List, Optional, Type
 
 from p2pfl_b200.management.logger import logger
-from p2pfl_b200.stages.common import evaluate_and_share, pack_model
+from p2pfl_b200.stages.common import announce_aggregated, evaluate_and_share, pack_model
 from p2pfl_b200.stages.stage import LearningContext, Stage
 from p2pfl_b200.stages.stage_factory import StageFactory
 
@@ -66,10 +66,10 @@ class TrainStage(Stage):
             st.fused_complete_round = st.round if fused.complete else None
             if not fused.complete:
                 # only an incomplete exchange leaves somebody who may need to know what we hold
-                getattr(proto, "broadcast_async", proto.broadcast)(proto.build_msg("models_aggregated", held, round=st.round))
+                announce_aggregated(proto, st, held)
         else:
             held = agg.add_model(st.learner.export_model(), [st.addr], st.learner.get_num_samples()[0])
-            proto.broadcast(proto.build_msg("models_aggregated", held, round=st.round))
+            announce_aggregated(proto, st, held)
             TrainStage._gossip_partial_aggregates(ctx)
         t3 = time.time()
         for k, dt in (("evaluate", t1 - t0), ("fit", t2 - t1), ("exchange", t3 - t2)):

@@ -29,6 +29,23 @@ def broadcast_metrics(protocol: Any, state: Any, results: Dict[str, float], lazy
     send_async(protocol, msg, lazy)  # nobody waits on metrics
 
 
+def announce_aggregated(protocol: Any, state: Any, held: List[str]) -> None:
+    """Tell the round's trainers whose models this node holds (``models_aggregated``,
+    reference: train_stage.py:83-87, add_model_command.py:84-91).  Flooded like in the reference
+    when every trainer is a direct neighbour anyway; otherwise sent to the trainers only."""
+    from p2pfl_b200.settings import Settings
+
+    msg = protocol.build_msg("models_aggregated", held, round=state.round)
+    peers = [n for n in state.train_set if n != state.addr]
+    multicast = getattr(protocol, "multicast_async", None)
+    if Settings.DIRECT_TRAINSET_STATUS and multicast is not None and peers:
+        direct = protocol.get_neighbors(only_direct=True)
+        if any(n not in direct for n in peers):
+            multicast(msg, peers)
+            return
+    send_async(protocol, msg)
+
+
 def send_async(protocol: Any, msg: Any, lazy: bool = False) -> None:
     """Fire-and-forget broadcast where the protocol has one (plain broadcast otherwise)."""
     fn = getattr(protocol, "broadcast_async", None)

@@ -228,10 +228,10 @@ def test_relay_pruning_in_a_clique_and_reach_on_a_line():
                 eng = n._communication_protocol
                 orig = eng.on_message
 
-                def counted(msg, _orig=orig, _i=i):
+                def counted(msg, _orig=orig, _i=i, **kw):
                     if msg.cmd == "probe2":
                         deliveries.append(_i)
-                    return _orig(msg)
+                    return _orig(msg, **kw)
 
                 eng.on_message = counted
             if topology == "clique":
