@@ -169,6 +169,8 @@ class ModelsAggregatedCommand(Command):
         if round == st.round:
             st.models_aggregated[source] = list(args)
             st.notify()
+        elif st.round is not None and round == st.round + 1:
+            st.early_aggregated[source] = (round, list(args))  # installed when this node reaches that round
 
 
 class ModelsReadyCommand(Command):

@@ -32,6 +32,9 @@ class NodeState:
 
         # who aggregated what this round: node -> list of contributors
         self.models_aggregated: Dict[str, List[str]] = {}
+        # `models_aggregated` notices for the NEXT round that arrived before this node got there
+        # (a fast trainer's notice travels point to point and can overtake a slow node's round change)
+        self.early_aggregated: Dict[str, Any] = {}
         # last round for which a neighbour is known to hold the model (-1 = initialised)
         self.nei_status: Dict[str, int] = {}
         self.train_set: List[str] = []
@@ -77,6 +80,7 @@ class NodeState:
         self.total_rounds = total_rounds
         self.round = 0
         self.models_aggregated = {}
+        self.early_aggregated = {}
         self.train_set = []
         self.train_set_votes = {}
         self.finished.clear()
@@ -87,7 +91,8 @@ class NodeState:
         if self.round is None:
             raise ValueError("round not initialised")
         self.round += 1
-        self.models_aggregated = {}
+        self.models_aggregated = {src: args for src, (rnd, args) in self.early_aggregated.items() if rnd == self.round}
+        self.early_aggregated = {}
         # drop votes of rounds that are over
         for r in [r for r in self.train_set_votes if r < self.round]:
             del self.train_set_votes[r]
@@ -102,6 +107,7 @@ class NodeState:
         self.round = None
         self.total_rounds = None
         self.models_aggregated = {}
+        self.early_aggregated = {}
         self.nei_status = {}
         self.train_set = []
         self.train_set_votes = {}

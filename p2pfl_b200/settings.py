@@ -108,11 +108,14 @@ class Settings:
     next round's ``metrics`` and the pre-vote cost one round trip per peer instead of three.
     Every RPC costs both ends ~0.1 ms of interpreter time, which at 8 nodes was the main
     part of the per-round overhead."""
-    DIRECT_TRAINSET_STATUS: bool = True
-    """``models_aggregated`` (who holds whose model) only matters to the round's trainers.  When some
-    of them are not direct neighbours it goes to them point to point (over the links the model
-    gossip opens anyway) instead of being flooded through every node: on a 64-node line with 16
-    trainers that was the largest share of all control traffic."""
+    DIRECT_TRAINSET_STATUS: bool = False
+    """``models_aggregated`` (who holds whose model) only matters to the round's trainers.  True: when
+    some of them are not direct neighbours it goes to them point to point instead of being flooded
+    through every node.  On a 64-node line with 16 trainers that removes the largest share of the
+    control messages (35 k -> 6 k per two rounds) and helps the in-memory transport (1.9 -> 1.65 s per
+    round), but over gRPC the same run got slower (2.1 -> 4.6 s per round, 8 processes on a CPU-only
+    box): the flooded copies ride in bundles between neighbours, the direct ones are 240 extra
+    channels and one RPC each.  Off by default."""
     BUNDLE_LINGER: float = 0.02
     """Longest a lazily queued broadcast waits for company before it is sent on its own."""
     NVTX_RANGES: bool = os.environ.get("P2PFL_NVTX", "0") not in ("", "0")

@@ -245,3 +245,30 @@ def test_own_model_push_policy():
     finally:
         Settings.OWN_MODEL_PUSH = "auto"
         _stop(nodes)
+
+
+def test_trainer_status_point_to_point():
+    """``DIRECT_TRAINSET_STATUS``: `models_aggregated` reaches the round's trainers directly (they are
+    not all neighbours on a line) instead of being flooded; the experiment must end the same way."""
+    Settings.TRAIN_SET_SIZE = 3
+    Settings.DIRECT_TRAINSET_STATUS = True
+    nodes = _line(6, InMemoryCommunicationProtocol)
+    seen = []
+    try:
+        for i, n in enumerate(nodes):
+            eng = n._communication_protocol
+            orig = eng.on_message
+
+            def spy(msg, _orig=orig, _i=i, **kw):
+                if msg.cmd == "models_aggregated":
+                    seen.append((_i, msg.ttl))
+                return _orig(msg, **kw)
+
+            eng.on_message = spy
+        nodes[0].set_start_learning(rounds=2, epochs=1)
+        wait_4_results(nodes, 120)
+        check_equal_models(nodes, atol=1e-6)
+        assert seen and all(ttl == 1 for _, ttl in seen), seen[:5]  # nothing was flooded
+    finally:
+        Settings.DIRECT_TRAINSET_STATUS = False
+        _stop(nodes)
