@@ -1,5 +1,5 @@
 mkdir -p gpurun_out
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29641 bench/run_config.py --config 4 --rounds 4 --timeout 250 > gpurun_out/cfg4_2gpu_16_v2.log 2>&1 || true
-tail -1 gpurun_out/cfg4_2gpu_16_v2.log | cut -c1-500
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29651 bench/run_config.py --config 4 --per-gpu 16 --rounds 3 --timeout 250 > gpurun_out/cfg4_2gpu_32.log 2>&1 || true
-tail -1 gpurun_out/cfg4_2gpu_32.log | cut -c1-500
+timeout 600 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu15_2gpu.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu15_2gpu.log
+tail -3 gpurun_out/pytest_gpu15_2gpu.log
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29631 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/bench2_v5.log 2>&1 || true
+tail -1 gpurun_out/bench2_v5.log | cut -c1-260
