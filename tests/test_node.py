@@ -272,3 +272,23 @@ def test_trainer_status_point_to_point():
     finally:
         Settings.DIRECT_TRAINSET_STATUS = False
         _stop(nodes)
+
+
+def test_early_models_aggregated_notice_is_kept_for_the_next_round():
+    """A notice for round r+1 that overtakes this node's own round change is installed when the
+    node gets there (dropping it would make the sender look empty-handed for the whole round)."""
+    from p2pfl_b200.commands.control import ModelsAggregatedCommand
+    from p2pfl_b200.node_state import NodeState
+
+    st = NodeState("me")
+    st.set_experiment("experiment", 3)
+    cmd = ModelsAggregatedCommand(st)
+    cmd.execute("peer", 0, "a", "b")
+    assert st.models_aggregated == {"peer": ["a", "b"]}
+    cmd.execute("peer", 1, "c")  # next round: stashed
+    cmd.execute("other", 5, "z")  # far away: ignored
+    assert st.models_aggregated == {"peer": ["a", "b"]}
+    st.increase_round()
+    assert st.round == 1 and st.models_aggregated == {"peer": ["c"]}
+    st.increase_round()
+    assert st.models_aggregated == {}
