@@ -97,7 +97,8 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         self._nonce = 0
         self._no_arena: set = set()
         self.add_command(ArenaInfoCommand(self))
-        self.stats = {"fused": 0, "pulled": 0, "host": 0, "fused_bytes": 0, "pulled_bytes": 0}
+        # counts, bytes and DEVICE time (CUDA events on the stream that did the work) per path
+        self.stats = {"fused": 0, "pulled": 0, "host": 0, "fused_bytes": 0, "pulled_bytes": 0, "fused_ms": 0.0, "pulled_ms": 0.0}
 
     # ------------------------------------------------------------------ wiring
     def bind_node(self, node: Any) -> None:
@@ -255,12 +256,16 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         # partial aggregates, none of which is bandwidth critical; the wire dtype applies
         # to the fused exchange
         comm = learner.comm_stream  # not the compute stream: that one may be capturing a graph
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with torch.cuda.stream(comm):
             out = torch.empty(ref.n, dtype=torch.float32, device=learner.device)
+            e0.record(comm)
             ops.fedavg_into([src], [1.0], out, None)  # copy kernel reading peer memory over NVLink
+            e1.record(comm)
         comm.synchronize()  # the sender may reuse its buffer once the RPC returns
         self.stats["pulled"] += 1
         self.stats["pulled_bytes"] += ref.n * 4
+        self.stats["pulled_ms"] += e0.elapsed_time(e1)
         extra = {k: torch.tensor(v) for k, v in ref.extra.items()}
         return FlatParams(out, learner.layout, extra)
 
@@ -336,11 +341,13 @@ class FusedExchange:
         )
         clock_hz = 1.9e9
         timeout_cycles = int(Settings.AGGREGATION_TIMEOUT * clock_hz)
+        began = torch.cuda.Event(enable_timing=True)
         with torch.cuda.stream(learner.stream):
             arena.status.zero_()
             arena.abort.zero_()
+            began.record(learner.stream)
             ops.gossip_fused(arena.params, learner.w16, arena.geo.tile, seq, push, red, arena.abort, timeout_cycles, arena.status)
-            done = torch.cuda.Event()
+            done = torch.cuda.Event(enable_timing=True)
             done.record(learner.stream)
         # host watchdog: flip the abort word if a contributor disappears or the experiment stops
         t0 = time.time()
@@ -355,6 +362,7 @@ class FusedExchange:
         status = arena.status.cpu()
         learner._params_written_by_plane()
         self.proto.stats["fused"] += 1
+        self.proto.stats["fused_ms"] += began.elapsed_time(done)  # includes the wait for the slowest peer's tiles
         self.proto.stats["fused_bytes"] += arena.n * (2 if wire_bf16 else 4) * len(others)
         self.complete = int(status[0]) == 0
         if not self.complete:

@@ -46,6 +46,7 @@ def test_colocated_nodes_use_the_pull_path():
     stats = _run_federation([DEV], NvlinkMemoryProtocol, rounds=2, n=3, train_set=2)
     assert all(s["host"] == 0 for s in stats), stats  # nothing went through pickle
     assert sum(s["pulled"] for s in stats) > 0
+    assert sum(s["pulled_ms"] for s in stats) > 0.0  # device-timed (CUDA events on the copy stream)
     assert all(s["fused"] == 0 for s in stats)  # co-located: no kernels that wait on one another
 
 
@@ -58,6 +59,7 @@ def test_fused_exchange_across_gpus_in_process():
     stats = _run_federation([f"cuda:{i}" for i in range(ng)], NvlinkMemoryProtocol, rounds=3, train_set=ng)
     assert all(s["host"] == 0 for s in stats), stats
     assert all(s["fused"] == 3 for s in stats), stats
+    assert all(s["fused_ms"] > 0.0 for s in stats), stats  # device-timed, includes the wait for peers
 
 
 @pytest.mark.gpu
