@@ -75,6 +75,10 @@ class B200Learner(TorchLearner):
         self._graphs: Dict[Tuple[str, int], Any] = {}
         self._train_dev: Optional[Tuple[torch.Tensor, torch.Tensor]] = None
         self._eval_dev: Dict[str, Tuple[torch.Tensor, torch.Tensor]] = {}
+        # "stream" mode: the next round's splits travel host -> device on a copy stream while this round
+        # computes (staging buffers, see _prefetch / _take_prefetched)
+        self._stage: Dict[str, Dict[str, Any]] = {}
+        self._copy_stream: Optional[torch.cuda.Stream] = None
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self.kernel_launches_per_epoch = 0
@@ -262,14 +266,60 @@ class B200Learner(TorchLearner):
             x_dev = x_dev.permute(0, 2, 3, 1)
         return x_dev.reshape(x_dev.shape[0], -1).contiguous()
 
+    def _prefetch(self, split: str) -> None:
+        """Stream mode: start the host -> device copy of ``split`` for the NEXT round now, on the
+        copy stream, into staging buffers (the live buffers are still being read by this round)."""
+        if self.data_mode != "stream" or not hasattr(self.data, "pinned_tensors"):
+            return
+        dst = self._train_dev if split == "train" else self._eval_dev.get(split)
+        if dst is None:
+            return
+        x, y = self.data.pinned_tensors(split)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        cs = self._copy_stream
+        st = self._stage.get(split)
+        if st is None:
+            st = self._stage[split] = {
+                "x": torch.empty(x.shape, dtype=x.dtype, device=self.device),
+                "y": torch.empty(y.shape, dtype=y.dtype, device=self.device),
+                "ready": None, "taken": None,
+            }  # fmt: skip
+        if st["ready"] is not None:
+            return  # one already in flight and not consumed yet
+        if st["taken"] is not None:
+            cs.wait_event(st["taken"])  # the last consumer's device copy out of the staging buffer
+        with torch.cuda.stream(cs):
+            st["x"].copy_(x, non_blocking=True)
+            st["y"].copy_(y, non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record(cs)
+        st["ready"] = ready
+        self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+
+    def _take_prefetched(self, split: str, dst: Tuple[torch.Tensor, torch.Tensor]) -> bool:
+        """Move a finished prefetch into the live buffers (device copy on the learner's stream)."""
+        st = self._stage.get(split)
+        if st is None or st["ready"] is None:
+            return False
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(st["ready"])
+        dst[0].copy_(self._rows(st["x"]))
+        dst[1].copy_(st["y"])  # int64 travels, the cast is on the device
+        taken = torch.cuda.Event()
+        taken.record(cur)
+        st["ready"], st["taken"] = None, taken
+        return True
+
     def _train_data(self) -> Tuple[torch.Tensor, torch.Tensor]:
         if self.data_mode == "stream" or self._train_dev is None:
             if self._train_dev is not None and self.data_mode == "stream":
                 # same device buffers every round so captured graphs stay valid
-                x, y = self.data.pinned_tensors("train")
-                self._train_dev[0].copy_(self._rows(x.to(self.device, non_blocking=True)))
-                self._train_dev[1].copy_(y.to(self.device, non_blocking=True))
-                self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+                if not self._take_prefetched("train", self._train_dev):
+                    x, y = self.data.pinned_tensors("train")
+                    self._train_dev[0].copy_(self._rows(x.to(self.device, non_blocking=True)))
+                    self._train_dev[1].copy_(y.to(self.device, non_blocking=True))
+                    self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
             else:
                 self._train_dev = self._upload("train")
         return self._train_dev
@@ -279,10 +329,11 @@ class B200Learner(TorchLearner):
         if cur is None:
             self._eval_dev[split] = cur = self._upload(split)
         elif self.data_mode == "stream":
-            x, y = self.data.pinned_tensors(split)
-            cur[0].copy_(self._rows(x.to(self.device, non_blocking=True)))
-            cur[1].copy_(y.to(self.device, non_blocking=True))
-            self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+            if not self._take_prefetched(split, cur):
+                x, y = self.data.pinned_tensors(split)
+                cur[0].copy_(self._rows(x.to(self.device, non_blocking=True)))
+                cur[1].copy_(y.to(self.device, non_blocking=True))
+                self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
         return cur
 
     # --------------------------------------------------------- fused forward
@@ -526,6 +577,7 @@ class B200Learner(TorchLearner):
                 up.record()
                 self.h2d_bytes += n * 4
                 tb = time.perf_counter()
+                self._prefetch("val")  # stream mode: this epoch's validation split travels during the epoch
                 ep["graph"].replay()
                 ops.add_launches(ep["launches"])
                 self.kernel_launches_per_epoch = ep["launches"]
@@ -537,6 +589,10 @@ class B200Learner(TorchLearner):
                 ep["perm_up2"] = up
                 ep["perm_host"].copy_(torch.randperm(n, dtype=torch.int32))
                 ep["perm_ready"] = True
+                if e == self.epochs - 1:
+                    # stream mode: next round's splits start travelling while the device runs this epoch
+                    self._prefetch("train")
+                    self._prefetch("test")
                 tc = time.perf_counter()
                 # per-epoch validation, as Lightning does for the reference (mlp.py:82-91)
                 val = self._eval_split("val")

@@ -335,3 +335,38 @@ def test_chain_kernel_matches_per_link_launches(mode):
     assert all(abs(a - b) < 1e-5 for a, b in zip(results[0][2], results[1][2])), (results[0][2], results[1][2])
     assert torch.allclose(results[0][1], results[1][1], atol=1e-6, rtol=1e-5)
     assert torch.allclose(results[0][0], results[1][0], atol=1e-5)
+
+
+def test_stream_mode_prefetch_matches_resident_mode():
+    """``data_mode="stream"`` copies the splits from pinned host memory every round - the next round's
+    on a copy stream while this round computes.  Same shuffles => the same model as the resident mode,
+    and the staged copy is what the next round trains on."""
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.models import MLP
+
+    out = {}
+    for mode in ("resident", "stream"):
+        dm = _dm(n_train=640, n_test=128)
+        torch.manual_seed(11)
+        learner = B200Learner(MLP(seed=2), dm, mode, epochs=1, device=DEV, data_mode=mode)
+        res = []
+        for _ in range(3):
+            res.append(learner.evaluate()["test_loss"])
+            learner.fit()
+        out[mode] = (learner.flat.clone(), res, learner.h2d_bytes)
+        if mode == "stream":
+            # rounds 2 and 3 took their splits from the staging buffers
+            assert learner._stage["train"]["taken"] is not None and learner._stage["test"]["taken"] is not None
+            # what is staged now is what the next round will see: change the host copy, prefetch again
+            x_host, _ = dm.pinned_tensors("train")
+            learner._take_prefetched("train", learner._train_dev)  # drain the copy issued by the last fit
+            x_host.zero_()
+            learner._prefetch("train")
+            with torch.cuda.stream(learner.stream):
+                x_dev, _ = learner._train_data()
+            learner.stream.synchronize()
+            assert float(x_dev.abs().max()) == 0.0
+        learner.close()
+    assert torch.equal(out["resident"][0], out["stream"][0])
+    assert out["resident"][1] == out["stream"][1]
+    assert out["stream"][2] > 3 * out["resident"][2] * 0.9  # every round's splits were copied
