@@ -285,6 +285,8 @@ class B200Learner(TorchLearner):
                 "y": torch.empty(y.shape, dtype=y.dtype, device=self.device),
                 "ready": None, "taken": None,
             }  # fmt: skip
+            for t in (st["x"], st["y"]):
+                t.record_stream(cs)  # written on the copy stream: the allocator must not recycle it early
         if st["ready"] is not None:
             return  # one already in flight and not consumed yet
         if st["taken"] is not None:
