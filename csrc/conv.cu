@@ -11,6 +11,10 @@
 // transpose for the weight-gradient GEMM whose K dimension is the pixel count), and
 // fold everything that is not a GEMM - ReLU masks, pooling, bias gradients, layout
 // changes - into single passes.
+//
+// The ResNet plan uses the tap-major variants further down (im2col_kc / col2im_kc, K ordered
+// (i, j, c), 16-byte channel vectors, weights repacked by conv_pack) and needs no transposed
+// column matrix: its backward GEMMs read MN-major operands.
 #include "common.cuh"
 
 using namespace p2pfl;

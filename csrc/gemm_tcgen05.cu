@@ -6,7 +6,7 @@
 //
 // Structure (one 128 x BN output tile per CTA, 6 warps):
 //   warp 0      TMA producer : cp.async.bulk.tensor (128B swizzle) global->smem,
-//                              4-stage ring, mbarrier complete_tx
+//                              mbarrier ring sized to the K loop, complete_tx
 //   warp 1      MMA issuer   : one elected lane issues tcgen05.mma (kind::f16,
 //                              bf16 x bf16 -> fp32) with smem descriptors;
 //                              accumulator lives in TMEM; tcgen05.commit frees
@@ -15,9 +15,13 @@
 //                              alpha / bias / ReLU / ReLU-mask / row-sum, then
 //                              up to four output layouts (fp32|bf16, direct|transposed)
 //
-// Operands are both K-major ("TN"); callers keep activations in both
-// orientations instead (see learning/b200_learner.py), which keeps every GEMM
-// of the train step on this one kernel.
+// Operands are K-major by default; an operand may also be MN-major (stored [K, MN]), which lets
+// the backward GEMMs of the convolutions read dZ, the column matrix and the weights in place.
+// Kernels in this file:
+//   gemm_tn_kernel             one tile per CTA, up to 4 problems per launch, optional split-K
+//   gemm_tn_persistent_kernel  one CTA per SM walks the tiles, two TMEM accumulators
+//   gemm_chain_kernel          a list of dependent links walked by one CTA or by ONE thread-block
+//                              cluster (tiles dealt to its CTAs, barrier.cluster between links)
 #include <cstdlib>
 #include <cuda.h>
 #include <string.h>

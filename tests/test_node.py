@@ -250,7 +250,7 @@ def test_own_model_push_policy():
 def test_trainer_status_point_to_point():
     """``DIRECT_TRAINSET_STATUS``: `models_aggregated` reaches the round's trainers directly (they are
     not all neighbours on a line) instead of being flooded; the experiment must end the same way."""
-    Settings.TRAIN_SET_SIZE = 3
+    Settings.TRAIN_SET_SIZE = 4  # three peers each, at most two of them neighbours on a line: never all direct
     Settings.DIRECT_TRAINSET_STATUS = True
     nodes = _line(6, InMemoryCommunicationProtocol)
     seen = []
