@@ -308,7 +308,7 @@ def test_pdl_on_and_off_give_identical_training():
     assert torch.equal(flats[0], flats[1])
 
 
-@pytest.mark.parametrize("mode", ["chain1", "cluster2", "cluster8", "cluster16"])
+@pytest.mark.parametrize("mode", ["chain1", "cluster1", "cluster2", "cluster8", "cluster16"])
 def test_chain_kernel_matches_per_link_launches(mode):
     """The GEMM chain - one CTA, or one thread-block cluster that also walks the weight-gradient
     link - must reproduce the per-link launches: same tiles, same MMA order, same epilogues (only
