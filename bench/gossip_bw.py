@@ -39,7 +39,7 @@ def main() -> None:
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     from p2pfl_b200 import ops
-    from p2pfl_b200.parallel.arena import ArenaGeometry, DeviceArena, PeerArena
+    from p2pfl_b200.parallel.arena import DeviceArena, PeerArena
 
     dev = torch.device(f"cuda:{local}")
     flush = torch.empty(64 << 20, dtype=torch.float32, device=dev)

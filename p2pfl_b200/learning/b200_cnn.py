@@ -20,7 +20,7 @@ The object owns the step's buffers; ``B200Learner`` captures the epoch as a CUDA
 
 from __future__ import annotations
 
-from typing import Any, Dict, List
+from typing import Any, Dict
 
 import torch
 from torch import nn

@@ -18,7 +18,7 @@ learners use, and ``pinned_tensors(split)`` for the end-to-end H2D path.
 
 from __future__ import annotations
 
-from typing import Dict, Optional, Tuple
+from typing import Dict, Tuple
 
 import torch
 from torch.utils.data import DataLoader, TensorDataset

@@ -7,7 +7,6 @@ import pytest
 import torch
 
 from p2pfl_b200.exceptions import DecodingParamsError, ModelNotMatchingError, NoModelsToAggregateError
-from p2pfl_b200.learning import codec
 from p2pfl_b200.learning.aggregators.fedavg import FedAvg, fedavg_state_dicts
 from p2pfl_b200.learning.data import MnistFederatedDM
 from p2pfl_b200.learning.params import FlatParams, ParamLayout
