@@ -368,5 +368,6 @@ def test_stream_mode_prefetch_matches_resident_mode():
             assert float(x_dev.abs().max()) == 0.0
         learner.close()
     assert torch.equal(out["resident"][0], out["stream"][0])
-    assert out["resident"][1] == out["stream"][1]
+    # (the evaluation's loss sum is reduced with atomics: equal up to the order of the additions)
+    assert all(abs(a - b) < 1e-5 * max(1.0, abs(a)) for a, b in zip(out["resident"][1], out["stream"][1])), out
     assert out["stream"][2] > 3 * out["resident"][2] * 0.9  # every round's splits were copied
