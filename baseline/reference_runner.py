@@ -21,7 +21,11 @@ from typing import Any, Dict, List
 import torch
 
 
-def run_reference_experiment(n_nodes: int, steps: int, warmup: int, fast: bool, timeout: float) -> Dict[str, Any]:
+def run_reference_experiment(n_nodes: int, steps: int, warmup: int, fast: bool, timeout: float,
+                             budget: float = 600.0) -> Dict[str, Any]:  # fmt: skip
+    """``budget``: seconds of run time after which the timed region is closed at the last round
+    boundary seen (the line then says ``"truncated": true`` and reports the rounds it did time), so a
+    slow stock run still yields a number inside the driver's per-run limit."""
     from p2pfl.communication.memory.memory_communication_protocol import InMemoryCommunicationProtocol
     from p2pfl.learning.pytorch.mnist_examples.models.mlp import MLP
     from p2pfl.management.logger import logger as ref_logger
@@ -63,24 +67,39 @@ def run_reference_experiment(n_nodes: int, steps: int, warmup: int, fast: bool, 
 
     W, K = warmup, steps
     total = W + K + 1
-    marks: Dict[str, float] = {}
+    marks: Dict[str, Any] = {}
     stop = threading.Event()
+    import pytorch_lightning as shim_pl  # the shim counts the bytes it copies (see its COUNTERS)
+
+    used = sorted({i % n_gpu for i in range(n_nodes)}) if n_gpu else []
+    flush = {d: torch.empty(bench.L2_FLUSH_BYTES // 4, dtype=torch.float32, device=f"cuda:{d}") for d in used}
+
+    def sync_all() -> None:
+        for d in used:
+            torch.cuda.synchronize(d)
 
     def watch() -> None:
         # all nodes finished >= r rounds  <=>  min over nodes of state.round >= r
+        seen = -1
         while not stop.is_set():
             rounds = [n.state.round for n in nodes]
             if all(r is not None for r in rounds):
                 lo = min(rounds)
-                if lo >= W and "t0" not in marks:
-                    if n_gpu:
-                        torch.cuda.synchronize()
-                    marks["t0"] = time.perf_counter()
-                if lo >= W + K and "t1" not in marks:
-                    if n_gpu:
-                        torch.cuda.synchronize()
-                    marks["t1"] = time.perf_counter()
-                    return
+                if lo > seen:
+                    seen = lo
+                    for buf in flush.values():
+                        buf.zero_()  # same L2 flush between rounds as the other arm
+                    if lo >= W and "t0" not in marks:
+                        sync_all()
+                        marks["c0"] = dict(shim_pl.COUNTERS)
+                        marks["t0"] = time.perf_counter()
+                    if lo > W and "t0" in marks:
+                        # every later boundary is a candidate end of the timed region
+                        sync_all()
+                        marks["last"] = (lo - W, time.perf_counter(), dict(shim_pl.COUNTERS))
+                    if lo >= W + K and "t1" not in marks:
+                        marks["t1"] = marks["last"][1]
+                        return
             time.sleep(0.0005)
 
     sampler = bench.ClockSampler(0)
@@ -89,31 +108,53 @@ def run_reference_experiment(n_nodes: int, steps: int, warmup: int, fast: bool, 
     th.start()
     t_begin = time.time()
     started_sampler = False
+    truncated = False
     while time.time() - t_begin < timeout:
         if "t0" in marks and not started_sampler:
             sampler.start()
             started_sampler = True
         if "t1" in marks:
             break
+        if time.time() - t_begin > budget and "last" in marks:
+            truncated = True  # out of budget: close the timed region at the last boundary seen
+            break
         time.sleep(0.01)
     clocks = sampler.stop() if started_sampler else None
     stop.set()
+    th.join(timeout=5)
+    if truncated:
+        for n in nodes:  # the reference's own API for ending an experiment early
+            try:
+                n.set_stop_learning()
+            except Exception:
+                pass
     # let the experiment end, then tear down
-    end_wait = time.time() + 120
+    end_wait = time.time() + (20 if truncated else 120)
     while any(n.state.round is not None for n in nodes) and time.time() < end_wait:
         time.sleep(0.05)
+    final = {}
+    try:
+        final = bench.final_metrics(ref_logger.get_global_logs())
+    except Exception:
+        pass
     for n in nodes:
         try:
             n.stop()
         except Exception:
             pass
-    if "t1" not in marks:
-        return {"impl": "reference", "unavailable": f"reference did not complete {W + K} rounds in {timeout}s"}
-    ms = (marks["t1"] - marks["t0"]) * 1e3
-    samples = n_nodes * n_train * K
+    if "last" not in marks:
+        return {"impl": "reference", "unavailable": f"reference did not complete {W + 1} rounds in {min(timeout, budget):.0f}s"}
+    done, t_end, c_end = marks["last"]
+    done = min(done, K)
+    ms = (t_end - marks["t0"]) * 1e3
+    samples = n_nodes * n_train * done
+    value = samples / (ms / 1e3)
+    h2d = (c_end["h2d"] - marks["c0"]["h2d"]) / done / n_nodes
+    d2h = (c_end["d2h"] - marks["c0"]["d2h"]) / done / n_nodes
+    K = done
     return {
         "metric": "fl_train_samples_per_sec",
-        "value": samples / (ms / 1e3),
+        "value": value,
         "unit": "samples/s",
         "n_gpus": n_nodes,
         "steps": K,
@@ -126,20 +167,27 @@ def run_reference_experiment(n_nodes: int, steps: int, warmup: int, fast: bool, 
         "dtype": "fp32",
         "data": "synthetic",
         "impl": "reference",
-        "config": {
-            "model": "MNIST-shaped MLP 784-256-128-10 (reference mlp.py)",
-            "nodes": n_nodes,
-            "topology": "full",
-            "aggregator": "FedAvg, all nodes in the train set",
-            "epochs_per_round": 1,
-            "train_samples_per_node": n_train,
-            "global_batch": bench.BATCH * n_nodes,
-            "seq_len": None,
-            "parallelism": f"fl{n_nodes} (reference simulation mode: N nodes in one process, one GPU per node)",
+        "config": bench.bench_config(n_nodes, n_train),
+        "arm": {
+            "model_class": "reference mlp.py MLP (fp32, TF32 off)",
+            "mode": "reference simulation mode: N nodes in one process, one GPU per node",
             "protocol": "InMemoryCommunicationProtocol",
             "settings": "pacing sleeps zeroed (--ref-fast)" if fast else "reference defaults (stock)",
             "shim": "pytorch_lightning/torchmetrics stand-ins (baseline/shim); synthetic MNIST-shaped datamodule",
             "timing": "host clock between observed round boundaries, cuda synchronize on both sides",
         },
+        "truncated": truncated,
+        "final": {"test_loss": final.get("test_loss"), "test_accuracy": final.get("test_metric"), "round": final.get("round")},
         "clocks": clocks,
+        # the host-clock number above already is end to end (every batch travels host -> device, every
+        # logged metric device -> host, the module moves to the device and back around each fit / test)
+        "e2e": {
+            "value": value,
+            "unit": "samples/s",
+            "ms_per_step": ms / K,
+            "h2d_bytes_per_step": h2d,
+            "d2h_bytes_per_step": d2h,
+            "note": "per node and round, counted by the Lightning shim from the tensors it copies; the reference's own "
+                    "model encode/decode copies are not counted",
+        },
     }

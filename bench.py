@@ -18,6 +18,7 @@ Prints ONE JSON line (rank 0).  See DESIGN.md "bench contract" for the fields.
 from __future__ import annotations
 
 import argparse
+import datetime
 import json
 import os
 import statistics
@@ -48,21 +49,72 @@ def dist_env() -> Dict[str, int]:
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock, power and throttle reasons DURING the timed region (B200_PROFILING.md recipe).
+
+    In-process NVML thread, 100 ms period (one per rank: every rank carries the same, negligible
+    load - a ``nvidia-smi -lms`` child on rank 0 alone made rank 0 the straggler of every
+    exchange).  Falls back to the ``nvidia-smi`` query loop when the NVML binding is missing."""
 
     Q = (
         "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
     )
+    PERIOD = 0.1
 
     def __init__(self, gpu_index: int) -> None:
         self.gpu = gpu_index
         self.proc: Optional[subprocess.Popen] = None
         self.lines: List[str] = []
         self._t: Optional[threading.Thread] = None
+        self._stop = threading.Event()
+        self._nvml: Any = None
+        self._handle: Any = None
+        self._rows: List[Any] = []  # (sm MHz, max MHz, watts, reason bits)
+
+    def _nvml_open(self) -> bool:
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            handle = None
+            try:
+                import torch
+
+                uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+                handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+            except Exception:
+                handle = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+            pynvml.nvmlDeviceGetClockInfo(handle, pynvml.NVML_CLOCK_SM)
+            self._nvml, self._handle = pynvml, handle
+            return True
+        except Exception:
+            self._nvml = None
+            return False
 
     def start(self) -> None:
+        self._stop.clear()
+        if self._nvml is not None or self._nvml_open():
+            nv, h = self._nvml, self._handle
+            mx = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+
+            def poll() -> None:
+                while True:
+                    try:
+                        try:
+                            bits = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                        except Exception:
+                            bits = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                        self._rows.append((float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), mx,
+                                           nv.nvmlDeviceGetPowerUsage(h) / 1000.0, bits))  # fmt: skip
+                    except Exception:
+                        pass
+                    if self._stop.wait(self.PERIOD):
+                        return
+
+            self._t = threading.Thread(target=poll, daemon=True)
+            self._t.start()
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.gpu)],
@@ -81,6 +133,27 @@ class ClockSampler:
         self._t.start()
 
     def stop(self) -> Dict[str, Any]:
+        if self._nvml is not None:
+            self._stop.set()
+            if self._t is not None:
+                self._t.join(timeout=1.0)
+            nv = self._nvml
+            rows, self._rows = self._rows, []
+            names = {
+                "hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap,
+            }
+            reasons = sorted(k for k, bit in names.items() if any(r[3] & bit for r in rows))
+            return {
+                "sm_mhz": statistics.median(r[0] for r in rows) if rows else None,
+                "sm_max_mhz": max(r[1] for r in rows) if rows else None,
+                "power_w_max": max(r[2] for r in rows) if rows else None,
+                "samples": len(rows),
+                "reasons": reasons,
+                "how": "in-process NVML thread, 100 ms",
+            }
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -110,7 +183,60 @@ class ClockSampler:
             "power_w_max": max(power) if power else None,
             "samples": len(sm),
             "reasons": sorted(reasons),
+            "how": "nvidia-smi -lms 100",
         }
+
+
+def merge_clocks(per_rank: List[Optional[Dict[str, Any]]]) -> Optional[Dict[str, Any]]:
+    """One clocks record for the job: lowest median SM clock over the ranks, union of the reasons."""
+    rows = [c for c in per_rank if c and c.get("sm_mhz") is not None]
+    if not rows:
+        return per_rank[0] if per_rank else None
+    return {
+        "sm_mhz": min(c["sm_mhz"] for c in rows),
+        "sm_max_mhz": max(c["sm_max_mhz"] for c in rows),
+        "power_w_max": max(c.get("power_w_max") or 0.0 for c in rows),
+        "samples": sum(c.get("samples", 0) for c in rows),
+        "reasons": sorted({r for c in rows for r in c.get("reasons", [])}),
+        "ranks": len(rows),
+        "how": rows[0].get("how"),
+    }
+
+
+def bench_config(world: int, n_train: int) -> Dict[str, Any]:
+    """The config block BOTH arms print: what is being measured, not how an arm does it."""
+    return {
+        "model": "MNIST-shaped MLP 784-256-128-10 (235146 params)",
+        "baseline_config": "MNIST-shaped MLP, N nodes (one per B200), fully connected topology, FedAvg",
+        "nodes": world,
+        "topology": "full",
+        "aggregator": "FedAvg, all nodes in the train set",
+        "epochs_per_round": 1,
+        "train_samples_per_node": n_train,
+        "global_batch": BATCH * world,
+        "batch_per_node": BATCH,
+        "seq_len": None,
+        "parallelism": f"fl{world} (one federated node per GPU)",
+        "step_definition": "one federated round: evaluate + 1 local epoch (+validation) + model exchange + FedAvg",
+        "l2": f"flushed between rounds ({L2_FLUSH_BYTES >> 20} MiB memset)",
+    }
+
+
+def final_metrics(global_logs: Dict[str, Any]) -> Dict[str, Any]:
+    """Last ``test_loss`` / ``test_metric`` each node logged, averaged over the nodes of this process."""
+    out: Dict[str, Any] = {}
+    for metric in ("test_loss", "test_metric"):
+        last = []
+        for nodes in global_logs.values():
+            for series in nodes.values():
+                vals = series.get(metric)
+                if vals:
+                    last.append(max(vals, key=lambda rv: rv[0]))
+        if last:
+            out[metric] = sum(v for _, v in last) / len(last)
+            out["round"] = max(r for r, _ in last)
+            out["nodes_reporting"] = len(last)
+    return out
 
 
 # ------------------------------------------------------------------ own arm
@@ -128,7 +254,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     if rank == 0:
         entry.build()
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"), timeout=datetime.timedelta(hours=2))
         dist.barrier()
 
     from p2pfl_b200 import ops
@@ -194,8 +320,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
                 if world > 1:
                     dist.barrier()
                 torch.cuda.synchronize()
-                if rank == 0:
-                    sampler.start()
+                sampler.start()
                 marks["launch0"] = ops.launch_count()
                 lr = node.state.learner
                 marks["h2d0"], marks["d2h0"] = lr.h2d_bytes, lr.d2h_bytes
@@ -215,10 +340,9 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
                 marks["ht1"] = dict(getattr(lr, "host_seconds", {}))
                 marks["launch1"] = ops.launch_count()
                 marks["h2d1"], marks["d2h1"] = lr.h2d_bytes, lr.d2h_bytes
+                marks["clocks"] = sampler.stop()
                 if world > 1:
                     dist.barrier()
-                if rank == 0:
-                    marks["clocks"] = sampler.stop()
 
         node.state.round_listeners = [on_round]
         if world > 1:
@@ -238,9 +362,12 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
             [marks["launch1"] - marks["launch0"], marks["h2d1"] - marks["h2d0"], marks["d2h1"] - marks["d2h0"]],
             dtype=torch.float64, device=f"cuda:{local}",
         )  # fmt: skip
+        clocks = [marks.get("clocks")]
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+            clocks = [None] * world
+            dist.all_gather_object(clocks, marks.get("clocks"))
         trace_dir = os.environ.get("P2PFL_BENCH_TRACE")
         if trace_dir:
             # per-rank host timeline of the timed region (ms per round), for scaling analysis
@@ -252,12 +379,33 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
                 json.dump(per, fh)
         return {
             "ms": float(t[0]), "wall_ms": float(t[1]), "launches": int(cnt[0]),
-            "h2d": float(cnt[1]), "d2h": float(cnt[2]), "clocks": marks.get("clocks"),
+            "h2d": float(cnt[1]), "d2h": float(cnt[2]), "clocks": merge_clocks(clocks),
             "timings": {k: v - marks.get("tim0", {}).get(k, 0.0) for k, v in marks.get("tim1", {}).items()},
         }  # fmt: skip
 
     dev = measure("resident")
     e2e = measure("stream")
+
+    # Correctness of what was just timed: after the last round every node holds the same aggregate
+    # (all nodes are trainers; the fused exchange sums in train-set order => identical bits), so a
+    # checksum of the live parameters must agree across ranks; and the model must have learned.
+    lr = node.state.learner
+    with torch.cuda.stream(lr.stream):
+        flat = lr.flat.double()
+        chk = torch.stack([flat.sum(), flat.abs().sum(), (flat * flat).sum()])
+    lr.stream.synchronize()
+    lo, hi = chk.clone(), chk.clone()
+    if world > 1:
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    bit_identical = bool(torch.equal(lo, hi))
+    ranks_equal = bool(((hi - lo).abs() <= 1e-6 * hi.abs().clamp_min(1e-30)).all()) and bool(torch.isfinite(chk).all())
+    fm = final_metrics(logger.get_global_logs())
+    fm_t = torch.tensor([fm.get("test_loss", float("nan")), fm.get("test_metric", float("nan"))], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(fm_t, op=dist.ReduceOp.SUM)
+        fm_t /= world
+    stats = dict(getattr(node._communication_protocol, "stats", {}))
     node.stop()
 
     samples = world * n_train * K
@@ -278,22 +426,14 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         "dtype": "bf16",
         "data": "synthetic",
         "impl": "p2pfl_b200",
-        "config": {
-            "model": "MNIST-shaped MLP 784-256-128-10 (235146 params)",
-            "baseline_config": "MNIST-shaped MLP, N nodes (one per B200), fully connected topology, FedAvg",
-            "nodes": world,
-            "topology": "full",
-            "aggregator": "FedAvg, all nodes in the train set",
-            "epochs_per_round": 1,
-            "train_samples_per_node": n_train,
-            "global_batch": BATCH * world,
-            "batch_per_node": BATCH,
-            "seq_len": None,
-            "parallelism": f"fl{world} (one federated node per GPU)",
-            "step_definition": "one federated round: evaluate + 1 local epoch (+validation) + model exchange + FedAvg",
-            "l2": f"flushed between rounds ({L2_FLUSH_BYTES >> 20} MiB memset)",
+        "config": bench_config(world, n_train),
+        "arm": {
             "control_plane": "in-memory (1 node)" if world == 1 else "gRPC loopback + NVLink device data plane",
+            "timing": "CUDA events on the learner's stream, max over ranks",
         },
+        "final": {"test_loss": float(fm_t[0]), "test_accuracy": float(fm_t[1]), "round": fm.get("round"),
+                  "param_checksum": [float(v) for v in chk], "ranks_equal": ranks_equal, "bit_identical": bit_identical},
+        "data_plane": {k: (round(v, 3) if isinstance(v, float) else v) for k, v in stats.items()},
         "clocks": dev["clocks"],
         "e2e": {
             "value": e2e_value,
@@ -311,6 +451,9 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if not ranks_equal:
+        sys.stderr.write(f"rank {rank}: parameters differ across ranks after the last round: min {lo.tolist()} max {hi.tolist()}\n")
+        raise SystemExit(3)
     return out if rank == 0 else {}
 
 
@@ -325,10 +468,16 @@ def run_reference(args: argparse.Namespace) -> Dict[str, Any]:
     import torch
     import torch.distributed as dist
 
+    host_group = None
     if world > 1:
         torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"), timeout=datetime.timedelta(hours=2))
         dist.barrier()
+        torch.cuda.synchronize()
+        # Ranks > 0 idle while rank 0 runs the reference (below).  They must wait on the HOST: an NCCL
+        # barrier parks a spinning kernel on every other GPU, which (a) time-slices against the
+        # reference's own nodes on those GPUs and (b) trips the NCCL watchdog after 10 minutes.
+        host_group = dist.new_group(backend="gloo", timeout=datetime.timedelta(hours=2))
     out: Dict[str, Any] = {}
     if rank == 0:
         # The reference's own multi-node mode is one process with N Node objects
@@ -337,9 +486,12 @@ def run_reference(args: argparse.Namespace) -> Dict[str, Any]:
         sys.path[:0] = [shim, ref_root]
         from baseline.reference_runner import run_reference_experiment
 
-        out = run_reference_experiment(world, args.steps, args.warmup, args.ref_fast, args.timeout)
+        try:
+            out = run_reference_experiment(world, args.steps, args.warmup, args.ref_fast, args.timeout, args.ref_budget)
+        except Exception as e:  # the line below must still be printed, and the other ranks released
+            out = {"impl": "reference", "unavailable": f"reference run failed: {type(e).__name__}: {e}"[:300]}
     if world > 1:
-        dist.barrier()
+        dist.barrier(group=host_group)
         dist.destroy_process_group()
     return out
 
@@ -352,6 +504,8 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ref-fast", action="store_true", help="zero the reference's pacing sleeps (not the stock path)")
     ap.add_argument("--timeout", type=float, default=1500.0)
+    ap.add_argument("--ref-budget", type=float, default=600.0,
+                    help="reference arm: seconds after which the timed region is closed at the last finished round")
     args = ap.parse_args()
     env = dist_env()
     if args.gpus != env["world"] and env["world"] == 1 and args.gpus > 1:

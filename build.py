@@ -30,7 +30,9 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, bringup: bool = False) -> str:
+    """``bringup``: compile the per-link clock stamps and the mbarrier-wait trap into the GEMM kernels
+    (-DP2PFL_BRINGUP, for experiments with tools/profile_target.py only; never for a measured run)."""
     if not force and not needs_build():
         return OUT
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
@@ -38,6 +40,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     cmd = [nvcc, *ARCH, "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-shared"]
     if verbose:
         cmd += ["-Xptxas", "-v"]
+    if bringup:
+        cmd += ["-DP2PFL_BRINGUP"]
     cmd += sources() + ["-o", OUT]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
@@ -49,5 +53,5 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    path = build(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    path = build(force="--force" in sys.argv or "--bringup" in sys.argv, verbose="-v" in sys.argv, bringup="--bringup" in sys.argv)
     print(path)

@@ -76,7 +76,9 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
+#ifdef P2PFL_BRINGUP
   const long long t0 = clock64();
+#endif
   while (true) {
     asm volatile(
         "{\n\t.reg .pred P;\n\t"
@@ -86,8 +88,10 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "r"(bar), "r"(parity)
         : "memory");
     if (done) break;
-    // bring-up guard: a protocol bug must fault, not hang the GPU
+#ifdef P2PFL_BRINGUP
+    // bring-up guard (-DP2PFL_BRINGUP only): a protocol bug faults instead of hanging the GPU
     if (clock64() - t0 > 4000000000LL) __trap();
+#endif
   }
 }
 
@@ -171,17 +175,26 @@ __device__ __forceinline__ uint32_t make_idesc(uint32_t bn, uint32_t mn = 0) {
 // Drain one 128 x bn accumulator tile: TMEM -> registers -> fused epilogue -> global.
 // Called by the four epilogue warps; `q` is the warp's TMEM lane quarter.
 __device__ __forceinline__ void epilogue_tile(const Epilogue& ep_mem, int M, int N, int m0, int n0, uint32_t bn,
-                                              uint32_t tmem_base, int q, int lane, bool single_n_tile,
-                                              long long* dbg = nullptr) {
+                                              uint32_t tmem_base, int q, int lane, bool single_n_tile
+#ifdef P2PFL_BRINGUP
+                                              , long long* dbg = nullptr
+#endif
+) {
   // by value: read through the reference (shared or constant memory), every field would be
   // reloaded after each global store - the stores might alias it as far as the compiler knows
   const Epilogue ep = ep_mem;
   const int m = m0 + q * 32 + lane;
+#ifdef P2PFL_BRINGUP
 #define EPI_STAMP(slot) \
   if (dbg && lane == 0) dbg[slot] = clock64()
+#else
+#define EPI_STAMP(slot)
+#endif
   EPI_STAMP(0);
   const float bias_row = (ep.bias && ep.bias_per_row && m < M) ? ep.bias[m] : 0.f;
+#ifdef P2PFL_BRINGUP
   if (dbg && bias_row == 123456.f) dbg[7] = 1;  // (forces the load to complete before the next stamp)
+#endif
   EPI_STAMP(1);
 #pragma unroll 1
   for (int c = 0; c < (int)bn / 32; ++c) {
@@ -231,7 +244,9 @@ __device__ __forceinline__ void epilogue_tile(const Epilogue& ep_mem, int M, int
       }
     }
     const int valid = (N - nb) < 32 ? (N - nb) : 32;
+#ifdef P2PFL_BRINGUP
     if (dbg && x[0] == 123456.f) dbg[7] = 2;
+#endif
     EPI_STAMP(3);
     if (m < M) {
       if (ep.rowsum) {
@@ -801,9 +816,11 @@ struct ChainScalars {
   int32_t idx[kChainMaxPhases];
   int32_t cnt[kChainMaxPhases];   // GEMM link: idx .. idx+cnt-1 are independent and share the link
   int32_t n_phases;
-  int32_t n_iter;  // bring-up aid: walk the whole list this many times in ONE launch (1 = normal)
+  int32_t pad_;
   p2pfl_ce_args ce;
-  long long* stamps;  // bring-up aid (nullable): [link][8] SM-clock stamps of CTA 0, see p2pfl_gemm_chain_set_stamps
+#ifdef P2PFL_BRINGUP
+  long long* stamps;  // [link][8] SM-clock stamps of CTA 0, see p2pfl_gemm_chain_set_stamps
+#endif
 };
 static_assert(sizeof(ChainScalars) % 4 == 0, "copied word by word");
 
@@ -857,10 +874,17 @@ __device__ __forceinline__ ChainTile chain_locate(const ChainScalars& g, int gi0
 // log-softmax + cross-entropy forward/backward by the 128 epilogue threads (one warp per row)
 // `scratch`: idle shared memory (the stage ring between links) for B * (C + 1) words, or null.
 // Staging the logits there costs ONE round trip to L2; read in place, every row pays three.
-__device__ void chain_ce(const p2pfl_ce_args& a_mem, int ewarp, int lane, float* s_db, float* scratch, bool small,
-                         long long* dbg = nullptr) {
+__device__ void chain_ce(const p2pfl_ce_args& a_mem, int ewarp, int lane, float* s_db, float* scratch, bool small
+#ifdef P2PFL_BRINGUP
+                         , long long* dbg = nullptr
+#endif
+) {
+#ifdef P2PFL_BRINGUP
 #define CE_STAMP(slot) \
   if (dbg && ewarp == 0 && lane == 0) dbg[slot] = clock64()
+#else
+#define CE_STAMP(slot)
+#endif
   CE_STAMP(0);
   const p2pfl_ce_args a = a_mem;  // by value, for the same reason as in epilogue_tile
   const int et = ewarp * 32 + lane;
@@ -1033,10 +1057,13 @@ gemm_chain_kernel(const __grid_constant__ ChainArgs ga) {
   // links are separated by the hardware cluster barrier (release / acquire)
   const int crank = (int)cluster_ctarank(), csize = (int)cluster_nctarank();
 
+#ifdef P2PFL_BRINGUP
   long long* const stamps = (g.stamps && crank == 0) ? g.stamps : nullptr;
 #define CHAIN_STAMP(slot) \
   if (stamps && lane == 0) stamps[p * 8 + (slot)] = clock64()
-  for (int iter = 0; iter < g.n_iter; ++iter)
+#else
+#define CHAIN_STAMP(slot)
+#endif
   for (int p = 0; p < g.n_phases; ++p) {
     if (threadIdx.x == 0) CHAIN_STAMP(0);
     if (g.kind[p] == 0) {
@@ -1107,7 +1134,11 @@ gemm_chain_kernel(const __grid_constant__ ChainArgs ga) {
           tc_fence_after();
           if (warp == 2 && t == crank) CHAIN_STAMP(3);  // first accumulator complete
           epilogue_tile(g.ep[ct.gi], g.M[ct.gi], g.N[ct.gi], ct.m0, ct.n0, (uint32_t)ct.bn, tmem_base + acc * kChainMaxBN, q,
-                        lane, g.N[ct.gi] <= ct.bn, (stamps && warp == 2 && t == crank) ? stamps + 96 + p * 8 : nullptr);
+                        lane, g.N[ct.gi] <= ct.bn
+#ifdef P2PFL_BRINGUP
+                        , (stamps && warp == 2 && t == crank) ? stamps + 96 + p * 8 : nullptr
+#endif
+          );
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(smem_u32(&tmem_empty_bar[acc]));
@@ -1118,8 +1149,11 @@ gemm_chain_kernel(const __grid_constant__ ChainArgs ga) {
       it += my_kb;
     } else if (warp >= 2 && crank == 0) {
       const bool fits = (size_t)g.ce.B * (2 * g.ce.C + 6) * 4 <= (size_t)kChainStages * kChainStageBytes;
-      chain_ce(g.ce, warp - 2, lane, s_db, fits ? reinterpret_cast<float*>(smem) : nullptr, g.ce.B <= 128 && g.ce.C <= 64,
-               stamps ? stamps + 96 + p * 8 : nullptr);
+      chain_ce(g.ce, warp - 2, lane, s_db, fits ? reinterpret_cast<float*>(smem) : nullptr, g.ce.B <= 128 && g.ce.C <= 64
+#ifdef P2PFL_BRINGUP
+               , stamps ? stamps + 96 + p * 8 : nullptr
+#endif
+      );
     }
     // ---- link boundary: this link's global stores (generic proxy, possibly another CTA's) must
     // be visible to the next link's TMA loads (async proxy) and to its plain loads
@@ -1169,10 +1203,19 @@ extern "C" int p2pfl_gemm_chain_max_cluster(int device) {
   return 1;
 }
 
+#ifdef P2PFL_BRINGUP
 static long long* g_chain_stamps = nullptr;
+#endif
+// Per-link clock stamps exist only in builds with -DP2PFL_BRINGUP; the shipped library refuses.
 extern "C" int p2pfl_gemm_chain_set_stamps(void* device_buffer) {
+#ifdef P2PFL_BRINGUP
   g_chain_stamps = reinterpret_cast<long long*>(device_buffer);
   return 0;
+#else
+  if (device_buffer == nullptr) return 0;
+  set_error("clock stamps are compiled out of this build (rebuild with -DP2PFL_BRINGUP)");
+  return -1;
+#endif
 }
 
 extern "C" int p2pfl_gemm_chain(int device, void* stream, const p2pfl_gemm_args* gemms, int n_gemm,
@@ -1225,9 +1268,9 @@ extern "C" int p2pfl_gemm_chain_cluster(int device, void* stream, const p2pfl_ge
     has_ce |= phase_kind[p] == 1;
   }
   g.sc.n_phases = n_phases;
+#ifdef P2PFL_BRINGUP
   g.sc.stamps = g_chain_stamps;
-  static const int n_iter = [] { const char* e = getenv("P2PFL_CHAIN_ITER"); return e && atoi(e) > 0 ? atoi(e) : 1; }();
-  g.sc.n_iter = n_iter;
+#endif
   if (has_ce) {
     P2PFL_REQUIRE(ce && ce->logits && ce->labels && ce->B > 0 && ce->C > 0 && ce->C <= 256, "bad cross-entropy link");
     g.sc.ce = *ce;
@@ -1260,9 +1303,5 @@ extern "C" int p2pfl_gemm_chain_cluster(int device, void* stream, const p2pfl_ge
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
   P2PFL_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_chain_kernel, g));
-  // bring-up aid: P2PFL_CHAIN_REPEAT=n relaunches the same chain n more times back to back (timing
-  // a warm instruction cache against a cold one); never set outside experiments
-  static const int repeat = [] { const char* e = getenv("P2PFL_CHAIN_REPEAT"); return e ? atoi(e) : 0; }();
-  for (int i = 0; i < repeat; ++i) P2PFL_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_chain_kernel, g));
   return 0;
 }

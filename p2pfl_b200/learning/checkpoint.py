@@ -25,9 +25,6 @@ def learner_state(learner: Any) -> Dict[str, Any]:
         t = getattr(learner, name, None)
         if t is not None:
             st[name] = t.detach().cpu().clone()
-    opt = getattr(learner, "_optimizer", None)
-    if opt is not None:
-        st["torch_optimizer"] = opt.state_dict()
     return st
 
 
@@ -47,10 +44,14 @@ def save_checkpoint(node: Any, path: str) -> None:
 
 
 def load_checkpoint(node: Any, path: str) -> Dict[str, Any]:
-    """Restore the model weights into ``node.model`` (and into the live learner, if any)."""
+    """Restore the model weights into ``node.model`` and, when the node has a live fused learner,
+    its Adam moments and step count as well.  Eager learners build a fresh optimizer per round (as
+    the reference does, Q16), so for them a checkpoint is weights only.  The file holds tensors,
+    strings and integers only and is read with ``weights_only=True`` (no code runs on load).  The
+    round counters are returned to the caller, which decides how many rounds are left to run."""
     from p2pfl_b200.learning.params import FlatParams, ParamLayout
 
-    ckpt = torch.load(path, map_location="cpu", weights_only=False)
+    ckpt = torch.load(path, map_location="cpu", weights_only=True)
     ls = ckpt["learner"]
     layout = ParamLayout.from_state_dict(node.model.state_dict())
     if layout.hash != ls["layout_hash"]:

@@ -30,6 +30,8 @@ from p2pfl_b200.learning.params import FlatParams, ParamLayout
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.settings import Settings
 
+_staging_lock = threading.Lock()
+
 torch.set_num_threads(max(1, min(4, torch.get_num_threads())))
 
 
@@ -121,13 +123,45 @@ class TorchLearner(NodeLearner):
         return params
 
     def encode_parameters(self, params: Any = None) -> bytes:
-        sd = self._as_state_dict(params)
+        """Host wire format (reference: lightning_learner.py:113-122).  A flat model on the device
+        crosses to the host as ONE copy into a pinned staging buffer, not one
+        ``.to("cpu")`` per tensor; the per-entry arrays are views of that buffer."""
         assert self.layout is not None
+        flat_src: Optional[torch.Tensor] = None
+        extra: Dict[str, torch.Tensor] = {}
+        if params is None and self.flat is not None:
+            flat_src, extra = self.flat.detach(), self._extra()
+        elif isinstance(params, FlatParams) and params.layout == self.layout:
+            flat_src, extra = params.flat.detach(), params.extra
+        if flat_src is not None and flat_src.is_cuda:
+            with _staging_lock:  # the gossiper and the learning thread may both encode
+                host = self._host_staging(flat_src.numel())
+                host.copy_(flat_src.to(torch.float32), non_blocking=True)
+                torch.cuda.current_stream(flat_src.device).synchronize()
+                views = self.layout.views(host)
+                arrays = []
+                for s in self.layout.slots:
+                    t = views[s.name] if s.in_arena else torch.as_tensor(extra[s.name]).detach().cpu()
+                    arrays.append(t.to(s.dtype).numpy())
+                return codec.encode_arrays(arrays)  # pickled (copied) before the staging buffer is reused
+        sd = self._as_state_dict(params)
         arrays = []
         for s in self.layout.slots:
             t = torch.as_tensor(sd[s.name]).detach()
             arrays.append(t.to("cpu", s.dtype).numpy())
         return codec.encode_arrays(arrays)
+
+    def _host_staging(self, numel: int) -> torch.Tensor:
+        """Pinned fp32 buffer reused by every device -> host encode of this learner."""
+        buf = getattr(self, "_staging", None)
+        if buf is None or buf.numel() != numel:
+            buf = torch.empty(numel, dtype=torch.float32)
+            try:
+                buf = buf.pin_memory()
+            except Exception:
+                pass
+            self._staging = buf
+        return buf
 
     def decode_parameters(self, data: Any) -> FlatParams:
         """bytes -> FlatParams on this learner's device.  Count, shapes and
