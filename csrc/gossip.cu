@@ -42,8 +42,10 @@ __device__ __forceinline__ uint4 ld_inbox_u4(const void* p) {
 }
 
 // ---------------------------------------------------------------------- push
+// `snap` (nullable): the tile is also copied there in fp32, so that the host can put the
+// pre-exchange model back if the exchange does not complete (the reduce overwrites `src`).
 __device__ __forceinline__ void push_tile_data(const float* __restrict__ src, uint64_t n, uint32_t tile,
-                                               const p2pfl_push_table& t, uint32_t ti) {
+                                               const p2pfl_push_table& t, uint32_t ti, float* __restrict__ snap = nullptr) {
   const uint64_t t0 = (uint64_t)ti * tile;
   const uint32_t len = (uint32_t)((n - t0) < tile ? (n - t0) : tile);
   if (t.wire_bf16) {
@@ -56,6 +58,10 @@ __device__ __forceinline__ void push_tile_data(const float* __restrict__ src, ui
         if (e < len) {
           const float4 a = *reinterpret_cast<const float4*>(src + t0 + e);
           const float4 b = *reinterpret_cast<const float4*>(src + t0 + e + 4);
+          if (snap) {
+            *reinterpret_cast<float4*>(snap + t0 + e) = a;
+            *reinterpret_cast<float4*>(snap + t0 + e + 4) = b;
+          }
           w[u].x = pack_bf16x2(a.x, a.y);
           w[u].y = pack_bf16x2(a.z, a.w);
           w[u].z = pack_bf16x2(b.x, b.y);
@@ -77,7 +83,10 @@ __device__ __forceinline__ void push_tile_data(const float* __restrict__ src, ui
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const uint32_t e = e0 + u * kThreads * 4;
-        if (e < len) w[u] = *reinterpret_cast<const uint4*>(src + t0 + e);
+        if (e < len) {
+          w[u] = *reinterpret_cast<const uint4*>(src + t0 + e);
+          if (snap) *reinterpret_cast<uint4*>(snap + t0 + e) = w[u];
+        }
       }
       for (int p = 0; p < t.n_peers; ++p) {
         float* dst = reinterpret_cast<float*>(t.inbox[p]) + t0;
@@ -134,7 +143,10 @@ __device__ __forceinline__ void reduce_tile(float* __restrict__ params, __nv_bfl
       __nanosleep(32);
     }
     s_arrived[threadIdx.x] = ok;
-    if (!ok && status) atomicExch(status, 1);
+    if (!ok && status) {
+      atomicExch(status, 1);
+      atomicOr(status + 2, 1 << threadIdx.x);  // which contributors (table positions) were missing somewhere
+    }
   }
   __syncthreads();
 
@@ -216,12 +228,12 @@ __device__ void reduce_phase(float* __restrict__ params, __nv_bfloat16* __restri
 __device__ void fused_phase(float* __restrict__ params, __nv_bfloat16* __restrict__ params_bf16, uint64_t n,
                             uint32_t tile, uint32_t seq, const p2pfl_push_table& push, const p2pfl_reduce_table& red,
                             const uint32_t* __restrict__ abort_flag, uint64_t timeout_cycles, int32_t* status, int cta,
-                            int n_cta) {
+                            int n_cta, float* __restrict__ snap = nullptr) {
   __shared__ int s_arrived[P2PFL_MAX_PEERS];
   const uint32_t n_tiles = (uint32_t)((n + tile - 1) / tile);
   const uint32_t mine = n_tiles > (uint32_t)cta ? (n_tiles - cta + n_cta - 1) / n_cta : 0;
   for (uint32_t k = 0; k < mine + kLag; ++k) {
-    if (k < mine) push_tile_data(params, n, tile, push, cta + k * n_cta);
+    if (k < mine) push_tile_data(params, n, tile, push, cta + k * n_cta, snap);
     if (k >= kLag)
       reduce_tile(params, params_bf16, n, tile, seq, red, abort_flag, timeout_cycles, status, cta + (k - kLag) * n_cta,
                   s_arrived);
@@ -259,7 +271,7 @@ __global__ void __launch_bounds__(kThreads, 2)
 gossip_fused_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ params_bf16, uint64_t n, uint32_t tile,
                     uint32_t seq, const __grid_constant__ p2pfl_push_table push,
                     const __grid_constant__ p2pfl_reduce_table red, const uint32_t* __restrict__ abort_flag,
-                    uint64_t timeout_cycles, int32_t* status) {
+                    uint64_t timeout_cycles, int32_t* status, float* __restrict__ snapshot) {
   __shared__ p2pfl_push_table s_push;
   __shared__ p2pfl_reduce_table s_red;
   if (threadIdx.x == 0) {
@@ -268,7 +280,35 @@ gossip_fused_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ para
   }
   __syncthreads();
   fused_phase(params, params_bf16, n, tile, seq, s_push, s_red, abort_flag, timeout_cycles, status, blockIdx.x,
-              gridDim.x);
+              gridDim.x, snapshot);
+}
+
+// Several federated nodes that share this GPU exchange in ONE cooperative launch
+// (blockIdx.y = local member): their tables may name inboxes on this GPU (the other
+// local members) and on peer GPUs alike.  Waits between local members are safe because
+// every CTA of a cooperative launch is resident; waits on peer GPUs are the ordinary
+// cross-device case.  (B200_PROFILING.md: kernels that wait on one another must never be
+// separate launches on one device.)
+struct GroupArgs {
+  const p2pfl_group_member* members;  // device array [n_members]
+  const p2pfl_push_table* push;       // device array [n_members]
+  const p2pfl_reduce_table* reduce;   // device array [n_members]
+};
+
+__global__ void __launch_bounds__(kThreads, 2)
+gossip_fused_group_kernel(GroupArgs a, uint64_t n, uint32_t tile, uint32_t seq, uint64_t timeout_cycles) {
+  const int r = blockIdx.y;
+  __shared__ p2pfl_push_table s_push;
+  __shared__ p2pfl_reduce_table s_red;
+  __shared__ p2pfl_group_member s_me;
+  if (threadIdx.x == 0) {
+    s_push = a.push[r];
+    s_red = a.reduce[r];
+    s_me = a.members[r];
+  }
+  __syncthreads();
+  fused_phase(s_me.params, reinterpret_cast<__nv_bfloat16*>(s_me.params_bf16), n, tile, seq, s_push, s_red,
+              s_me.abort_flag, timeout_cycles, s_me.status, blockIdx.x, gridDim.x, s_me.snapshot);
 }
 
 // Test harness: R logical ranks in ONE cooperative launch on one GPU
@@ -337,6 +377,13 @@ int p2pfl_gossip_reduce(int device, void* stream, float* params, void* params_bf
 int p2pfl_gossip_fused(int device, void* stream, float* params, void* params_bf16, uint64_t n, uint32_t tile,
                        uint32_t seq, const p2pfl_push_table* push, const p2pfl_reduce_table* reduce,
                        const uint32_t* abort_flag, uint64_t timeout_cycles, int32_t* status) {
+  return p2pfl_gossip_fused_snap(device, stream, params, params_bf16, n, tile, seq, push, reduce, abort_flag,
+                                 timeout_cycles, status, nullptr);
+}
+
+int p2pfl_gossip_fused_snap(int device, void* stream, float* params, void* params_bf16, uint64_t n, uint32_t tile,
+                            uint32_t seq, const p2pfl_push_table* push, const p2pfl_reduce_table* reduce,
+                            const uint32_t* abort_flag, uint64_t timeout_cycles, int32_t* status, float* snapshot) {
   if (int rc = check_common(n, tile)) return rc;
   P2PFL_REQUIRE(push && reduce, "null table");
   P2PFL_REQUIRE(push->n_peers <= P2PFL_MAX_PEERS && reduce->n_slots <= P2PFL_MAX_PEERS, "too many peers");
@@ -350,8 +397,34 @@ int p2pfl_gossip_fused(int device, void* stream, float* params, void* params_bf1
   uint64_t cap = (uint64_t)sm_count(device) * per_sm;
   int grid = (int)(tiles < cap ? tiles : cap);
   gossip_fused_kernel<<<grid, kThreads, 0, as_stream(stream)>>>(params, (__nv_bfloat16*)params_bf16, n, tile, seq,
-                                                               *push, *reduce, abort_flag, timeout_cycles, status);
+                                                               *push, *reduce, abort_flag, timeout_cycles, status,
+                                                               snapshot);
   P2PFL_LAUNCH_OK();
+  return 0;
+}
+
+int p2pfl_gossip_fused_group(int device, void* stream, int n_members, const p2pfl_group_member* members_dev,
+                             uint64_t n, uint32_t tile, uint32_t seq, const p2pfl_push_table* push_tables_dev,
+                             const p2pfl_reduce_table* reduce_tables_dev, uint64_t timeout_cycles) {
+  if (int rc = check_common(n, tile)) return rc;
+  P2PFL_REQUIRE(n_members >= 1 && n_members <= P2PFL_MAX_PEERS, "a group exchange takes 1..16 local members");
+  P2PFL_REQUIRE(members_dev && push_tables_dev && reduce_tables_dev, "null table");
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  GroupArgs a;
+  a.members = members_dev;
+  a.push = push_tables_dev;
+  a.reduce = reduce_tables_dev;
+  int per_sm = 0;
+  P2PFL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gossip_fused_group_kernel, kThreads, 0));
+  if (per_sm > 2) per_sm = 2;
+  const int capacity = per_sm * sm_count(device);
+  int gx = capacity / n_members;
+  const uint64_t tiles = (n + tile - 1) / tile;
+  if ((uint64_t)gx > tiles) gx = (int)tiles;
+  P2PFL_REQUIRE(gx >= 1, "not enough resident CTAs for the group exchange");
+  dim3 grid(gx, n_members, 1), block(kThreads, 1, 1);
+  void* args[] = {&a, &n, &tile, &seq, &timeout_cycles};
+  P2PFL_CUDA_OK(cudaLaunchCooperativeKernel((void*)gossip_fused_group_kernel, grid, block, args, 0, as_stream(stream)));
   return 0;
 }
 

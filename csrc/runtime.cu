@@ -113,6 +113,12 @@ int p2pfl_rt_memset32(int device, void* stream, void* ptr, uint32_t value, uint6
   return -1;
 }
 
+int p2pfl_rt_sm_clock_khz(int device, int* out_khz) {
+  P2PFL_REQUIRE(out_khz != nullptr, "null argument");
+  P2PFL_CUDA_OK(cudaDeviceGetAttribute(out_khz, cudaDevAttrClockRate, device));
+  return 0;
+}
+
 int p2pfl_rt_device_info(int device, int* sms, int* cc_major, int* cc_minor, uint64_t* total_mem) {
   cudaDeviceProp prop;
   P2PFL_CUDA_OK(cudaGetDeviceProperties(&prop, device));

@@ -36,6 +36,8 @@ int p2pfl_rt_ipc_close(int device, void* ptr);
 int p2pfl_rt_enable_peer(int device, int peer_device);
 int p2pfl_rt_can_access_peer(int device, int peer_device, int* out_yes);
 int p2pfl_rt_memset32(int device, void* stream, void* ptr, uint32_t value, uint64_t count);
+/* peak SM clock in kHz (converts the device-side timeouts, which count SM cycles, from seconds) */
+int p2pfl_rt_sm_clock_khz(int device, int* out_khz);
 int p2pfl_rt_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, uint64_t* total_mem);
 
 /* One 2-D matrix inside the flat arena and where its bf16 transpose goes. */
@@ -121,7 +123,8 @@ typedef struct {
 } p2pfl_reduce_table;
 
 /* status words written by the reduce kernels (device memory, int32[4]):
- * [0] = 1 if aborted/timeout, [1] = number of tiles finalised, [2],[3] reserved */
+ * [0] = 1 if aborted/timeout, [1] = number of tiles finalised, [2] = bit j set when the
+ * contributor at reduce-table position j was missing from at least one tile, [3] reserved */
 
 /* G1/G3: push `src` (fp32, n elements) into every peer's inbox slot. */
 int p2pfl_gossip_push(int device, void* stream, const float* src, uint64_t n, uint32_t tile,
@@ -139,6 +142,29 @@ int p2pfl_gossip_fused(int device, void* stream, float* params, void* params_bf1
                        uint64_t n, uint32_t tile, uint32_t seq, const p2pfl_push_table* push,
                        const p2pfl_reduce_table* reduce, const uint32_t* abort_flag,
                        uint64_t timeout_cycles, int32_t* status);
+/* Same, and every tile of the pre-exchange model is also copied to `snapshot` (fp32[n],
+ * nullable) before the reduce overwrites it: a host that finds status[0] != 0 afterwards
+ * can put the model back and exchange some other way instead of keeping a partly averaged one. */
+int p2pfl_gossip_fused_snap(int device, void* stream, float* params, void* params_bf16 /* nullable */,
+                            uint64_t n, uint32_t tile, uint32_t seq, const p2pfl_push_table* push,
+                            const p2pfl_reduce_table* reduce, const uint32_t* abort_flag,
+                            uint64_t timeout_cycles, int32_t* status, float* snapshot /* nullable */);
+/* The exchange of SEVERAL federated nodes that live on one GPU (BASELINE config 4: simulated
+ * nodes packed on a device) as ONE cooperative launch: member m runs the fused push+reduce
+ * schedule with push_tables_dev[m] / reduce_tables_dev[m]; a table may name inboxes of the
+ * other local members and of nodes on peer GPUs alike.  All three arrays are DEVICE memory.
+ * (train_stage.py:115-177 for every co-located trainer at once.) */
+typedef struct {
+  float* params;              /* fp32[n] live model of the member, overwritten with the average */
+  void* params_bf16;          /* nullable bf16 working copy, refreshed */
+  float* snapshot;            /* nullable, see p2pfl_gossip_fused_snap */
+  const uint32_t* abort_flag; /* nullable */
+  int32_t* status;            /* int32[4] of the member */
+} p2pfl_group_member;
+int p2pfl_gossip_fused_group(int device, void* stream, int n_members,
+                             const p2pfl_group_member* members_dev, uint64_t n, uint32_t tile,
+                             uint32_t seq, const p2pfl_push_table* push_tables_dev,
+                             const p2pfl_reduce_table* reduce_tables_dev, uint64_t timeout_cycles);
 /* Single-GPU emulation of R ranks exchanging through one cooperative launch
  * (test harness for machines with fewer GPUs than ranks). */
 int p2pfl_gossip_fused_emulated(int device, void* stream, int n_ranks, float* const* params,

@@ -60,7 +60,7 @@ class InitModelCommand(Command):
             logger.debug(st.addr, f"init_model for round {round} ignored (mine: {st.round})")
             return
         try:
-            learner.set_parameters(learner.decode_parameters(weights))
+            learner.set_parameters(_decode_from(learner, weights, source))
         except (DecodingParamsError, ModelNotMatchingError) as e:
             logger.error(st.addr, f"initial model unusable ({e!r}); stopping node")
             self._stop()
@@ -73,6 +73,18 @@ class InitModelCommand(Command):
         st.notify()
         logger.info(st.addr, f"initial model received from {source}")
         self._protocol.broadcast(self._protocol.build_msg("model_initialized"))
+
+
+def _decode_from(learner: Any, weights: Any, source: str) -> Any:
+    """Decode a model payload; a device reference may only name the arena of the node that sent it
+    (model messages are never relayed, so any other owner is a forged or confused reference)."""
+    from p2pfl_b200.parallel.payload import DeviceRef
+
+    if DeviceRef.is_ref(weights):
+        owner = DeviceRef.from_bytes(weights).addr
+        if owner != source:
+            raise DecodingParamsError(f"device reference of {owner} arrived in a message from {source}")
+    return learner.decode_parameters(weights)
 
 
 class AddModelCommand(Command):
@@ -110,14 +122,24 @@ class AddModelCommand(Command):
             return
         with st.stash_lock:
             if not self._aggregator.get_train_set():
-                # vote still running here: keep the payload, Train/Wait stage replays it
+                # vote still running here: keep the payload, Train/Wait stage replays it.  A device
+                # reference is resolved NOW: the sender only keeps the memory it names stable until
+                # this call returns, and may be training on it again by the time of the replay.
+                from p2pfl_b200.parallel.payload import DeviceRef
+
+                if DeviceRef.is_ref(weights):
+                    try:
+                        weights = _decode_from(learner, weights, source)
+                    except Exception as e:
+                        logger.error(st.addr, f"early model from {source} could not be fetched ({e!r}); dropped")
+                        return
                 st.pending_models.append(
                     (round, lambda: self.execute(source, round, weights=weights, contributors=contributors, weight=weight))
                 )
                 logger.debug(st.addr, f"add_model from {source} stashed: train set not armed yet")
                 return
         try:
-            model = learner.decode_parameters(weights)
+            model = _decode_from(learner, weights, source)
             learner.check_parameters(model)
             held = self._aggregator.add_model(model, list(contributors), int(weight))
         except (DecodingParamsError, ModelNotMatchingError) as e:

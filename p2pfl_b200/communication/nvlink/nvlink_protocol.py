@@ -57,7 +57,9 @@ _local_lock = threading.Lock()
 
 
 class ArenaInfoCommand(Command):
-    """``arena_info [geo_key, layout_hash, device, pid, host, ipc_hex, n_samples]``."""
+    """``arena_info [geo_key, layout_hash, device, pid, host, ipc_hex, n_samples, fused]``.
+    A node without a device arena announces too (geometry ``0:0:0:0``), so that its peers know
+    rather than wait."""
 
     def __init__(self, proto: "NvlinkCommunicationProtocol") -> None:
         self._proto = proto
@@ -79,7 +81,13 @@ class PeerInfo:
         self.host = args[4]
         self.ipc = bytes.fromhex(args[5])
         self.n_samples = int(args[6])
+        # willing and able to take part in fused exchanges (has an arena, Settings.FUSED_EXCHANGE)
+        self.fused = bool(int(args[7])) if len(args) > 7 else self.geo.n > 0
         self.mapped: Optional[PeerArena] = None
+
+    @property
+    def has_arena(self) -> bool:
+        return self.geo.n > 0
 
 
 class NvlinkCommunicationProtocol(BaseProtocol):
@@ -96,7 +104,10 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         self._peers_lock = threading.Lock()
         self._nonce = 0
         self._no_arena: set = set()
+        self._my_peerinfo: Optional[PeerInfo] = None
+        self._cancelled_round = -1  # highest round whose fused exchange somebody called off
         self.add_command(ArenaInfoCommand(self))
+        self.add_command(FusedCancelCommand(self))
         # counts, bytes and DEVICE time (CUDA events on the stream that did the work) per path
         self.stats = {"fused": 0, "pulled": 0, "host": 0, "fused_bytes": 0, "pulled_bytes": 0, "fused_ms": 0.0, "pulled_ms": 0.0}
 
@@ -124,18 +135,24 @@ class NvlinkCommunicationProtocol(BaseProtocol):
     def publish_arena(self, learner: Any) -> None:
         """Announce this node's arena to everybody (called when the learner is built)."""
         arena = getattr(learner, "arena", None)
+        self._cancelled_round = -1  # a new experiment starts
+        layout_hash = getattr(getattr(learner, "layout", None), "hash", "")
+        n_samples = str(learner.get_num_samples()[0])
         if arena is None:
-            return
-        with _local_lock:
-            _local_arenas[self.addr] = arena
-        learner.plane = self
-        try:
-            ipc = arena.ipc_handle().hex()
-        except Exception as e:  # IPC export can be refused in restricted containers
-            logger.debug(self.addr, f"arena IPC export failed: {e}")
-            ipc = ""
-        args = [arena.geo.key(), learner.layout.hash, str(arena.device), str(_PID), _HOST, ipc, str(learner.get_num_samples()[0])]
+            args = ["0:0:0:0", layout_hash, "-1", str(_PID), _HOST, "", n_samples, "0"]
+        else:
+            with _local_lock:
+                _local_arenas[self.addr] = arena
+            learner.plane = self
+            try:
+                ipc = arena.ipc_handle().hex()
+            except Exception as e:  # IPC export can be refused in restricted containers
+                logger.debug(self.addr, f"arena IPC export failed: {e}")
+                ipc = ""
+            args = [arena.geo.key(), layout_hash, str(arena.device), str(_PID), _HOST, ipc, n_samples,
+                    str(int(bool(Settings.FUSED_EXCHANGE)))]  # fmt: skip
         self._my_info = args
+        self._my_peerinfo = PeerInfo(args)
         self.broadcast(self.build_msg("arena_info", args))
 
     def _on_arena_info(self, source: str, args: List[str]) -> None:
@@ -143,7 +160,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         with self._peers_lock:
             old = self._peers.get(source)
             if old is not None and old.ipc == info.ipc and old.pid == info.pid and old.geo == info.geo:
-                old.n_samples, old.layout_hash = info.n_samples, info.layout_hash
+                old.n_samples, old.layout_hash, old.fused = info.n_samples, info.layout_hash, info.fused
                 return  # same arena as before (pooled): keep the mapping
             self._peers[source] = info
             self._no_arena.discard(source)
@@ -160,7 +177,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
             return None
         with self._peers_lock:
             info = self._peers.get(addr)
-            if info is None or info.host != _HOST:
+            if info is None or info.host != _HOST or not info.has_arena:
                 return None
             if info.mapped is not None:
                 return info.mapped
@@ -200,9 +217,10 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         arena = getattr(learner, "arena", None)
         with self._peers_lock:
             info = self._peers.get(nei)
-        if info is None and arena is not None and nei not in self._no_arena and self._node is not None:
-            # the peer may still be building its learner: its announcement is milliseconds away
-            self._node.state.wait_for(lambda: nei in self._peers, 0.5)
+        if info is None and arena is not None and nei not in self._no_arena and self._node is not None and nei in self._extended:
+            # one of ours that has not announced yet is still building its learner (every extended
+            # node announces, arena or not): its announcement is milliseconds away
+            self._node.state.wait_for(lambda: nei in self._peers, Settings.ARENA_INFO_WAIT)
             with self._peers_lock:
                 info = self._peers.get(nei)
             if info is None:
@@ -210,6 +228,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         reachable = (
             arena is not None
             and info is not None
+            and info.has_arena
             and info.host == _HOST
             and info.layout_hash == learner.layout.hash
             and (info.pid == _PID or bool(getattr(self, "_my_info", ["", "", "", "", "", ""])[5]))
@@ -235,10 +254,10 @@ class NvlinkCommunicationProtocol(BaseProtocol):
     # A ``DeviceRef`` travels through the ordinary command path untouched; the device
     # learner resolves it in ``decode_parameters`` by calling :meth:`pull`.  That way a
     # reference that arrives before the learner exists is stashed like any other payload.
-    def pull(self, ref: DeviceRef) -> Any:
-        return self._pull(ref)
+    def pull(self, ref: DeviceRef, source: Optional[str] = None) -> Any:
+        return self._pull(ref, source)
 
-    def _pull(self, ref: DeviceRef) -> Any:
+    def _pull(self, ref: DeviceRef, source: Optional[str] = None) -> Any:
         """Read the sender's tensor over NVLink into a private bf16/fp32 buffer."""
         learner = self._learner()
         if learner is None or getattr(learner, "arena", None) is None:
@@ -247,9 +266,19 @@ class NvlinkCommunicationProtocol(BaseProtocol):
             from p2pfl_b200.exceptions import ModelNotMatchingError
 
             raise ModelNotMatchingError("layout hash differs from the local model")
+        from p2pfl_b200.exceptions import DecodingParamsError
+
+        # the reference arrived in an unauthenticated message: nothing in it sizes a read of peer
+        # memory before it has been checked against what is known about that peer
+        if ref.region not in ("params", "outbox"):
+            raise DecodingParamsError(f"device reference names an unknown region {ref.region!r}")
+        if source is not None and ref.addr != source:
+            raise DecodingParamsError(f"device reference of {ref.addr} arrived in a message from {source}")
         peer = self._map_peer(ref.addr)
         if peer is None:
             raise RuntimeError(f"arena of {ref.addr} is not mapped")
+        if int(ref.n) != learner.layout.total or int(ref.n) != peer.geo.n:
+            raise DecodingParamsError(f"device reference has {ref.n} elements, the layout has {learner.layout.total}")
         dev = learner.arena.device
         src = tensor_from_ptr(peer.region_ptr(ref.region), ref.n, torch.float32, dev)
         # pulled models stay fp32 (exact): this path carries initial weights, diffusion and
@@ -270,55 +299,172 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         return FlatParams(out, learner.layout, extra)
 
     # ------------------------------------------------------------ fused exchange
-    def plan_fused_exchange(self, state: Any, learner: Any, wait: float = 2.0) -> Optional["FusedExchange"]:
-        """A plan when every train-set member's arena is mapped, else None."""
-        if not Settings.FUSED_EXCHANGE:
-            return None
+    def cancel_fused(self, rnd: int) -> None:
+        """Tell the round's trainers that this node will NOT take part in (or could not finish) the
+        fused exchange of round ``rnd``: whoever has not launched yet skips it, whoever is spinning
+        in it aborts, and everybody exchanges through the ordinary add_model path instead."""
+        self._note_cancel(rnd)
+        try:
+            self.broadcast_async(self.build_msg("fused_cancel", [], round=rnd))
+        except Exception as e:
+            logger.debug(self.addr, f"fused_cancel not sent: {e}")
+
+    def _note_cancel(self, rnd: int) -> None:
+        if rnd > self._cancelled_round:
+            self._cancelled_round = rnd
+        if self._node is not None:
+            st = self._node.state
+            if st.fused_complete_round == rnd:
+                # a trainer could not finish the exchange this node completed: it will need the
+                # aggregate through the ordinary diffusion after all
+                st.fused_complete_round = None
+            st.notify()
+
+    def fused_cancelled(self, rnd: int) -> bool:
+        return self._cancelled_round >= rnd
+
+    def plan_fused_exchange(self, state: Any, learner: Any, wait: Optional[float] = None) -> Optional["FusedExchange"]:
+        """A plan for this round's train set, or None (exchange through add_model messages).
+
+        The answer must be the same on every trainer, or one of them would spin on flags nobody
+        writes.  It is therefore a function of what every node eventually knows alike - the train
+        set and the ``arena_info`` each member announced (geometry, layout, host, process, GPU,
+        whether it is willing) - and a member whose announcement has not arrived yet is WAITED for
+        (every extended node announces, with or without an arena) rather than guessed.  What can
+        still differ between trainers is local: an IPC mapping that fails here.  That trainer then
+        says so (``fused_cancel``) and the others fall back with it."""
+        rnd = state.round
         arena = getattr(learner, "arena", None)
         train_set = sorted(state.train_set)
-        if arena is None or state.addr not in train_set or len(train_set) < 2:
+        if arena is None or rnd is None or state.addr not in train_set or len(train_set) < 2:
             return None
         others = [n for n in train_set if n != state.addr]
+        if self.fused_cancelled(rnd):
+            return None
+        deadline = time.time() + (Settings.FUSED_INFO_WAIT if wait is None else wait)
+
+        def settled() -> bool:
+            if self.fused_cancelled(rnd) or state.round is None:
+                return True
+            known = self.get_neighbors(only_direct=False)
+            with self._peers_lock:
+                # a member that left the network, or that is not one of ours (a reference node
+                # never announces), settles the question as well: no fused exchange
+                return all(n in self._peers or n not in known or (n in known and self._is_plain(n)) for n in others)
+
+        state.wait_for(settled, max(0.0, deadline - time.time()))
+        if self.fused_cancelled(rnd) or state.round is None:
+            return None
+        with self._peers_lock:
+            infos = {n: self._peers.get(n) for n in others}
+        mine = self._my_peerinfo
+        if mine is None or not mine.fused:
+            return None
+        for n in others:
+            info = infos[n]
+            if info is None or not info.fused or info.host != _HOST:
+                return None
+            if info.layout_hash != learner.layout.hash or info.geo != arena.geo:
+                return None
+            if info.device == arena.device and info.pid != _PID:
+                # kernels that wait on one another must not be separate launches on one GPU
+                # (B200_PROFILING.md): co-located trainers are grouped into ONE cooperative launch,
+                # which only a single process can do
+                return None
         if len(train_set) > arena.geo.slots or len(others) > ops.MAX_PEERS:
             return None
-        deadline = time.time() + wait
-
-        def known() -> bool:
-            with self._peers_lock:
-                return all(n in self._peers for n in others)
-
-        state.wait_for(known, max(0.0, deadline - time.time()))
+        # ---- from here on a failure is local to this node: tell the others
         peers: Dict[str, PeerArena] = {}
         samples: Dict[str, int] = {state.addr: learner.get_num_samples()[0]}
         for n in others:
-            with self._peers_lock:
-                info = self._peers.get(n)
-            if info is None or info.layout_hash != learner.layout.hash or info.geo != arena.geo:
-                return None
-            if info.device == arena.device:
-                # co-located on my GPU: kernels that wait on one another must not share a device
-                # (B200_PROFILING.md); such train sets use the pull path
-                return None
             p = self._map_peer(n)
             if p is None:
+                logger.warning(self.addr, f"fused exchange of round {rnd} cancelled: cannot map the arena of {n}")
+                self.cancel_fused(rnd)
                 return None
             peers[n] = p
-            samples[n] = info.n_samples
-        return FusedExchange(self, state, learner, train_set, peers, samples)
+            samples[n] = infos[n].n_samples
+        local = [state.addr] + [n for n in others if infos[n].pid == _PID and infos[n].device == arena.device]
+        return FusedExchange(self, state, learner, train_set, peers, samples, sorted(local))
+
+    def _is_plain(self, addr: str) -> bool:
+        """Known neighbour that does not speak this framework's extra commands."""
+        return addr not in self._extended and addr in self._neighbors.get_all(only_direct=True)
+
+
+class FusedCancelCommand(Command):
+    """``fused_cancel`` (round in the message's round field): see ``cancel_fused``."""
+
+    def __init__(self, proto: "NvlinkCommunicationProtocol") -> None:
+        self._proto = proto
+
+    @staticmethod
+    def get_name() -> str:
+        return "fused_cancel"
+
+    def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
+        self._proto._note_cancel(int(round))
+
+
+class _DeviceGroup:
+    """Rendezvous of the trainers of ONE process that share a GPU in one round: the last to
+    arrive launches the single cooperative kernel that runs all their exchanges."""
+
+    def __init__(self, expected: List[str]) -> None:
+        self.expected = list(expected)
+        self.members: Dict[str, Dict[str, Any]] = {}
+        self.cond = threading.Condition()
+        self.done: Optional[torch.cuda.Event] = None
+        self.began: Optional[torch.cuda.Event] = None
+        self.failed: Optional[str] = None
+        self.keep: List[Any] = []  # device tables must outlive the launch
+        self.left = 0
+
+
+_groups: Dict[Tuple[int, int], _DeviceGroup] = {}
+_groups_lock = threading.Lock()
+_group_streams: Dict[int, torch.cuda.Stream] = {}
+
+
+def _group_for(device: int, seq: int, expected: List[str]) -> _DeviceGroup:
+    with _groups_lock:
+        g = _groups.get((device, seq))
+        if g is None:
+            g = _groups[(device, seq)] = _DeviceGroup(expected)
+        return g
+
+
+def _group_leave(device: int, seq: int, grp: _DeviceGroup) -> None:
+    """A member is done with the group; the last one out removes it from the registry (sequence
+    numbers may repeat from one experiment to the next: a finished group must never be found again)."""
+    with _groups_lock:
+        grp.left += 1
+        if grp.left >= len(grp.members) and _groups.get((device, seq)) is grp:
+            del _groups[(device, seq)]
+
+
+def _group_stream(device: torch.device) -> torch.cuda.Stream:
+    idx = device.index or 0
+    with _groups_lock:
+        s = _group_streams.get(idx)
+        if s is None:
+            s = _group_streams[idx] = torch.cuda.Stream(device=device)
+        return s
 
 
 class FusedExchange:
-    """One all-to-all push + FedAvg among the train set as a single kernel per node."""
+    """One all-to-all push + FedAvg among the train set: a single kernel per node, or - when
+    several trainers of this process share the GPU - a single cooperative kernel for all of them."""
 
     def __init__(self, proto: NvlinkCommunicationProtocol, state: Any, learner: Any, train_set: List[str],
-                 peers: Dict[str, PeerArena], samples: Dict[str, int]) -> None:  # fmt: skip
+                 peers: Dict[str, PeerArena], samples: Dict[str, int], local: Optional[List[str]] = None) -> None:  # fmt: skip
         self.proto, self.state, self.learner = proto, state, learner
         self.train_set, self.peers, self.samples = train_set, peers, samples
+        self.local = local or [state.addr]
         self.complete = False
 
-    def run(self, seq: int) -> Tuple[List[str], int]:
-        """Launch, wait, and return (contributors included, total weight)."""
-        learner, arena = self.learner, self.learner.arena
+    def _tables(self, seq: int) -> Tuple[Any, Any]:
+        arena = self.learner.arena
         me = self.state.addr
         my_slot = self.train_set.index(me)
         bank = seq & 1
@@ -339,35 +485,128 @@ class FusedExchange:
             wire_bf16,
             True,
         )
-        clock_hz = 1.9e9
-        timeout_cycles = int(Settings.AGGREGATION_TIMEOUT * clock_hz)
+        return push, red
+
+    def run(self, seq: int) -> Optional[Tuple[List[str], int]]:
+        """Launch, wait, and return (contributors, total weight) - or None when the exchange did
+        not complete: the pre-exchange model is back in place then and the caller exchanges through
+        add_model messages (a partly averaged model is never labelled as the round's aggregate)."""
+        learner, arena, proto = self.learner, self.learner.arena, self.proto
+        me, rnd = self.state.addr, self.state.round
+        others = [n for n in self.train_set if n != me]
+        total = float(sum(self.samples[n] for n in self.train_set))
+        wire_bf16 = arena.geo.wire_bf16
+        push, red = self._tables(seq)
+        timeout_cycles = int(Settings.AGGREGATION_TIMEOUT * ops.rt_sm_clock_hz(arena.device))
+        snap = learner.exchange_snapshot()
         began = torch.cuda.Event(enable_timing=True)
-        with torch.cuda.stream(learner.stream):
-            arena.status.zero_()
-            arena.abort.zero_()
-            began.record(learner.stream)
-            ops.gossip_fused(arena.params, learner.w16, arena.geo.tile, seq, push, red, arena.abort, timeout_cycles, arena.status)
-            done = torch.cuda.Event(enable_timing=True)
-            done.record(learner.stream)
-        # host watchdog: flip the abort word if a contributor disappears or the experiment stops
+        done = torch.cuda.Event(enable_timing=True)
+        grp: Optional[_DeviceGroup] = None
+        if len(self.local) == 1:
+            with torch.cuda.stream(learner.stream):
+                arena.status.zero_()
+                arena.abort.zero_()
+                began.record(learner.stream)
+                ops.gossip_fused(arena.params, learner.w16, arena.geo.tile, seq, push, red, arena.abort, timeout_cycles,
+                                 arena.status, snapshot=snap)  # fmt: skip
+                done.record(learner.stream)
+        else:
+            grp = self._join_group(seq, push, red, snap, timeout_cycles)
+            if grp is None:
+                return None
+            began, done = grp.began, grp.done
+            learner.stream.wait_event(done)
+        try:
+            return self._finish(seq, began, done, snap, others, total)
+        finally:
+            if grp is not None:
+                _group_leave(arena.device, seq, grp)
+
+    def _finish(self, seq: int, began: Any, done: Any, snap: Any, others: List[str], total: float) -> Optional[Tuple[List[str], int]]:
+        learner, arena, proto = self.learner, self.learner.arena, self.proto
+        me, rnd = self.state.addr, self.state.round
+        wire_bf16 = arena.geo.wire_bf16
+        # host watchdog: flip the abort word if a contributor disappears, somebody cancels or the experiment stops
         t0 = time.time()
         while not done.query():
-            gone = [n for n in others if n not in self.proto.get_neighbors(only_direct=False)]
-            if gone or self.state.round is None or time.time() - t0 > Settings.AGGREGATION_TIMEOUT:
-                with torch.cuda.stream(self.proto._abort_stream(learner)):
+            gone = [n for n in others if n not in proto.get_neighbors(only_direct=False)]
+            if gone or self.state.round is None or proto.fused_cancelled(rnd) or time.time() - t0 > Settings.AGGREGATION_TIMEOUT:
+                with torch.cuda.stream(proto._abort_stream(learner)):
                     arena.abort.fill_(1)
                 done.synchronize()
                 break
             time.sleep(0.0002)
         status = arena.status.cpu()
-        learner._params_written_by_plane()
-        self.proto.stats["fused"] += 1
-        self.proto.stats["fused_ms"] += began.elapsed_time(done)  # includes the wait for the slowest peer's tiles
-        self.proto.stats["fused_bytes"] += arena.n * (2 if wire_bf16 else 4) * len(others)
         self.complete = int(status[0]) == 0
+        proto.stats["fused_ms"] += began.elapsed_time(done)  # includes the wait for the slowest peer's tiles
         if not self.complete:
-            logger.warning(me, "fused exchange finished with missing contributors (timeout/abort)")
+            missing = [n for j, n in enumerate(others) if int(status[2]) >> j & 1]
+            logger.warning(me, f"fused exchange of round {rnd} incomplete (missing {missing}); restoring the local model")
+            with torch.cuda.stream(learner.stream):
+                if snap is not None:
+                    arena.params.copy_(snap)
+                learner._params_written()
+            learner.stream.synchronize()
+            proto.stats["fused_incomplete"] = proto.stats.get("fused_incomplete", 0) + 1
+            proto.cancel_fused(rnd)
+            return None
+        learner._params_written_by_plane()
+        proto.stats["fused"] += 1
+        proto.stats["fused_bytes"] += arena.n * (2 if wire_bf16 else 4) * len(others)
         return list(self.train_set), int(total)
+
+    def _join_group(self, seq: int, push: Any, red: Any, snap: Any, timeout_cycles: int) -> Optional[_DeviceGroup]:
+        learner, arena, proto = self.learner, self.learner.arena, self.proto
+        me, rnd = self.state.addr, self.state.round
+        ready = torch.cuda.Event()
+        ready.record(learner.stream)
+        grp = _group_for(arena.device, seq, self.local)
+        member = ops.make_group_member(arena.params, learner.w16, snap, arena.abort, arena.status)
+        with grp.cond:
+            grp.members[me] = {"push": push, "red": red, "member": member, "ready": ready, "arena": arena}
+            if grp.failed is None and len(grp.members) == len(grp.expected) and grp.done is None:
+                try:
+                    self._launch_group(grp, seq, timeout_cycles)
+                except Exception as e:  # a launch failure must not leave the others waiting
+                    grp.failed = f"{type(e).__name__}: {e}"
+                grp.cond.notify_all()
+            else:
+                # the other local trainers are still training; a cancellation ends the wait
+                deadline = time.time() + Settings.AGGREGATION_TIMEOUT
+                while grp.done is None and grp.failed is None:
+                    if proto.fused_cancelled(rnd) or self.state.round is None or time.time() > deadline:
+                        grp.failed = grp.failed or "cancelled before every local trainer had joined"
+                        grp.cond.notify_all()
+                        break
+                    grp.cond.wait(0.005)
+        if grp.failed is not None:
+            logger.warning(me, f"group exchange of round {rnd} not launched: {grp.failed}")
+            proto.cancel_fused(rnd)
+            _group_leave(arena.device, seq, grp)
+            return None
+        return grp
+
+    def _launch_group(self, grp: _DeviceGroup, seq: int, timeout_cycles: int) -> None:
+        """Called by the last local trainer to arrive, with the group's lock held."""
+        arena = self.learner.arena
+        order = [a for a in grp.expected if a in grp.members]
+        gs = _group_stream(self.learner.device)
+        with torch.cuda.stream(gs):
+            for a in order:
+                gs.wait_event(grp.members[a]["ready"])
+                grp.members[a]["arena"].status.zero_()
+                grp.members[a]["arena"].abort.zero_()
+            dev = self.learner.device
+            members_dev = ops.tables_to_device([grp.members[a]["member"] for a in order], dev)
+            push_dev = ops.tables_to_device([grp.members[a]["push"] for a in order], dev)
+            red_dev = ops.tables_to_device([grp.members[a]["red"] for a in order], dev)
+            grp.keep = [members_dev, push_dev, red_dev]
+            began = torch.cuda.Event(enable_timing=True)
+            began.record(gs)
+            ops.gossip_fused_group(arena.device, arena.n, arena.geo.tile, seq, members_dev, push_dev, red_dev, len(order), timeout_cycles)
+            done = torch.cuda.Event(enable_timing=True)
+            done.record(gs)
+        grp.began, grp.done = began, done
 
 
 def _abort_stream(self: NvlinkCommunicationProtocol, learner: Any) -> torch.cuda.Stream:

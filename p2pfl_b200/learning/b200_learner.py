@@ -192,6 +192,16 @@ class B200Learner(TorchLearner):
                 else:
                     ops.transpose_cast(self.flat, self.wT16, self._tdescs)
 
+    def exchange_snapshot(self) -> Optional[torch.Tensor]:
+        """fp32 buffer the fused exchange copies the pre-exchange model into (tile by tile, as it
+        pushes), so that an exchange that does not complete can be undone."""
+        if not Settings.FUSED_SNAPSHOT:
+            return None
+        snap = getattr(self, "_snapshot", None)
+        if snap is None or snap.numel() != self.flat.numel():
+            snap = self._snapshot = torch.empty_like(self.flat)
+        return snap
+
     def _s(self) -> torch.cuda.Stream:
         return getattr(self, "stream", None) or torch.cuda.current_stream(self.device)
 

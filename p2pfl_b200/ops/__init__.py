@@ -558,11 +558,45 @@ def gossip_reduce(params, params_bf16, tile: int, seq: int, table: ReduceTable, 
     _count()
 
 
-def gossip_fused(params, params_bf16, tile: int, seq: int, push: PushTable, reduce: ReduceTable, abort_flag=None, timeout_cycles: int = 0, status=None) -> None:
+def gossip_fused(params, params_bf16, tile: int, seq: int, push: PushTable, reduce: ReduceTable, abort_flag=None,
+                 timeout_cycles: int = 0, status=None, snapshot=None) -> None:  # fmt: skip
+    """``snapshot`` (fp32, same length as ``params``): receives the pre-exchange model tile by tile."""
     _check(
-        lib().p2pfl_gossip_fused(
+        lib().p2pfl_gossip_fused_snap(
             _dev(params), _stream(), _p(params), _p(params_bf16), C.c_uint64(params.numel()), C.c_uint32(tile), C.c_uint32(seq),
-            C.byref(push), C.byref(reduce), _p(abort_flag), C.c_uint64(timeout_cycles), _p(status),
+            C.byref(push), C.byref(reduce), _p(abort_flag), C.c_uint64(timeout_cycles), _p(status), _p(snapshot),
+        )
+    )  # fmt: skip
+    _count()
+
+
+class GroupMember(C.Structure):
+    """Mirror of ``p2pfl_group_member``."""
+
+    _fields_ = [
+        ("params", C.c_void_p),
+        ("params_bf16", C.c_void_p),
+        ("snapshot", C.c_void_p),
+        ("abort_flag", C.c_void_p),
+        ("status", C.c_void_p),
+    ]
+
+
+def make_group_member(params, params_bf16, snapshot, abort_flag, status) -> GroupMember:
+    m = GroupMember()
+    m.params, m.params_bf16, m.snapshot = params.data_ptr(), _p(params_bf16).value, _p(snapshot).value
+    m.abort_flag, m.status = _p(abort_flag).value, status.data_ptr()
+    return m
+
+
+def gossip_fused_group(device: int, n: int, tile: int, seq: int, members_dev: torch.Tensor, push_dev: torch.Tensor,
+                       reduce_dev: torch.Tensor, n_members: int, timeout_cycles: int = 0) -> None:  # fmt: skip
+    """The exchange of every federated node of this process that trains on ``device``, as ONE
+    cooperative launch on the current stream; the three tables are packed uint8 device tensors."""
+    _check(
+        lib().p2pfl_gossip_fused_group(
+            C.c_int(device), _stream(), C.c_int(n_members), _p(members_dev), C.c_uint64(n), C.c_uint32(tile), C.c_uint32(seq),
+            _p(push_dev), _p(reduce_dev), C.c_uint64(timeout_cycles),
         )
     )  # fmt: skip
     _count()
@@ -613,6 +647,19 @@ def rt_ipc_open(device: int, handle: bytes) -> int:
 
 def rt_ipc_close(device: int, ptr: int) -> None:
     _check(lib().p2pfl_rt_ipc_close(C.c_int(device), C.c_void_p(ptr)))
+
+
+_clock_hz: dict = {}
+
+
+def rt_sm_clock_hz(device: int) -> float:
+    """Peak SM clock of ``device`` in Hz (cached)."""
+    hz = _clock_hz.get(device)
+    if hz is None:
+        khz = C.c_int(0)
+        _check(lib().p2pfl_rt_sm_clock_khz(C.c_int(device), C.byref(khz)))
+        hz = _clock_hz[device] = float(khz.value) * 1e3 if khz.value > 0 else 1.9e9
+    return hz
 
 
 def rt_enable_peer(device: int, peer: int) -> None:

@@ -164,6 +164,23 @@ class DeviceArena:
     def ipc_handle(self) -> bytes:
         return ops.rt_ipc_export(self.device, self.base)
 
+    def clear_arrivals(self) -> None:
+        """Zero both banks of arrival flags, the status words and the abort word.
+
+        Readiness of a tile is ``flag - seq >= 0`` (signed), so a flag left over from an earlier
+        experiment must never survive into one whose sequence numbers start lower (a reference
+        initiator always starts at 0; the wall-clock base wraps).  Called when the arena goes back to
+        the pool: by then the last round's reduce has consumed every push addressed to this arena and
+        nobody pushes again before the next experiment announces itself."""
+        if self._closed:
+            return
+        geo = self.geo
+        nbytes = geo.off_abort + 256 - geo.off_flags
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize(self.device)
+            tensor_from_ptr(self.base + geo.off_flags, nbytes, torch.uint8, self.device).zero_()
+            torch.cuda.synchronize(self.device)
+
     def close(self) -> None:
         if not self._closed:
             self._closed = True
@@ -201,6 +218,7 @@ class ArenaPool:
         if key is None or arena._closed:
             arena.close()
             return
+        arena.clear_arrivals()
         with cls._lock:
             old = cls._free.pop(key, None)
             cls._free[key] = arena
@@ -236,14 +254,49 @@ class PeerArena:
 
     def close(self) -> None:
         if self._ipc_dev is not None:
-            try:
-                ops.rt_ipc_close(self._ipc_dev, self.base)
-            finally:
-                self._ipc_dev = None
+            dev, self._ipc_dev = self._ipc_dev, None
+            _IpcCache.release(dev, self.base)
 
     @classmethod
     def open_ipc(cls, handle: bytes, geo: ArenaGeometry, local_device: int, peer_device: int) -> "PeerArena":
-        return cls(ops.rt_ipc_open(local_device, handle), geo, peer_device, ipc_opened_on=local_device)
+        return cls(_IpcCache.open(local_device, handle), geo, peer_device, ipc_opened_on=local_device)
+
+
+class _IpcCache:
+    """One ``cudaIpcOpenMemHandle`` per (peer allocation, local device) and PROCESS.
+
+    Several federated nodes of one process (BASELINE config 4: eight per GPU) all talk to the same
+    remote arenas; CUDA maps an exported allocation once per process - a second open of the same
+    handle fails - so the mapping is shared and reference counted."""
+
+    _lock = threading.Lock()
+    _by_handle: Dict[Tuple[int, bytes], List[int]] = {}  # (device, handle) -> [base, refs]
+    _by_base: Dict[Tuple[int, int], bytes] = {}
+
+    @classmethod
+    def open(cls, device: int, handle: bytes) -> int:
+        with cls._lock:
+            ent = cls._by_handle.get((device, handle))
+            if ent is None:
+                base = ops.rt_ipc_open(device, handle)
+                ent = cls._by_handle[(device, handle)] = [base, 0]
+                cls._by_base[(device, base)] = handle
+            ent[1] += 1
+            return ent[0]
+
+    @classmethod
+    def release(cls, device: int, base: int) -> None:
+        with cls._lock:
+            handle = cls._by_base.get((device, base))
+            if handle is None:
+                return
+            ent = cls._by_handle[(device, handle)]
+            ent[1] -= 1
+            if ent[1] > 0:
+                return
+            del cls._by_handle[(device, handle)]
+            del cls._by_base[(device, base)]
+        ops.rt_ipc_close(device, base)
 
 
 # ------------------------------------------------------------------ test harness

@@ -141,6 +141,17 @@ class Settings:
     FUSED_EXCHANGE: bool = True
     """Use the single-kernel push+FedAvg exchange whenever the whole train set has
     device arenas on distinct GPUs; otherwise models are pulled one by one."""
+    FUSED_SNAPSHOT: bool = True
+    """The fused exchange keeps a copy of the pre-exchange model (written by the kernel while it
+    pushes; one extra fp32 store per element).  An exchange that ends with contributors missing is
+    then undone and repeated through add_model messages instead of leaving a partly averaged model."""
+    FUSED_INFO_WAIT: float = 30.0
+    """Longest a trainer waits for a train-set member's ``arena_info`` before deciding how to
+    exchange.  The decision must come out the same on every trainer, so a missing announcement is
+    waited for (every node of this framework announces, arena or not), not guessed around."""
+    ARENA_INFO_WAIT: float = 2.0
+    """Longest a sender waits for the announcement of an extended peer that is still building its
+    learner before it falls back to a host payload for that peer."""
     DEVICE_INBOX_SLOTS: int = 8
     """Inbox slots per arena = the largest train set the data plane can serve."""
     TRAINER_DIFFUSION_GRACE: float = 0.5

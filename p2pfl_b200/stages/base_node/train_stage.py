@@ -56,18 +56,21 @@ class TrainStage(Stage):
         plan = getattr(proto, "plan_fused_exchange", None)
         if plan is not None and getattr(st.learner, "arena", None) is not None:
             fused = plan(st, st.learner)
+        result = None
         if fused is not None:
             # device data plane: ONE kernel pushes this model to every trainer and
             # FedAvg-accumulates theirs into the live parameters as the tiles land
-            contributors, total_w = fused.run(st.seq_base + st.round + 1)
+            result = fused.run(st.seq_base + st.round + 1)
+        if result is not None:
+            contributors, total_w = result
             held = agg.add_model(st.learner.live_params(), contributors, total_w)
             # every trainer that ran the exchange to completion holds the aggregate by
             # construction: GossipModelStage need not wait for their `models_ready`
-            st.fused_complete_round = st.round if fused.complete else None
-            if not fused.complete:
-                # only an incomplete exchange leaves somebody who may need to know what we hold
-                announce_aggregated(proto, st, held)
+            st.fused_complete_round = st.round
         else:
+            # no fused exchange this round, or it did not complete (the local model is back in
+            # place and everybody was told): contribute through add_model messages
+            st.fused_complete_round = None
             held = agg.add_model(st.learner.export_model(), [st.addr], st.learner.get_num_samples()[0])
             announce_aggregated(proto, st, held)
             TrainStage._gossip_partial_aggregates(ctx)

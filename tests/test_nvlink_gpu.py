@@ -40,14 +40,87 @@ def _run_federation(devices, protocol, rounds=2, train_set=None, n=None):
 
 
 @pytest.mark.gpu
-def test_colocated_nodes_use_the_pull_path():
+def test_colocated_trainers_exchange_in_one_group_launch():
+    """Several trainers of one process on ONE GPU (BASELINE config 4): their exchanges run as a
+    single cooperative launch, never as kernels that wait on one another."""
+    from p2pfl_b200.communication.nvlink import NvlinkMemoryProtocol
+
+    stats = _run_federation([DEV], NvlinkMemoryProtocol, rounds=3, n=4, train_set=4)
+    assert all(s["host"] == 0 for s in stats), stats  # nothing went through pickle
+    assert all(s["fused"] == 3 for s in stats), stats
+    assert all(s.get("fused_incomplete", 0) == 0 for s in stats), stats
+
+
+@pytest.mark.gpu
+def test_colocated_trainers_and_a_waiting_node():
+    """Train set smaller than the network, all on one GPU: the trainers use the group launch, the
+    node that waits gets the aggregate by pulling it."""
     from p2pfl_b200.communication.nvlink import NvlinkMemoryProtocol
 
     stats = _run_federation([DEV], NvlinkMemoryProtocol, rounds=2, n=3, train_set=2)
-    assert all(s["host"] == 0 for s in stats), stats  # nothing went through pickle
+    assert all(s["host"] == 0 for s in stats), stats
+    assert sum(s["fused"] for s in stats) == 4, stats  # two trainers x two rounds
     assert sum(s["pulled"] for s in stats) > 0
     assert sum(s["pulled_ms"] for s in stats) > 0.0  # device-timed (CUDA events on the copy stream)
-    assert all(s["fused"] == 0 for s in stats)  # co-located: no kernels that wait on one another
+
+
+def _group_exchange(models, samples, drop=None, timeout_cycles=0):
+    """R members through p2pfl_gossip_fused_group on one GPU; ``drop``: a rank whose tables are left
+    out of the launch (it never pushes), so everybody else misses it."""
+    from p2pfl_b200 import ops
+    from p2pfl_b200.parallel.arena import DeviceArena
+
+    r, n = len(models), models[0].numel()
+    dev = models[0].device
+    arenas = [DeviceArena(n, slots=r, tile=16384, wire_bf16=True, device=dev.index or 0) for _ in range(r)]
+    snaps = [torch.full_like(m, float("nan")) for m in models]
+    try:
+        total = float(sum(samples))
+        members, pushes, reds = [], [], []
+        live = [k for k in range(r) if k != drop]
+        for me in live:
+            arenas[me].params.copy_(models[me])
+            peers = [p for p in range(r) if p != me]
+            pushes.append(ops.make_push_table([arenas[p].slot_ptr(me, 1) for p in peers], [arenas[p].flag_ptr(me, 1) for p in peers], True))
+            reds.append(ops.make_reduce_table([arenas[me].slot_ptr(p, 1) for p in peers], [arenas[me].flag_ptr(p, 1) for p in peers],
+                                              [samples[p] / total for p in peers], me, samples[me] / total, True, True))  # fmt: skip
+            members.append(ops.make_group_member(arenas[me].params, None, snaps[me], arenas[me].abort, arenas[me].status))
+        md, pd, rd = (ops.tables_to_device(t, dev) for t in (members, pushes, reds))
+        ops.gossip_fused_group(dev.index or 0, n, 16384, 1, md, pd, rd, len(live), timeout_cycles)
+        torch.cuda.synchronize(dev)
+        return ([arenas[k].params.clone() for k in range(r)], [arenas[k].status.cpu() for k in range(r)], snaps)
+    finally:
+        for a in arenas:
+            a.close()
+
+
+@pytest.mark.gpu
+def test_group_kernel_matches_fp32_average_and_keeps_a_snapshot():
+    torch.manual_seed(3)
+    n, r = 235264, 5
+    models = [torch.randn(n, device=DEV) for _ in range(r)]
+    samples = [100, 200, 300, 150, 250]
+    outs, status, snaps = _group_exchange(models, samples)
+    ref = sum(w / sum(samples) * m.bfloat16().float() for w, m in zip(samples, models))
+    for k in range(r):
+        assert int(status[k][0]) == 0 and int(status[k][2]) == 0
+        assert torch.equal(outs[k], outs[0])  # identical bits on every member
+        assert torch.allclose(outs[k], ref, atol=2e-6, rtol=1e-5)
+        assert torch.equal(snaps[k], models[k])  # the pre-exchange model, exactly
+
+
+@pytest.mark.gpu
+def test_group_kernel_reports_who_was_missing():
+    """A member that never pushes: the others time out on its tiles, say so in the status words
+    (flag + position mask) and still hold their own model in the snapshot."""
+    torch.manual_seed(4)
+    n, r = 65536, 3
+    models = [torch.randn(n, device=DEV) for _ in range(r)]
+    outs, status, snaps = _group_exchange(models, [1, 1, 1], drop=2, timeout_cycles=2_000_000)
+    for k in (0, 1):
+        assert int(status[k][0]) == 1
+        assert int(status[k][2]) == 0b10  # table position 1 of ranks 0 and 1 is rank 2
+        assert torch.equal(snaps[k], models[k])
 
 
 @pytest.mark.gpu
