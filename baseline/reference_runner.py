@@ -79,12 +79,20 @@ def run_reference_experiment(n_nodes: int, steps: int, warmup: int, fast: bool, 
             torch.cuda.synchronize(d)
 
     def watch() -> None:
-        # all nodes finished >= r rounds  <=>  min over nodes of state.round >= r
+        # all nodes finished >= r rounds  <=>  min over nodes of state.round >= r.  A reference node
+        # can drop out of its own experiment (at 8 nodes its aggregator sometimes raises "release
+        # unlocked lock" and the node stops itself; the others evict it and carry on): once the
+        # experiment has started everywhere, a node whose round went back to None is counted as
+        # lost and the boundaries are those of the nodes still learning.
         seen = -1
+        started = False
         while not stop.is_set():
             rounds = [n.state.round for n in nodes]
-            if all(r is not None for r in rounds):
-                lo = min(rounds)
+            if not started and all(r is not None for r in rounds):
+                started = True
+            live = [r for r in rounds if r is not None]
+            if started and live:
+                lo = min(live)
                 if lo > seen:
                     seen = lo
                     for buf in flush.values():
@@ -96,6 +104,9 @@ def run_reference_experiment(n_nodes: int, steps: int, warmup: int, fast: bool, 
                     if lo > W and "t0" in marks:
                         # every later boundary is a candidate end of the timed region
                         sync_all()
+                        marks["node_rounds"] = marks.get("node_rounds", 0) + len(live) * (lo - W - marks.get("counted", 0))
+                        marks["counted"] = lo - W
+                        marks["live_last"] = len(live)
                         marks["last"] = (lo - W, time.perf_counter(), dict(shim_pl.COUNTERS))
                     if lo >= W + K and "t1" not in marks:
                         marks["t1"] = marks["last"][1]
@@ -147,10 +158,11 @@ def run_reference_experiment(n_nodes: int, steps: int, warmup: int, fast: bool, 
     done, t_end, c_end = marks["last"]
     done = min(done, K)
     ms = (t_end - marks["t0"]) * 1e3
-    samples = n_nodes * n_train * done
+    node_rounds = marks.get("node_rounds", n_nodes * done)  # trainer-rounds actually completed in the region
+    samples = n_train * node_rounds
     value = samples / (ms / 1e3)
-    h2d = (c_end["h2d"] - marks["c0"]["h2d"]) / done / n_nodes
-    d2h = (c_end["d2h"] - marks["c0"]["d2h"]) / done / n_nodes
+    h2d = (c_end["h2d"] - marks["c0"]["h2d"]) / max(node_rounds, 1)
+    d2h = (c_end["d2h"] - marks["c0"]["d2h"]) / max(node_rounds, 1)
     K = done
     return {
         "metric": "fl_train_samples_per_sec",
@@ -177,6 +189,7 @@ def run_reference_experiment(n_nodes: int, steps: int, warmup: int, fast: bool, 
             "timing": "host clock between observed round boundaries, cuda synchronize on both sides",
         },
         "truncated": truncated,
+        "nodes_lost": n_nodes - int(marks.get("live_last", n_nodes)),
         "final": {"test_loss": final.get("test_loss"), "test_accuracy": final.get("test_metric"), "round": final.get("round")},
         "clocks": clocks,
         # the host-clock number above already is end to end (every batch travels host -> device, every

@@ -462,6 +462,7 @@ class FusedExchange:
         self.train_set, self.peers, self.samples = train_set, peers, samples
         self.local = local or [state.addr]
         self.complete = False
+        self._launched: Any = None
 
     def _tables(self, seq: int) -> Tuple[Any, Any]:
         arena = self.learner.arena
@@ -487,40 +488,60 @@ class FusedExchange:
         )
         return push, red
 
-    def run(self, seq: int) -> Optional[Tuple[List[str], int]]:
-        """Launch, wait, and return (contributors, total weight) - or None when the exchange did
-        not complete: the pre-exchange model is back in place then and the caller exchanges through
-        add_model messages (a partly averaged model is never labelled as the round's aggregate)."""
-        learner, arena, proto = self.learner, self.learner.arena, self.proto
-        me, rnd = self.state.addr, self.state.round
-        others = [n for n in self.train_set if n != me]
-        total = float(sum(self.samples[n] for n in self.train_set))
-        wire_bf16 = arena.geo.wire_bf16
+    @property
+    def can_prelaunch(self) -> bool:
+        """True when this node's exchange is a launch of its own (no other trainer of this process on
+        the GPU to meet first): it can be queued behind the training kernels before they have run."""
+        return len(self.local) == 1
+
+    def launch(self, seq: int) -> None:
+        """Queue the single-member exchange on the learner's stream; ``finish`` waits for it."""
+        learner, arena = self.learner, self.learner.arena
         push, red = self._tables(seq)
         timeout_cycles = int(Settings.AGGREGATION_TIMEOUT * ops.rt_sm_clock_hz(arena.device))
         snap = learner.exchange_snapshot()
         began = torch.cuda.Event(enable_timing=True)
         done = torch.cuda.Event(enable_timing=True)
-        grp: Optional[_DeviceGroup] = None
+        with torch.cuda.stream(learner.stream):
+            arena.status.zero_()
+            arena.abort.zero_()
+            began.record(learner.stream)
+            ops.gossip_fused(arena.params, learner.w16, arena.geo.tile, seq, push, red, arena.abort, timeout_cycles,
+                             arena.status, snapshot=snap)  # fmt: skip
+            done.record(learner.stream)
+        self._launched = (seq, began, done, snap)
+
+    def finish(self) -> Optional[Tuple[List[str], int]]:
+        """Wait for a ``launch``-ed exchange; same result as ``run``."""
+        seq, began, done, snap = self._launched
+        me = self.state.addr
+        others = [n for n in self.train_set if n != me]
+        total = float(sum(self.samples[n] for n in self.train_set))
+        return self._finish(seq, began, done, snap, others, total)
+
+    def run(self, seq: int) -> Optional[Tuple[List[str], int]]:
+        """Launch, wait, and return (contributors, total weight) - or None when the exchange did
+        not complete: the pre-exchange model is back in place then and the caller exchanges through
+        add_model messages (a partly averaged model is never labelled as the round's aggregate)."""
+        learner, arena = self.learner, self.learner.arena
+        me = self.state.addr
+        others = [n for n in self.train_set if n != me]
+        total = float(sum(self.samples[n] for n in self.train_set))
         if len(self.local) == 1:
-            with torch.cuda.stream(learner.stream):
-                arena.status.zero_()
-                arena.abort.zero_()
-                began.record(learner.stream)
-                ops.gossip_fused(arena.params, learner.w16, arena.geo.tile, seq, push, red, arena.abort, timeout_cycles,
-                                 arena.status, snapshot=snap)  # fmt: skip
-                done.record(learner.stream)
-        else:
-            grp = self._join_group(seq, push, red, snap, timeout_cycles)
-            if grp is None:
-                return None
-            began, done = grp.began, grp.done
-            learner.stream.wait_event(done)
+            self.launch(seq)
+            return self.finish()
+        # several trainers of this process share the GPU: meet them, ONE cooperative launch for all
+        push, red = self._tables(seq)
+        timeout_cycles = int(Settings.AGGREGATION_TIMEOUT * ops.rt_sm_clock_hz(arena.device))
+        snap = learner.exchange_snapshot()
+        grp = self._join_group(seq, push, red, snap, timeout_cycles)
+        if grp is None:
+            return None
+        learner.stream.wait_event(grp.done)
         try:
-            return self._finish(seq, began, done, snap, others, total)
+            return self._finish(seq, grp.began, grp.done, snap, others, total)
         finally:
-            if grp is not None:
-                _group_leave(arena.device, seq, grp)
+            _group_leave(arena.device, seq, grp)
 
     def _finish(self, seq: int, began: Any, done: Any, snap: Any, others: List[str], total: float) -> Optional[Tuple[List[str], int]]:
         learner, arena, proto = self.learner, self.learner.arena, self.proto

@@ -552,7 +552,11 @@ class B200Learner(TorchLearner):
         ep["graph"] = g
         return ep
 
-    def fit(self) -> None:
+    def fit(self, after_launch: Optional[Any] = None) -> None:
+        """``after_launch`` (fused plans only): called on this thread once the LAST epoch, its
+        validation pass and the copies of their results are queued on the stream, before anything
+        waits for them - whatever it queues (the round's model exchange) starts the moment training
+        ends on the device, with no host round trip in between."""
         if self.epochs <= 0 or self.model is None:
             return
         if not self.fused:
@@ -575,6 +579,7 @@ class B200Learner(TorchLearner):
                 self.adam_m.zero_()
                 self.adam_v.zero_()
                 self.adam_step.zero_()
+            loss_ready = None
             for e in range(self.epochs):
                 if self._interrupt.is_set():
                     logger.info(self.addr, "fit interrupted")
@@ -607,7 +612,18 @@ class B200Learner(TorchLearner):
                     self._prefetch("test")
                 tc = time.perf_counter()
                 # per-epoch validation, as Lightning does for the reference (mlp.py:82-91)
-                val = self._eval_split("val")
+                last = e == self.epochs - 1
+                vh = self._eval_launch("val")
+                if last:
+                    loss_host = ep.get("loss_host")
+                    if loss_host is None:
+                        loss_host = ep["loss_host"] = torch.empty(ep["nb"], dtype=torch.float32).pin_memory()
+                    loss_host.copy_(ep["loss"], non_blocking=True)
+                    loss_ready = torch.cuda.Event()
+                    loss_ready.record()
+                    if after_launch is not None:
+                        after_launch()
+                val = self._eval_result(vh)
                 td = time.perf_counter()
                 ht = self.host_seconds
                 ht["fit_perm"] = ht.get("fit_perm", 0.0) + tb - ta
@@ -616,7 +632,11 @@ class B200Learner(TorchLearner):
                 if val is not None:
                     logger.log_metric(self.addr, "val_loss", val[0], step=(e + 1) * ep["nb"])
                     logger.log_metric(self.addr, "val_metric", val[1], step=(e + 1) * ep["nb"])
-            losses = ep["loss"].cpu()  # one D2H per fit
+            if loss_ready is not None:
+                loss_ready.synchronize()
+                losses = ep["loss_host"].clone()  # one D2H per fit, queued before the exchange
+            else:
+                losses = ep["loss"].cpu()
             self.d2h_bytes += losses.numel() * 4
         sizes = [min(B, n - i * B) for i in range(ep["nb"])]
         for i in range(0, ep["nb"], self.LOG_EVERY):
@@ -663,8 +683,9 @@ class B200Learner(TorchLearner):
         ev["graph"] = g
         return ev
 
-    def _eval_split(self, split: str) -> Optional[Tuple[float, float]]:
-        """(mean loss, accuracy) of the live model on a split: one graph launch, one 8-byte D2H."""
+    def _eval_launch(self, split: str) -> Optional[Tuple[Any, torch.Tensor, Any, int]]:
+        """Queue the evaluation of a split (one graph launch) and the 8-byte copy of its result into
+        pinned memory; nothing waits.  ``_eval_result`` collects."""
         x, _ = self._eval_data(split)
         n = x.shape[0]
         if n == 0:
@@ -675,9 +696,41 @@ class B200Learner(TorchLearner):
         ev = self._graphs[key]
         ev["graph"].replay()
         ops.add_launches(ev["launches"])
-        res = ev["out"].cpu()
+        if "out_host" not in ev:
+            ev["out_host"] = torch.empty(2, dtype=torch.float32).pin_memory()
+        ev["out_host"].copy_(ev["out"], non_blocking=True)
+        ready = torch.cuda.Event()
+        ready.record()
         self.d2h_bytes += 8
-        return float(res[0]) / n, float(res[1]) / n
+        return ev, ev["out_host"], ready, n
+
+    def _eval_result(self, handle: Optional[Tuple[Any, torch.Tensor, Any, int]]) -> Optional[Tuple[float, float]]:
+        if handle is None:
+            return None
+        _, host, ready, n = handle
+        ready.synchronize()
+        return float(host[0]) / n, float(host[1]) / n
+
+    def _eval_split(self, split: str) -> Optional[Tuple[float, float]]:
+        """(mean loss, accuracy) of the live model on a split: one graph launch, one 8-byte D2H."""
+        return self._eval_result(self._eval_launch(split))
+
+    def evaluate_async(self) -> Any:
+        """Queue the test evaluation and return a handle for ``evaluate_finish`` (fused plans only;
+        None otherwise: call ``evaluate``)."""
+        if self.epochs <= 0 or self.model is None or not self.fused:
+            return None
+        with torch.cuda.stream(self._s()):
+            return self._eval_launch("test")
+
+    def evaluate_finish(self, handle: Any) -> Dict[str, float]:
+        res = self._eval_result(handle)
+        if res is None:
+            return {}
+        out = {"test_loss": res[0], "test_metric": res[1]}
+        for k, v in out.items():
+            logger.log_metric(self.addr, k, v)
+        return out
 
     def evaluate(self) -> Dict[str, float]:
         if self.epochs <= 0 or self.model is None:

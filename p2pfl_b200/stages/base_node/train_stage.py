@@ -13,7 +13,7 @@ import time
 from typing import Any, List, Optional, Type
 
 from p2pfl_b200.management.logger import logger
-from p2pfl_b200.stages.common import announce_aggregated, evaluate_and_share, pack_model
+from p2pfl_b200.stages.common import announce_aggregated, broadcast_metrics, evaluate_and_share, pack_model
 from p2pfl_b200.stages.stage import LearningContext, Stage
 from p2pfl_b200.stages.stage_factory import StageFactory
 
@@ -36,31 +36,56 @@ class TrainStage(Stage):
 
         if ctx.early_stopping_fn():
             return None
-        # the metrics wait (lazily queued) for the pre-vote that follows the evaluation: the two
-        # - and last round's models_ready - reach each neighbour as one bundled message
-        will_prevote = TrainStage.will_prevote(ctx)
-        evaluate_and_share(ctx, lazy=will_prevote)
-        if will_prevote:
-            TrainStage.prevote(ctx)
-        t1 = time.time()
-
-        if ctx.early_stopping_fn():
-            return None
-        logger.info(st.addr, "training")
-        st.learner.fit()
-        t2 = time.time()
-
-        if ctx.early_stopping_fn():
-            return None
+        # How this round's models will be exchanged is decided BEFORE any device work is queued (it
+        # depends on the vote and on the arenas the members announced, not on the training).
         fused = None
         plan = getattr(proto, "plan_fused_exchange", None)
         if plan is not None and getattr(st.learner, "arena", None) is not None:
             fused = plan(st, st.learner)
+        seq = st.seq_base + st.round + 1
+        will_prevote = TrainStage.will_prevote(ctx)
+        pipelined = fused is not None and fused.can_prelaunch and hasattr(st.learner, "evaluate_async")
+        handle = st.learner.evaluate_async() if pipelined else None
         result = None
-        if fused is not None:
-            # device data plane: ONE kernel pushes this model to every trainer and
-            # FedAvg-accumulates theirs into the live parameters as the tiles land
-            result = fused.run(st.seq_base + st.round + 1)
+        if handle is not None:
+            # Device pipeline of the round: evaluation, the epoch(s), validation and the exchange are
+            # queued back to back; the host reads their results afterwards.  Between the last training
+            # kernel and the exchange kernel there is no host round trip any more.
+            if will_prevote:
+                TrainStage.prevote(ctx)
+            t1 = time.time()
+            logger.info(st.addr, "training")
+            launched = []
+            st.learner.fit(after_launch=lambda: (fused.launch(seq), launched.append(1)))
+            t2 = time.time()
+            results = st.learner.evaluate_finish(handle)
+            broadcast_metrics(proto, st, results, lazy=True)  # nobody waits on metrics
+            if launched:
+                result = fused.finish()  # always collected: its watchdog is what stops a spinning kernel
+            if ctx.early_stopping_fn():
+                return None
+            if not launched:
+                result = fused.run(seq)
+        else:
+            # the metrics wait (lazily queued) for the pre-vote that follows the evaluation: the two
+            # - and last round's models_ready - reach each neighbour as one bundled message
+            evaluate_and_share(ctx, lazy=will_prevote)
+            if will_prevote:
+                TrainStage.prevote(ctx)
+            t1 = time.time()
+
+            if ctx.early_stopping_fn():
+                return None
+            logger.info(st.addr, "training")
+            st.learner.fit()
+            t2 = time.time()
+
+            if ctx.early_stopping_fn():
+                return None
+            if fused is not None:
+                # device data plane: ONE kernel pushes this model to every trainer and
+                # FedAvg-accumulates theirs into the live parameters as the tiles land
+                result = fused.run(seq)
         if result is not None:
             contributors, total_w = result
             held = agg.add_model(st.learner.live_params(), contributors, total_w)
