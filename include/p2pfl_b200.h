@@ -274,6 +274,28 @@ int p2pfl_gemm_chain_max_cluster(int device);
  * issued, 3 first accumulator complete, 4 epilogue stores issued, 5 fences done, 6 barrier passed. */
 int p2pfl_gemm_chain_set_stamps(void* device_buffer);
 
+/* A whole training EPOCH of the 784-256-128-10 MLP (mlp.py:53-80: forward, cross-entropy, backward,
+ * Adam; batch 32) as ONE launch of one 16-CTA thread-block cluster: bf16 weights resident in shared
+ * memory, layer-1 slices exchanged through distributed shared memory, weight gradients consumed by
+ * Adam straight out of TMEM.  `flat` / `m` / `v` are the fp32 master and Adam moments in ParamLayout
+ * order (l1.weight, l1.bias, l2.weight, l2.bias, l3.weight, l3.bias; slots 128-byte aligned), `w16`
+ * the bf16 working copy of `flat`; all four are updated every step.  xs: bf16 [n_rows, 784], the
+ * epoch's samples in training order; step s uses rows 32s .. 32s+31 (the last step may be partial).
+ * Adam's step number is *step_ptr + s + 1. */
+typedef struct {
+  const void* xs;
+  const int32_t* ys;      /* int32 [n_rows] */
+  int32_t n_rows, n_steps; /* n_steps = ceil(n_rows / 32) */
+  float* flat; float* m; float* v; void* w16;
+  float* grads_out;       /* nullable fp32, same layout as flat: the LAST step's gradients (tests) */
+  float* loss;            /* nullable [n_steps]: sum of the per-sample losses of each step */
+  const int32_t* step_ptr; /* nullable */
+  float lr, beta1, beta2, eps;
+} p2pfl_mlp_epoch_args;
+int p2pfl_mlp_epoch(int device, void* stream, const p2pfl_mlp_epoch_args* args);
+/* 1 if the device can co-schedule the 16-CTA cluster (non-portable size) the epoch kernel needs */
+int p2pfl_mlp_epoch_supported(int device);
+
 /* ----------------------------------------------------------- convolution path
  * K6/K7 (cnn.py:78-81 Conv2d + ReLU + MaxPool2d through cuDNN/ATen) and the
  * ResNet-style blocks of BASELINE.json config 3.  Activations are NHWC bf16.

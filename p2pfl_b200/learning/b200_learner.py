@@ -119,6 +119,7 @@ class B200Learner(TorchLearner):
         """A model qualifies for the fully fused path when it is a plain stack of
         ``nn.Linear`` layers with ReLU in between (the reference MLP)."""
         self.fused = False
+        self._epoch_kernel = False
         self._layers = []
         self.cnn = None
         self.host_seconds: Dict[str, float] = {}  # where the host thread spends a fit (perm upload / launch / sync)
@@ -171,6 +172,20 @@ class B200Learner(TorchLearner):
         self.wT16 = torch.zeros(max(off, 8), dtype=torch.bfloat16, device=self.device)
         self._feat, self._ncls = self._layers[0].in_f, self._layers[-1].out_f
         self.fused = True
+        # the whole-epoch cluster kernel is compiled for one architecture and one parameter layout
+        dims = tuple([self._layers[0].in_f] + [L.out_f for L in self._layers])
+        offs = [o for L in self._layers for o in (L.w_off, L.b_off)]
+        want, o = [], 0
+        for i_f, o_f in zip(ops.MLP_EPOCH_DIMS[:-1], ops.MLP_EPOCH_DIMS[1:]):
+            want += [o, o + i_f * o_f]
+            o += i_f * o_f + (o_f + 31) // 32 * 32
+        self._epoch_kernel = (
+            Settings.MLP_EPOCH_KERNEL
+            and dims == ops.MLP_EPOCH_DIMS
+            and offs == want
+            and int(getattr(self.data, "batch_size", 32)) == ops.MLP_EPOCH_BATCH
+            and ops.mlp_epoch_supported(self.device)
+        )
 
     def _params_written(self) -> None:
         """fp32 master changed from outside: refresh the bf16 working copies."""
@@ -390,6 +405,13 @@ class B200Learner(TorchLearner):
         feat = Ls[0].in_f
         ldB = act["ldB"]
         C = Ls[-1].out_f
+        if self._epoch_kernel and bsz <= ops.MLP_EPOCH_BATCH:
+            # one step through the epoch kernel (tests / odd call sites; an epoch is ONE such call)
+            if step_offset != 1:
+                raise RuntimeError("single steps through the epoch kernel start at step offset 1")
+            ops.mlp_epoch(x16, y, bsz, self.flat, self.adam_m, self.adam_v, self.w16, loss_slot, self.adam_step, lr,
+                          grads=self.grads)  # fmt: skip
+            return
         if Settings.MLP_CHAIN_CLUSTER > 0 and 3 * nL - 1 <= 8 and C <= 256 and bsz <= 32:
             cluster = min(Settings.MLP_CHAIN_CLUSTER, ops.gemm_chain_max_cluster(self.device))
             self._train_step_chain(x16, xT16, y, bsz, act, loss_slot, step_offset, lr, cluster=cluster)
@@ -529,6 +551,13 @@ class B200Learner(TorchLearner):
         lr = float(getattr(self.model, "lr", 1e-3))
 
         def body() -> None:
+            if self._epoch_kernel:
+                # shuffle, then the whole epoch in ONE cluster launch (weights resident on chip)
+                ops.gather_rows(x, ep["perm"], n, feat, _pad8(B), ep["xs"], None, y, ep["ys"])
+                ops.mlp_epoch(ep["xs"], ep["ys"], n, self.flat, self.adam_m, self.adam_v, self.w16, ep["loss"],
+                              self.adam_step, lr)  # fmt: skip
+                ops.add_i32(self.adam_step, nb)
+                return
             ep["loss"].zero_()
             ops.gather_rows(x, ep["perm"], n, feat, _pad8(B), ep["xs"], ep["xsT"] if need_t else None, y, ep["ys"])
             for i in range(nb):

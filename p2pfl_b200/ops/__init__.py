@@ -356,6 +356,42 @@ def gemm_chain(device: torch.device, gemms: Sequence[GemmArgs], links: Sequence[
 _max_cluster: dict = {}
 
 
+class MlpEpochArgs(C.Structure):
+    """Mirror of ``p2pfl_mlp_epoch_args``."""
+
+    _fields_ = [
+        ("xs", C.c_void_p), ("ys", C.c_void_p), ("n_rows", C.c_int32), ("n_steps", C.c_int32),
+        ("flat", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("w16", C.c_void_p),
+        ("grads_out", C.c_void_p), ("loss", C.c_void_p), ("step_ptr", C.c_void_p),
+        ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
+    ]  # fmt: skip
+
+
+MLP_EPOCH_DIMS = (784, 256, 128, 10)  # the architecture the epoch kernel is compiled for
+MLP_EPOCH_BATCH = 32
+_mlp_epoch_ok: dict = {}
+
+
+def mlp_epoch_supported(device: torch.device) -> bool:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _mlp_epoch_ok:
+        _mlp_epoch_ok[idx] = bool(lib().p2pfl_mlp_epoch_supported(C.c_int(idx)))
+    return _mlp_epoch_ok[idx]
+
+
+def mlp_epoch(xs, ys, n_rows: int, flat, m, v, w16, loss, step_ptr, lr: float, grads=None,
+              beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8) -> None:  # fmt: skip
+    """One training epoch of the 784-256-128-10 MLP over ``xs[:n_rows]`` (batches of 32 in row
+    order) as a single cluster launch; updates ``flat`` / ``m`` / ``v`` / ``w16`` in place."""
+    n_steps = (n_rows + MLP_EPOCH_BATCH - 1) // MLP_EPOCH_BATCH
+    a = MlpEpochArgs(
+        xs.data_ptr(), ys.data_ptr(), n_rows, n_steps, flat.data_ptr(), m.data_ptr(), v.data_ptr(), w16.data_ptr(),
+        _p(grads).value, _p(loss).value, _p(step_ptr).value, lr, beta1, beta2, eps,
+    )  # fmt: skip
+    _check(lib().p2pfl_mlp_epoch(_dev(flat), _stream(), C.byref(a)))
+    _count()
+
+
 def gemm_chain_max_cluster(device: torch.device) -> int:
     """Largest cluster size (16, 8, 4, 2, 1) the chain kernel can be launched with on ``device``."""
     dev = device.index if device.index is not None else torch.cuda.current_device()

@@ -120,6 +120,11 @@ class Settings:
     """Longest a lazily queued broadcast waits for company before it is sent on its own."""
     NVTX_RANGES: bool = os.environ.get("P2PFL_NVTX", "0") not in ("", "0")
     """Wrap every stage of the workflow in an NVTX range (``P2PFL_NVTX=1``), for timeline tools."""
+    MLP_EPOCH_KERNEL: bool = True
+    """Train the 784-256-128-10 MLP (batch 32) with ``p2pfl_mlp_epoch``: a whole epoch as ONE launch of
+    a 16-CTA cluster that keeps the bf16 weights in shared memory, hands activations from layer to
+    layer on chip and applies Adam straight out of TMEM.  Other widths / batch sizes, or a device
+    that cannot schedule the cluster, use the per-step paths below."""
     MLP_CHAIN_CLUSTER: int = 16
     """Run the fused MLP step as TWO launches: one thread-block cluster of this many CTAs walks
     every GEMM link (forward chain, loss, dgrad chain, then all weight gradients side by side),

@@ -16,15 +16,33 @@ def _dm(n_train=640, n_test=128, **kw):
     return MnistFederatedDM(0, 1, n_train=n_train, n_test=n_test, **kw)
 
 
-def test_single_step_gradients_match_autograd():
+@pytest.fixture
+def per_step_paths():
+    """The per-step launch arrangements (per link / chain / cluster chain), not the epoch kernel."""
+    from p2pfl_b200.settings import Settings
+
+    prev = Settings.MLP_EPOCH_KERNEL
+    Settings.MLP_EPOCH_KERNEL = False
+    yield
+    Settings.MLP_EPOCH_KERNEL = prev
+
+
+@pytest.mark.parametrize("epoch_kernel", [True, False])
+def test_single_step_gradients_match_autograd(epoch_kernel):
     from p2pfl_b200.learning.b200_learner import B200Learner
     from p2pfl_b200.models import MLP
+    from p2pfl_b200.settings import Settings
 
     torch.manual_seed(0)
     model = MLP(seed=0)
     ref = copy.deepcopy(model).to(DEV)
-    learner = B200Learner(model, _dm(), "t", epochs=1, device=DEV)
-    assert learner.fused
+    prev = Settings.MLP_EPOCH_KERNEL
+    Settings.MLP_EPOCH_KERNEL = epoch_kernel
+    try:
+        learner = B200Learner(model, _dm(), "t", epochs=1, device=DEV)
+    finally:
+        Settings.MLP_EPOCH_KERNEL = prev
+    assert learner.fused and learner._epoch_kernel == epoch_kernel
     x, y = _dm().tensors("train")
     x, y = x[:32], y[:32]
     before = learner.flat.clone()
@@ -46,11 +64,53 @@ def test_single_step_gradients_match_autograd():
     # Adam moved the parameters, the bf16 copies follow the master
     assert not torch.equal(before, learner.flat)
     assert torch.equal(learner.w16, learner.flat.to(torch.bfloat16))
-    L2 = learner._layers[1]
-    w2 = learner.layout.views(learner.flat)["l2.weight"]
-    wt = learner.wT16[L2.wt_off : L2.wt_off + L2.in_f * 128].view(L2.in_f, 128)
-    assert torch.equal(wt, w2.t().to(torch.bfloat16))
+    if not epoch_kernel:  # the per-step paths also keep transposed copies for their dgrad GEMMs
+        L2 = learner._layers[1]
+        w2 = learner.layout.views(learner.flat)["l2.weight"]
+        wt = learner.wT16[L2.wt_off : L2.wt_off + L2.in_f * 128].view(L2.in_f, 128)
+        assert torch.equal(wt, w2.t().to(torch.bfloat16))
     learner.close()
+
+
+def test_epoch_kernel_matches_per_step_path():
+    """The whole-epoch cluster kernel against the per-link launches: single steps (full and partial
+    batches: loss, every gradient, the updated parameters), then whole fits with the same shuffles."""
+    from p2pfl_b200.learning.b200_learner import B200Learner
+    from p2pfl_b200.models import MLP
+    from p2pfl_b200.settings import Settings
+
+    prev = (Settings.MLP_EPOCH_KERNEL, Settings.MLP_CHAIN_CLUSTER)
+    steps, fits = [], []
+    try:
+        for epoch_kernel in (True, False):
+            Settings.MLP_EPOCH_KERNEL, Settings.MLP_CHAIN_CLUSTER = epoch_kernel, 0
+            dm = _dm(n_train=640, n_test=128)
+            learner = B200Learner(MLP(seed=3), dm, "p", epochs=1, device=DEV)
+            assert learner._epoch_kernel == epoch_kernel
+            x, y = dm.tensors("train")
+            res = []
+            for lo, hi in ((0, 32), (32, 64), (64, 96), (96, 126), (126, 134)):  # two partial batches
+                loss = learner.debug_single_step(x[lo:hi], y[lo:hi])
+                res.append((loss, learner.grads.clone(), learner.flat.clone()))
+            steps.append(res)
+            learner.close()
+            dm = _dm(n_train=1000, n_test=250, noise=6.0)
+            torch.manual_seed(7)
+            learner = B200Learner(MLP(seed=1), dm, "t", epochs=2, device=DEV)
+            learner.fit()
+            fits.append((learner.flat.clone(), learner.evaluate(), learner.w16.clone()))
+            assert torch.equal(learner.w16, learner.flat.to(torch.bfloat16))
+            learner.close()
+    finally:
+        Settings.MLP_EPOCH_KERNEL, Settings.MLP_CHAIN_CLUSTER = prev
+    for i, ((la, ga, fa), (lb, gb, fb)) in enumerate(zip(*steps)):
+        assert abs(la - lb) < 1e-4 * max(1.0, abs(lb)), (i, la, lb)
+        rel = float((ga - gb).norm() / (gb.norm() + 1e-12))
+        assert rel < 2e-3, f"step {i}: relative gradient difference {rel:.5f}"
+        assert float((fa - fb).abs().max()) < 2.5e-3, i  # Adam: at most about one lr per step where a sign flips
+    (fa, ra, _), (fb, rb, _) = fits
+    assert abs(ra["test_loss"] - rb["test_loss"]) < 5e-3, (ra, rb)
+    assert float((fa - fb).abs().max()) < 5e-3
 
 
 def test_fit_and_evaluate_graphs():
@@ -92,7 +152,7 @@ def test_fit_and_evaluate_graphs():
         Settings.RESET_OPTIMIZER_EACH_ROUND = default
 
 
-def test_cluster_chain_fit_matches_per_link_fit():
+def test_cluster_chain_fit_matches_per_link_fit(per_step_paths):
     """Whole fits (graph replays, the same shuffles, a partial last batch of 4) with the step as
     one thread-block cluster and as one launch per link must end in the same model."""
     from p2pfl_b200.learning.b200_learner import B200Learner
@@ -309,7 +369,7 @@ def test_pdl_on_and_off_give_identical_training():
 
 
 @pytest.mark.parametrize("mode", ["chain1", "cluster1", "cluster2", "cluster8", "cluster16"])
-def test_chain_kernel_matches_per_link_launches(mode):
+def test_chain_kernel_matches_per_link_launches(mode, per_step_paths):
     """The GEMM chain - one CTA, or one thread-block cluster that also walks the weight-gradient
     link - must reproduce the per-link launches: same tiles, same MMA order, same epilogues (only
     the loss sum and the last layer's bias gradient are reduced with atomics, whose order may differ)."""
