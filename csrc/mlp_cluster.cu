@@ -37,10 +37,11 @@ constexpr int D0 = 784, D1 = 256, D2 = 128, D3 = 10;
 constexpr int kRows = 32;            // batch rows per step (boxes are sized for it)
 constexpr int kK0Boxes = 13;         // 64-wide column boxes of the layer-1 input (784 -> 832, zero padded)
 constexpr int kR1 = D1 / kC;         // rows of W1 (= features of layer 1) per CTA
-constexpr int kW2Owners = D2 / 16;   // CTAs 0..7 own 16 rows of W2 each
+constexpr int kR2 = D2 / kC;         // rows of W2 per CTA (8; their GEMM is 16 wide, the upper half is ignored)
 constexpr int kW3Owner = 8;          // CTA 8 owns W3 / b3
-constexpr int kWorkers = 16;         // worker warps (epilogues, Adam); warp 16 issues TMA and MMA
-constexpr int kThreads = (kWorkers + 1) * 32;
+constexpr int kWarps = 16;           // four warps per scheduler: 128 registers per thread
+constexpr int kIssuer = 1;           // lane 0 of this warp issues every TMA load and every MMA
+constexpr int kThreads = kWarps * 32;
 
 // offsets in the flat parameter vector (ParamLayout: state_dict order, 128-byte aligned slots)
 constexpr uint32_t kW1Off = 0, kB1Off = kW1Off + D1 * D0, kW2Off = kB1Off + D1, kB2Off = kW2Off + D2 * D1,
@@ -58,9 +59,8 @@ constexpr uint32_t oH2 = oH1 + 4 * kBoxX;                 // H2     [32 x 128]  
 constexpr uint32_t oDZ3 = oH2 + 2 * kBoxX;                // dZ3    [32 x 16(64)]
 constexpr uint32_t oDZ2 = oDZ3 + kBoxX;                   // dZ2    [32 x 128]   2 boxes
 constexpr uint32_t oDZ1S = oDZ2 + 2 * kBoxX;              // dZ1, own 16 columns
-constexpr uint32_t oDZ2S = oDZ1S + kBoxX;                 // dZ2, own 16 columns (W2 owners)
 constexpr uint32_t kBoxW1 = kR1 * 128;                    // 2 KB
-constexpr uint32_t oW1 = oDZ2S + kBoxX;                   // W1 rows of this CTA [16 x 832] 13 boxes
+constexpr uint32_t oW1 = oDZ1S + kBoxX;                   // W1 rows of this CTA [16 x 832] 13 boxes
 constexpr uint32_t kBoxW2 = D2 * 128;                     // 16 KB
 constexpr uint32_t oW2 = oW1 + kK0Boxes * kBoxW1;         // W2 [128 x 256] 4 boxes
 constexpr uint32_t kBoxW3 = 16 * 128;                     // 2 KB
@@ -69,8 +69,15 @@ constexpr uint32_t kSmemBytes = oW3 + 2 * kBoxW3;
 static_assert(kSmemBytes <= 200 * 1024, "shared-memory budget");
 static_assert(oW1 % 1024 == 0 && oW2 % 1024 == 0 && oW3 % 1024 == 0, "swizzled boxes start on 1 KB boundaries");
 
-// TMEM columns of the accumulators
-constexpr uint32_t cFwd2 = 0, cDg3 = 128, cDg2 = 0, cFwd1 = 256, cFwd3 = 272, cWg1 = 288, cWg2 = 400, cWg3 = 432;
+// TMEM columns.  Accumulators whose lifetimes do not overlap share columns; the 224 columns that
+// are left hold Adam's two moments of this CTA's W1 rows (fp32, same lane / column map as the
+// weight-gradient accumulator, so the update is TMEM -> registers -> TMEM with no other traffic).
+constexpr uint32_t cFwd2 = 0, cDg3 = 0;                   // [32 x 128]
+constexpr uint32_t cFwd1 = 128, cFwd3 = 128, cDg2 = 128;  // [32 x 16]; the W3 gradient reuses them last
+constexpr uint32_t cWg3 = 128;
+constexpr uint32_t cWg1 = 144;                            // 7 tiles x 16 columns
+constexpr uint32_t cWg2 = 256;                            // 2 tiles x 16 columns
+constexpr uint32_t cM = 288, cV = 400;                    // 7 x 16 columns each
 
 struct Args {
   const int32_t* ys;
@@ -83,6 +90,9 @@ struct Args {
   const int32_t* step_ptr;
   int32_t n_rows, n_steps;
   float lr, b1, b2, eps;
+#ifdef P2PFL_BRINGUP
+  long long* stamps;  // [16 CTAs][16] SM-clock stamps of one steady-state step, see p2pfl_mlp_epoch_set_stamps
+#endif
 };
 
 // byte offset of element (row, col) inside a swizzled box row group: col in [0, 64)
@@ -110,6 +120,16 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
       : "r"(taddr));
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t cluster_rank() {
   uint32_t r;
@@ -161,11 +181,16 @@ __device__ __forceinline__ AdamK adam_consts(const Args& a, int t) {
   k.eps = a.eps;
   return k;
 }
-// same arithmetic as adam_kernel (elementwise.cu), weight decay 0
+// Same formula as adam_kernel (elementwise.cu), weight decay 0, with the hardware's approximate
+// square root and reciprocal (2 ulp each): the 16 SMs of the cluster update all 235 k parameters every
+// step, and with IEEE sqrt / division this loop alone was 7 us of a 21 us step.
 __device__ __forceinline__ float adam_one(const AdamK& k, float g, float& p, float& m, float& v) {
-  m = k.b1 * m + k.one_m_b1 * g;
-  v = k.b2 * v + k.one_m_b2 * g * g;
-  p -= k.step_size * (m / (sqrtf(v) * k.inv_sqrt_bc2 + k.eps));
+  m = fmaf(k.b1, m, k.one_m_b1 * g);
+  v = fmaf(k.b2, v, k.one_m_b2 * g * g);
+  float sq, rc;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(v));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(fmaf(sq, k.inv_sqrt_bc2, k.eps)));
+  p = fmaf(-k.step_size * m, rc, p);
   return p;
 }
 
@@ -240,10 +265,11 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t c = cluster_rank();
-  const bool issuer = warp == kWorkers;
+  const bool issuer = warp == kIssuer;
   const bool one = issuer && lane == 0;  // the thread that issues every TMA load and every MMA
-  const int q = warp & 3, g = warp >> 2;  // TMEM lane quarter of this warp / its group among the workers
-  const bool q0 = !issuer && q == 0;      // warps that can read accumulator lanes 0..31 (the batch rows)
+  const int q = warp & 3, g = warp >> 2;  // TMEM lane quarter of this warp / its group of four
+  const bool q0 = q == 0;                 // warps that can read accumulator lanes 0..31 (the batch rows)
+  const uint32_t lane_base = (uint32_t)(q * 32) << 16;
 
   if (one) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmX)) : "memory");
@@ -270,11 +296,30 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     mbar_expect_tx(smem_u32(&mb_x), kK0Boxes * kBoxX);
     for (int j = 0; j < kK0Boxes; ++j) tma_load_2d(&tmX, smem_u32(&mb_x), sb + oXB + j * kBoxX, 64 * j, 0);
   }
+  // Adam's moments of this CTA's W1 rows move into TMEM for the whole epoch: lane = input
+  // feature (mod 128), column = 16 * tile + row, exactly where the gradient of that weight lands
+  for (int tt = g; tt < 7; tt += 4) {
+    const uint32_t i = 128u * tt + 32u * q + lane;
+    uint32_t rm[16], rv[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const uint32_t idx = kW1Off + (kR1 * c + j) * D0 + i;
+      rm[j] = i < (uint32_t)D0 ? __float_as_uint(a.m[idx]) : 0u;
+      rv[j] = i < (uint32_t)D0 ? __float_as_uint(a.v[idx]) : 0u;
+    }
+    tmem_st16(tmem + lane_base + cM + 16 * tt, rm);
+    tmem_st16(tmem + lane_base + cV + 16 * tt, rv);
+  }
+  tmem_st_wait();
+  tc_fence_before();
   cluster_barrier();  // every CTA of the cluster is running before anybody stores into a neighbour
+  tc_fence_after();
 
   const int32_t step0 = a.step_ptr ? *a.step_ptr : 0;
   uint32_t par = 0;  // parity of the next completion of mb_mma (every thread counts the links alike)
   uint32_t hbits = 0;  // warp 0: which of this row's 16 layer-1 activations are positive (ReLU mask)
+  // bias gradients (batch sums) wait in a register of the lane that will apply them with the weights
+  float g_b1 = 0.f, g_b2 = 0.f, g_b3 = 0.f;
 
 #define LINK_WAIT()                  \
   mbar_wait(smem_u32(&mb_mma), par); \
@@ -285,7 +330,15 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   __syncthreads();    \
   tc_fence_after()
 
+#ifdef P2PFL_BRINGUP
+#define STAMP(slot) \
+  if (a.stamps && warp == 0 && lane == 0 && t == stamp_step) a.stamps[c * 16 + (slot)] = clock64()
+  const int stamp_step = a.n_steps > 8 ? a.n_steps / 2 : a.n_steps - 1;
+#else
+#define STAMP(slot)
+#endif
   for (int t = 0; t < a.n_steps; ++t) {
+    STAMP(0);
     const int row0 = t * kRows;
     const int bsz = (a.n_rows - row0) < kRows ? (a.n_rows - row0) : kRows;
     const AdamK ak = adam_consts(a, step0 + t + 1);
@@ -310,6 +363,7 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
 #pragma unroll
       for (int j = 0; j < 16; ++j) bias[j] = __ldcg(a.flat + kB1Off + kR1 * c + j);
       LINK_WAIT();
+      STAMP(1);
       uint32_t r[16];
       tmem_ld16(tmem + cFwd1, r);
       float h[16];
@@ -332,11 +386,13 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         st_cluster_u4(map_to_cta(a1, dst), u[1]);
       }
       fence_async_all();  // these stores (other CTAs' shared memory included) vs. the MMAs that will read them
+      STAMP(2);
     }
     par ^= 1u;
     tc_fence_before();
     cluster_barrier();  // (a) all 16 slices of H1 are in place everywhere
     tc_fence_after();
+    STAMP(3);
 
     // ================= layer 2 (every CTA): H2 = relu(H1 . W2^T + b2) =================
     if (issuer) {
@@ -371,6 +427,7 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     }
     LINK_END();
 
+    STAMP(4);
     // ================= layer 3 + softmax cross-entropy (every CTA): dZ3 =================
     if (issuer) {
       if (lane == 0) {
@@ -421,17 +478,16 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       loss = warp_sum(loss);
       if (c == 0 && lane == 0 && a.loss) a.loss[t] = loss;
       if (c == kW3Owner) {
-        float mine = 0.f;
 #pragma unroll
         for (int j = 0; j < D3; ++j) {
           const float s = warp_sum(gq[j]);
-          if (lane == j) mine = s;
+          if (lane == j) g_b3 = s;
         }
-        if (lane < D3) adam_bias(a, ak, kB3Off + lane, mine);
       }
     }
     LINK_END();
 
+    STAMP(5);
     // ================= dZ2 = (dZ3 . W3) * (H2 > 0)  (every CTA) =================
     if (issuer) {
       if (lane == 0) {
@@ -462,32 +518,32 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       pack32(x, u);
 #pragma unroll
       for (int ch = 0; ch < 4; ++ch) st_shared_u4(chunk_addr(dbox, lane, (g & 1) * 4 + ch), u[ch]);
-      if (c < (uint32_t)kW2Owners && (int)(c >> 1) == g) {
-        // this CTA owns rows 16c..16c+15 of W2: keep its 16 columns of dZ2 as a box of their own
-        // (the B operand of its weight-gradient GEMM) and fold their batch sums into b2 right away
-        const bool hi = (c & 1) != 0;
-        st_shared_u4(chunk_addr(sb + oDZ2S, lane, 0), hi ? u[2] : u[0]);
-        st_shared_u4(chunk_addr(sb + oDZ2S, lane, 1), hi ? u[3] : u[1]);
-        float mine = 0.f;
+      if ((int)(c >> 2) == g) {
+        // this CTA owns rows 8c..8c+7 of W2: batch sums of its 8 columns of dZ2 = its slice of db2
+        const uint32_t off = (c & 3u) * 8u;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float s = warp_sum(hi ? x[16 + j] : x[j]);
-          if (lane == j) mine = s;
+        for (int j = 0; j < 32; ++j) {
+          if ((uint32_t)(j >> 3) == (c & 3u)) {  // warp-uniform: the same 8 columns for every lane
+            const float s = warp_sum(x[j]);
+            if ((uint32_t)lane == (uint32_t)j - off) g_b2 = s;
+          }
         }
-        if (lane < 16) adam_bias(a, ak, kB2Off + 16 * c + lane, mine);
       }
       fence_async_smem();
     }
     LINK_END();
 
+    STAMP(6);
     // ================= dZ1[:, 16c .. 16c+15] = (dZ2 . W2)[:, own columns] * (H1 > 0) =================
     if (issuer) {
       if (lane == 0) {
-        // K = the 128 output rows of W2, 16 per MMA; B = the W2 boxes read MN-major (N = 256 columns)
-        const uint32_t idesc = make_idesc(256, 2);
+        // K = the 128 output rows of W2, 16 per MMA; B = the W2 boxes read MN-major, only the 16
+        // columns this CTA's rows of W1 need (a 32-byte offset inside the swizzled rows of box c / 4)
+        const uint32_t idesc = make_idesc(16, 2);
+        const uint32_t bsl = sb + oW2 + (c >> 2) * kBoxW2 + (c & 3u) * 32u;
         for (int s = 0; s < 8; ++s) {
           const uint64_t da = make_smem_desc(sb + oDZ2 + (s >> 2) * kBoxX) + 2 * (s & 3);
-          const uint64_t db = mn_desc(sb + oW2, kBoxW2) + (uint64_t)s * (2048 >> 4);
+          const uint64_t db = mn_desc(bsl, kBoxW2) + (uint64_t)s * (2048 >> 4);
           umma_bf16(tmem + cDg2, da, db, idesc, s != 0 ? 1u : 0u);
         }
         umma_commit(smem_u32(&mb_mma));
@@ -496,7 +552,7 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     } else if (warp == 0) {
       LINK_WAIT();
       uint32_t r[16];
-      tmem_ld16(tmem + cDg2 + kR1 * c, r);
+      tmem_ld16(tmem + cDg2, r);
       float x[16];
 #pragma unroll
       for (int j = 0; j < 16; ++j) x[j] = (hbits >> j & 1u) ? __uint_as_float(r[j]) : 0.f;
@@ -505,19 +561,19 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       st_shared_u4(chunk_addr(sb + oDZ1S, lane, 0), u[0]);
       st_shared_u4(chunk_addr(sb + oDZ1S, lane, 1), u[1]);
       fence_async_smem();
-      float mine = 0.f;
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
         const float s = warp_sum(x[j]);
-        if (lane == j) mine = s;
+        if (lane == j) g_b1 = s;
       }
-      if (lane < 16) adam_bias(a, ak, kB1Off + kR1 * c + lane, mine);
     }
     LINK_END();
 
+    STAMP(7);
     // ================= weight gradients (owner CTAs) -> Adam =================
     // D[input feature i (accumulator lane), output row j] = sum_b act[b, i] * dZ[b, j]: the activation
-    // boxes read MN-major give M = i, the owner's 16 columns of dZ give N = 16, K = the batch rows.
+    // boxes read MN-major give M = i, 16 columns of dZ give N = 16, K = the batch rows.
+    const bool last = t + 1 == a.n_steps;
     if (issuer) {
       if (lane == 0) {
         const uint32_t idesc = make_idesc(16, 3);
@@ -525,66 +581,129 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           for (int s = 0; s < 2; ++s)
             umma_bf16(tmem + cWg1 + 16 * tt, mn_desc(sb + oXB + 2 * tt * kBoxX, kBoxX) + (uint64_t)s * (2048 >> 4),
                       mn_desc(sb + oDZ1S, kBoxX) + (uint64_t)s * (2048 >> 4), idesc, s != 0 ? 1u : 0u);
-        if (c < (uint32_t)kW2Owners)
-          for (int tt = 0; tt < 2; ++tt)
-            for (int s = 0; s < 2; ++s)
-              umma_bf16(tmem + cWg2 + 16 * tt, mn_desc(sb + oH1 + 2 * tt * kBoxX, kBoxX) + (uint64_t)s * (2048 >> 4),
-                        mn_desc(sb + oDZ2S, kBoxX) + (uint64_t)s * (2048 >> 4), idesc, s != 0 ? 1u : 0u);
+        // rows 8c..8c+7 of W2: the 16 columns of dZ2 that contain them (slices start on 32-byte
+        // boundaries inside the swizzled rows; CTAs 2k and 2k+1 read the same one and keep one half each)
+        const uint32_t b2sl = sb + oDZ2 + (c >> 3) * kBoxX + ((c >> 1) & 3u) * 32u;
+        for (int tt = 0; tt < 2; ++tt)
+          for (int s = 0; s < 2; ++s)
+            umma_bf16(tmem + cWg2 + 16 * tt, mn_desc(sb + oH1 + 2 * tt * kBoxX, kBoxX) + (uint64_t)s * (2048 >> 4),
+                      mn_desc(b2sl, kBoxX) + (uint64_t)s * (2048 >> 4), idesc, s != 0 ? 1u : 0u);
         if (c == (uint32_t)kW3Owner)
           for (int s = 0; s < 2; ++s)
             umma_bf16(tmem + cWg3, mn_desc(sb + oH2, kBoxX) + (uint64_t)s * (2048 >> 4),
                       mn_desc(sb + oDZ3, kBoxX) + (uint64_t)s * (2048 >> 4), idesc, s != 0 ? 1u : 0u);
         umma_commit(smem_u32(&mb_mma));
-        mbar_wait(smem_u32(&mb_mma), par);
-        // the batch buffer is free: the next batch travels while Adam runs
-        if (t + 1 < a.n_steps) {
-          mbar_expect_tx(smem_u32(&mb_x), kK0Boxes * kBoxX);
-          for (int j = 0; j < kK0Boxes; ++j) tma_load_2d(&tmX, smem_u32(&mb_x), sb + oXB + j * kBoxX, 64 * j, row0 + kRows);
-        }
       }
       __syncwarp();
-    } else {
-      LINK_WAIT();
-      const uint32_t lane_base = (uint32_t)(q * 32) << 16;
-      // --- W1 rows of this CTA: 7 tiles of 128 input features, two tiles per warp group
-#pragma unroll 1
-      for (int tt = g; tt < 7; tt += 4) {
-        uint32_t r[16];
-        tmem_ld16(tmem + lane_base + cWg1 + 16 * tt, r);
-        const uint32_t i = 128u * tt + 32u * q + lane;
-        if (i < (uint32_t)D0) {
-          float p[16];
-          adam_column<16>(a, ak, r, kW1Off + (kR1 * c) * D0 + i, D0, p);
-          // refresh this CTA's resident bf16 rows (K-major boxes: row j, column i)
-          const uint32_t box = sb + oW1 + (i >> 6) * kBoxW1;
+    }
+    // What Adam reads besides the gradients does not depend on this step: fetch it while the MMAs
+    // run - the fp32 masters of this thread's W1 elements, and master + moments of its W2 elements.
+    float p1[2][16];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) st_shared_b16(box + swz(j, i & 63u), __float2bfloat16_rn(p[j]));
+    for (int sl = 0; sl < 2; ++sl) {
+      const int tt = g + 4 * sl;
+      const uint32_t i = 128u * tt + 32u * q + lane;
+      const float* src = a.flat + kW1Off + (kR1 * c) * D0 + i;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) p1[sl][j] = (tt < 7 && i < (uint32_t)D0) ? __ldcg(src + j * D0) : 0.f;
+    }
+    float p2[kR2], m2[kR2], v2[kR2];
+    const uint32_t w2base = kW2Off + (kR2 * c) * D1 + 128u * (g & 1) + 32u * q + lane;
+    if (g < 2) {
+#pragma unroll
+      for (int j = 0; j < kR2; ++j) {
+        p2[j] = __ldcg(a.flat + w2base + j * D1);
+        m2[j] = __ldcg(a.m + w2base + j * D1);
+        v2[j] = __ldcg(a.v + w2base + j * D1);
+      }
+    }
+    LINK_WAIT();
+    STAMP(8);
+    if (one && !last) {
+      // the batch buffer is free: the next batch travels while Adam runs
+      mbar_expect_tx(smem_u32(&mb_x), kK0Boxes * kBoxX);
+      for (int j = 0; j < kK0Boxes; ++j) tma_load_2d(&tmX, smem_u32(&mb_x), sb + oXB + j * kBoxX, 64 * j, row0 + kRows);
+    }
+    // --- W2 rows 8c..8c+7 first (the other CTAs wait for these): 2 tiles of 128 input features
+    if (g < 2) {
+      uint32_t r[16];
+      tmem_ld16(tmem + lane_base + cWg2 + 16 * g, r);
+#pragma unroll
+      for (int j = 0; j < kR2; ++j) {
+        const float gj = __uint_as_float((c & 1u) ? r[8 + j] : r[j]);
+        adam_one(ak, gj, p2[j], m2[j], v2[j]);
+        a.flat[w2base + j * D1] = p2[j];
+        a.m[w2base + j * D1] = m2[j];
+        a.v[w2base + j * D1] = v2[j];
+        a.w16[w2base + j * D1] = __float2bfloat16_rn(p2[j]);
+        if (a.grads) a.grads[w2base + j * D1] = gj;
+      }
+    }
+    // --- W3 (CTA 8): one tile, 10 rows
+    if (c == (uint32_t)kW3Owner && g == 2) {
+      uint32_t r[16];
+      tmem_ld16(tmem + lane_base + cWg3, r);
+      const uint32_t i = 32u * q + lane;
+      float p[16];
+      adam_column<D3>(a, ak, r, kW3Off + i, D2, p);
+    }
+    // --- biases: the lanes that hold the batch sums
+    if (warp == 0 && lane < kR1) adam_bias(a, ak, kB1Off + kR1 * c + lane, g_b1);
+    if (q0 && (int)(c >> 2) == g && lane < kR2) adam_bias(a, ak, kB2Off + kR2 * c + lane, g_b2);
+    if (warp == 0 && c == (uint32_t)kW3Owner && lane < D3) adam_bias(a, ak, kB3Off + lane, g_b3);
+    // --- W1 rows of this CTA: 7 tiles of 128 input features, two tiles per warp group; the moments
+    // live in TMEM beside the gradient
+#pragma unroll
+    for (int sl = 0; sl < 2; ++sl) {
+      const int tt = g + 4 * sl;
+      if (tt < 7) {  // warp-uniform
+        uint32_t r[16], rm[16], rv[16];
+        tmem_ld16(tmem + lane_base + cWg1 + 16 * tt, r);
+        tmem_ld16(tmem + lane_base + cM + 16 * tt, rm);
+        tmem_ld16(tmem + lane_base + cV + 16 * tt, rv);
+        const uint32_t i = 128u * tt + 32u * q + lane;
+        const bool valid = i < (uint32_t)D0;
+        const uint32_t sdst = sb + oW1 + (i >> 6) * kBoxW1 + (((i & 63u) >> 3) << 4) + ((i & 7u) << 1);
+        float* pdst = a.flat + kW1Off + (kR1 * c) * D0 + i;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          float mj = __uint_as_float(rm[j]), vj = __uint_as_float(rv[j]);
+          if (!valid) r[j] = 0u;
+          adam_one(ak, __uint_as_float(r[j]), p1[sl][j], mj, vj);
+          rm[j] = __float_as_uint(mj);
+          rv[j] = __float_as_uint(vj);
+          if (valid) {
+            pdst[j * D0] = p1[sl][j];
+            // this CTA's resident bf16 rows: row j, column i of the K-major swizzled boxes
+            st_shared_b16(sdst + j * 128u ^ ((uint32_t)(j & 7) << 4), __float2bfloat16_rn(p1[sl][j]));
+          }
+        }
+        tmem_st16(tmem + lane_base + cM + 16 * tt, rm);
+        tmem_st16(tmem + lane_base + cV + 16 * tt, rv);
+        if (valid && (last || a.grads)) {
+          const uint32_t idx0 = kW1Off + (kR1 * c) * D0 + i;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            if (last) {
+              a.w16[idx0 + j * D0] = __float2bfloat16_rn(p1[sl][j]);
+              a.m[idx0 + j * D0] = __uint_as_float(rm[j]);
+              a.v[idx0 + j * D0] = __uint_as_float(rv[j]);
+            }
+            if (a.grads) a.grads[idx0 + j * D0] = __uint_as_float(r[j]);
+          }
         }
       }
-      // --- W2 rows 16c..16c+15 (CTAs 0..7): 2 tiles of 128 input features
-      if (c < (uint32_t)kW2Owners && g < 2) {
-        uint32_t r[16];
-        tmem_ld16(tmem + lane_base + cWg2 + 16 * g, r);
-        const uint32_t i = 128u * g + 32u * q + lane;
-        float p[16];
-        adam_column<16>(a, ak, r, kW2Off + (16 * c) * D1 + i, D1, p);
-      }
-      // --- W3 (CTA 8): one tile, 10 rows
-      if (c == (uint32_t)kW3Owner && g == 2) {
-        uint32_t r[16];
-        tmem_ld16(tmem + lane_base + cWg3, r);
-        const uint32_t i = 32u * q + lane;
-        float p[16];
-        adam_column<D3>(a, ak, r, kW3Off + i, D2, p);
-      }
-      fence_async_smem();      // the rewritten W1 rows vs. the next step's layer-1 MMAs
-      __threadfence();         // W2 / W3 / biases in global memory vs. the other CTAs' reloads
-      fence_async_global();
     }
+    tmem_st_wait();
+    STAMP(9);
+    fence_async_smem();      // the rewritten W1 rows vs. the next step's layer-1 MMAs
+    fence_async_global();    // W2 / W3 in global memory vs. the other CTAs' TMA reloads (the barrier releases them)
+    STAMP(10);
     par ^= 1u;
     tc_fence_before();
     cluster_barrier();  // (b) every owner has published its rows
     tc_fence_after();
+    STAMP(11);
     if (one && t + 1 < a.n_steps) {
       fence_async_global();
       mbar_expect_tx(smem_u32(&mb_w), 4 * kBoxW2 + 2 * kBoxW3);
@@ -594,6 +713,7 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   }
 #undef LINK_WAIT
 #undef LINK_END
+#undef STAMP
 
   tc_fence_before();
   __syncthreads();
@@ -658,6 +778,22 @@ void launch_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr, cudaStrea
 
 }  // namespace
 
+#ifdef P2PFL_BRINGUP
+static long long* g_mlp_stamps = nullptr;
+#endif
+// Bring-up builds only (-DP2PFL_BRINGUP): `device_buffer` (int64 [16][16], NULL = off) receives the
+// SM-clock stamps every CTA's warp 0 takes at the phase boundaries of one steady-state step.
+extern "C" int p2pfl_mlp_epoch_set_stamps(void* device_buffer) {
+#ifdef P2PFL_BRINGUP
+  g_mlp_stamps = reinterpret_cast<long long*>(device_buffer);
+  return 0;
+#else
+  if (device_buffer == nullptr) return 0;
+  set_error("clock stamps are compiled out of this build (rebuild with -DP2PFL_BRINGUP)");
+  return -1;
+#endif
+}
+
 // 1 when this device can co-schedule the 16-CTA cluster the epoch kernel needs, else 0.
 extern "C" int p2pfl_mlp_epoch_supported(int device) {
   if (cudaSetDevice(device) != cudaSuccess) return 0;
@@ -707,6 +843,9 @@ extern "C" int p2pfl_mlp_epoch(int device, void* stream, const p2pfl_mlp_epoch_a
   a.b1 = e->beta1;
   a.b2 = e->beta2;
   a.eps = e->eps;
+#ifdef P2PFL_BRINGUP
+  a.stamps = g_mlp_stamps;
+#endif
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr[1];
   launch_config(cfg, attr, as_stream(stream));
