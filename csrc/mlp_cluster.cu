@@ -69,15 +69,15 @@ constexpr uint32_t kSmemBytes = oW3 + 2 * kBoxW3;
 static_assert(kSmemBytes <= 200 * 1024, "shared-memory budget");
 static_assert(oW1 % 1024 == 0 && oW2 % 1024 == 0 && oW3 % 1024 == 0, "swizzled boxes start on 1 KB boundaries");
 
-// TMEM columns.  Accumulators whose lifetimes do not overlap share columns; the 224 columns that
-// are left hold Adam's two moments of this CTA's W1 rows (fp32, same lane / column map as the
-// weight-gradient accumulator, so the update is TMEM -> registers -> TMEM with no other traffic).
-constexpr uint32_t cFwd2 = 0, cDg3 = 0;                   // [32 x 128]
-constexpr uint32_t cFwd1 = 128, cFwd3 = 128, cDg2 = 128;  // [32 x 16]; the W3 gradient reuses them last
-constexpr uint32_t cWg3 = 128;
-constexpr uint32_t cWg1 = 144;                            // 7 tiles x 16 columns
-constexpr uint32_t cWg2 = 256;                            // 2 tiles x 16 columns
-constexpr uint32_t cM = 288, cV = 400;                    // 7 x 16 columns each
+// TMEM columns.  Accumulators whose lifetimes do not overlap share columns; the 336 columns that
+// are left hold the fp32 master and Adam's two moments of this CTA's W1 rows for the whole epoch, in
+// the lane / column map of the weight-gradient accumulator (lane = input feature mod 128, column =
+// 16 * tile + row): the update of W1 is TMEM -> registers -> TMEM, with no other memory traffic.
+constexpr uint32_t cFwd2 = 0, cDg3 = 0, cWg2 = 0;                 // [128 features x 32 batch columns] / 2 tiles x 16
+constexpr uint32_t cFwd1 = 32, cFwd3 = 32, cDg2 = 32, cWg3 = 32;  // [32 batch rows x 16] / 1 tile x 16
+constexpr uint32_t cWg1 = 48;                                     // 7 tiles x 16 columns
+constexpr uint32_t cM = 160, cV = 272, cP = 384;                  // 7 x 16 columns each
+static_assert(cP + 112 <= 512, "TMEM columns");
 
 struct Args {
   const int32_t* ys;
@@ -91,7 +91,7 @@ struct Args {
   int32_t n_rows, n_steps;
   float lr, b1, b2, eps;
 #ifdef P2PFL_BRINGUP
-  long long* stamps;  // [16 CTAs][16] SM-clock stamps of one steady-state step, see p2pfl_mlp_epoch_set_stamps
+  long long* stamps;  // [16 CTAs][32] SM-clock stamps of one steady-state step, see p2pfl_mlp_epoch_set_stamps
 #endif
 };
 
@@ -121,6 +121,17 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ld_shared_bf16(uint32_t addr) {
+  unsigned short h;
+  asm volatile("ld.shared.b16 %0, [%1];" : "=h"(h) : "r"(addr));
+  return __uint_as_float((uint32_t)h << 16);
+}
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
@@ -163,7 +174,7 @@ __device__ __forceinline__ void st_shared_b16(uint32_t addr, __nv_bfloat16 v) {
 }
 // generic-proxy writes to shared memory become visible to the async proxy (tcgen05.mma operands)
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.async.shared::cluster;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 
 struct AdamK {
@@ -244,7 +255,7 @@ __device__ __forceinline__ void adam_column(const Args& a, const AdamK& k, const
   }
 }
 // Adam of one bias element (gradient already summed over the batch)
-__device__ __forceinline__ void adam_bias(const Args& a, const AdamK& k, uint32_t idx, float g) {
+__device__ __forceinline__ float adam_bias(const Args& a, const AdamK& k, uint32_t idx, float g) {
   float p = __ldcg(a.flat + idx), m = __ldcg(a.m + idx), v = __ldcg(a.v + idx);
   adam_one(k, g, p, m, v);
   a.flat[idx] = p;
@@ -252,6 +263,7 @@ __device__ __forceinline__ void adam_bias(const Args& a, const AdamK& k, uint32_
   a.v[idx] = v;
   a.w16[idx] = __float2bfloat16_rn(p);
   if (a.grads) a.grads[idx] = g;
+  return p;
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -262,6 +274,8 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   const uint32_t sb = smem_u32(smem);
   __shared__ __align__(8) uint64_t mb_mma, mb_x, mb_w, mb_w1;
   __shared__ uint32_t tmem_base_smem;
+  __shared__ float s_b1[kR1];      // this CTA's slice of b1 (kept current by the lanes that update it)
+  __shared__ float s_db2[4][kR2];  // batch sums of this CTA's 8 columns of dZ2: one partial per warp group
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t c = cluster_rank();
@@ -281,6 +295,7 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) tmem_alloc(smem_u32(&tmem_base_smem), 512);
+  if (threadIdx.x >= 32 && threadIdx.x < 32 + kR1) s_b1[threadIdx.x - 32] = a.flat[kB1Off + kR1 * c + threadIdx.x - 32];
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -296,30 +311,50 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     mbar_expect_tx(smem_u32(&mb_x), kK0Boxes * kBoxX);
     for (int j = 0; j < kK0Boxes; ++j) tma_load_2d(&tmX, smem_u32(&mb_x), sb + oXB + j * kBoxX, 64 * j, 0);
   }
-  // Adam's moments of this CTA's W1 rows move into TMEM for the whole epoch: lane = input
-  // feature (mod 128), column = 16 * tile + row, exactly where the gradient of that weight lands
+  // The fp32 master and Adam's moments of this CTA's W1 rows move into TMEM for the whole epoch: lane
+  // = input feature (mod 128), column = 16 * tile + row, exactly where the gradient of that weight lands
   for (int tt = g; tt < 7; tt += 4) {
     const uint32_t i = 128u * tt + 32u * q + lane;
-    uint32_t rm[16], rv[16];
+    uint32_t rm[16], rv[16], rp[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
       const uint32_t idx = kW1Off + (kR1 * c + j) * D0 + i;
       rm[j] = i < (uint32_t)D0 ? __float_as_uint(a.m[idx]) : 0u;
       rv[j] = i < (uint32_t)D0 ? __float_as_uint(a.v[idx]) : 0u;
+      rp[j] = i < (uint32_t)D0 ? __float_as_uint(a.flat[idx]) : 0u;
     }
     tmem_st16(tmem + lane_base + cM + 16 * tt, rm);
     tmem_st16(tmem + lane_base + cV + 16 * tt, rv);
+    tmem_st16(tmem + lane_base + cP + 16 * tt, rp);
   }
   tmem_st_wait();
   tc_fence_before();
   cluster_barrier();  // every CTA of the cluster is running before anybody stores into a neighbour
   tc_fence_after();
 
+  // Layer 1 of step `step` (issuing thread only): H1[:, 16c .. 16c+15] pre-activation = X . W1_c^T.  It
+  // needs nothing from the other CTAs - the batch and this CTA's own rows of W1 - so it is issued as
+  // soon as Adam has rewritten those rows, BEFORE the step's closing cluster barrier, and runs under it.
+  auto issue_layer1 = [&](int step) {
+    if (step == 0) mbar_wait(smem_u32(&mb_w1), 0);
+    mbar_wait(smem_u32(&mb_x), (uint32_t)step & 1u);
+    tc_fence_after();
+    fence_async_smem();
+    const uint32_t idesc = make_idesc(16);
+    for (int j = 0; j < kK0Boxes; ++j) {
+      const uint64_t da = make_smem_desc(sb + oXB + j * kBoxX), db = make_smem_desc(sb + oW1 + j * kBoxW1);
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) umma_bf16(tmem + cFwd1, da + 2 * ks, db + 2 * ks, idesc, (j | ks) != 0 ? 1u : 0u);
+    }
+    umma_commit(smem_u32(&mb_mma));
+  };
+  if (one) issue_layer1(0);
+
   const int32_t step0 = a.step_ptr ? *a.step_ptr : 0;
   uint32_t par = 0;  // parity of the next completion of mb_mma (every thread counts the links alike)
   uint32_t hbits = 0;  // warp 0: which of this row's 16 layer-1 activations are positive (ReLU mask)
   // bias gradients (batch sums) wait in a register of the lane that will apply them with the weights
-  float g_b1 = 0.f, g_b2 = 0.f, g_b3 = 0.f;
+  float g_b1 = 0.f, g_b3 = 0.f;
 
 #define LINK_WAIT()                  \
   mbar_wait(smem_u32(&mb_mma), par); \
@@ -332,36 +367,32 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
 
 #ifdef P2PFL_BRINGUP
 #define STAMP(slot) \
-  if (a.stamps && warp == 0 && lane == 0 && t == stamp_step) a.stamps[c * 16 + (slot)] = clock64()
+  if (a.stamps && warp == 0 && lane == 0 && t == stamp_step) a.stamps[c * 32 + (slot)] = clock64()
   const int stamp_step = a.n_steps > 8 ? a.n_steps / 2 : a.n_steps - 1;
+#define STAMP1(slot) \
+  if (a.stamps && lane == 0 && t == stamp_step) a.stamps[c * 32 + (slot)] = clock64()
 #else
 #define STAMP(slot)
+#define STAMP1(slot)
 #endif
   for (int t = 0; t < a.n_steps; ++t) {
     STAMP(0);
     const int row0 = t * kRows;
     const int bsz = (a.n_rows - row0) < kRows ? (a.n_rows - row0) : kRows;
     const AdamK ak = adam_consts(a, step0 + t + 1);
+    const float bias2 = __ldcg(a.flat + kB2Off + 32u * q + lane);  // used after barrier (a): latency hidden
+    float bias3[D3];
+    if (warp == 0) {
+#pragma unroll
+      for (int j = 0; j < D3; ++j) bias3[j] = __ldcg(a.flat + kB3Off + j);
+    }
 
     // ================= layer 1: H1[:, 16c .. 16c+15] = relu(X . W1_c^T + b1_c) =================
-    if (issuer) {
-      if (lane == 0) {
-        if (t == 0) mbar_wait(smem_u32(&mb_w1), 0);
-        mbar_wait(smem_u32(&mb_x), (uint32_t)t & 1u);
-        tc_fence_after();
-        const uint32_t idesc = make_idesc(16);
-        for (int j = 0; j < kK0Boxes; ++j) {
-          const uint64_t da = make_smem_desc(sb + oXB + j * kBoxX), db = make_smem_desc(sb + oW1 + j * kBoxW1);
-#pragma unroll
-          for (int ks = 0; ks < 4; ++ks) umma_bf16(tmem + cFwd1, da + 2 * ks, db + 2 * ks, idesc, (j | ks) != 0 ? 1u : 0u);
-        }
-        umma_commit(smem_u32(&mb_mma));
-      }
-      __syncwarp();
-    } else if (q0) {
+    // (the MMAs were issued before the previous step's closing barrier - see issue_layer1 below)
+    if (q0) {
       float bias[16];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) bias[j] = __ldcg(a.flat + kB1Off + kR1 * c + j);
+      for (int j = 0; j < 16; ++j) bias[j] = s_b1[j];
       LINK_WAIT();
       STAMP(1);
       uint32_t r[16];
@@ -394,35 +425,37 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     tc_fence_after();
     STAMP(3);
 
-    // ================= layer 2 (every CTA): H2 = relu(H1 . W2^T + b2) =================
+    // ================= layer 2 (every CTA): H2^T[feature, batch] = relu(W2 . H1^T + b2) =================
+    // The 128 features sit on the accumulator lanes, so all four lane quarters hold live rows and
+    // all 16 warps share the epilogue: 8 batch columns per thread (with the batch on the lanes only
+    // the four quarter-0 warps could read the result, 32 columns per thread, one after the other).
     if (issuer) {
       if (lane == 0) {
         mbar_wait(smem_u32(&mb_w), (uint32_t)t & 1u);  // W2 / W3 as updated by the previous step
         tc_fence_after();
         fence_async_smem();
-        const uint32_t idesc = make_idesc(128);
+        const uint32_t idesc = make_idesc(32);
         for (int j = 0; j < 4; ++j) {
-          const uint64_t da = make_smem_desc(sb + oH1 + j * kBoxX), db = make_smem_desc(sb + oW2 + j * kBoxW2);
+          const uint64_t da = make_smem_desc(sb + oW2 + j * kBoxW2), db = make_smem_desc(sb + oH1 + j * kBoxX);
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks) umma_bf16(tmem + cFwd2, da + 2 * ks, db + 2 * ks, idesc, (j | ks) != 0 ? 1u : 0u);
         }
         umma_commit(smem_u32(&mb_mma));
       }
       __syncwarp();
-    } else if (q0) {
-      float x[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) x[j] = __ldcg(a.flat + kB2Off + 32 * g + j);
+    }
+    {
+      const uint32_t o = 32u * q + lane;  // feature of this thread
+      const float bias = bias2;
       LINK_WAIT();
-      uint32_t r[32];
-      tmem_ld32(tmem + cFwd2 + 32 * g, r);
+      uint32_t r[8];
+      tmem_ld8(tmem + lane_base + cFwd2 + 8 * g, r);
+      const uint32_t dst = sb + oH2 + (o >> 6) * kBoxX + (((o & 63u) >> 3) << 4) + ((o & 7u) << 1);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) x[j] = fmaxf(__uint_as_float(r[j]) + x[j], 0.f);
-      uint4 u[4];
-      pack32(x, u);
-      const uint32_t box = sb + oH2 + (g >> 1) * kBoxX;
-#pragma unroll
-      for (int ch = 0; ch < 4; ++ch) st_shared_u4(chunk_addr(box, lane, (g & 1) * 4 + ch), u[ch]);
+      for (int k = 0; k < 8; ++k) {
+        const uint32_t b = 8u * g + k;  // batch row
+        st_shared_b16((dst + b * 128u) ^ ((b & 7u) << 4), __float2bfloat16_rn(fmaxf(__uint_as_float(r[k]) + bias, 0.f)));
+      }
       fence_async_smem();
     }
     LINK_END();
@@ -441,9 +474,6 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       }
       __syncwarp();
     } else if (warp == 0) {
-      float bias[D3];
-#pragma unroll
-      for (int j = 0; j < D3; ++j) bias[j] = __ldcg(a.flat + kB3Off + j);
       const int y = lane < bsz ? a.ys[row0 + lane] : -1;
       LINK_WAIT();
       uint32_t r[16];
@@ -451,7 +481,7 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       float x[D3], mx = -INFINITY;
 #pragma unroll
       for (int j = 0; j < D3; ++j) {
-        x[j] = __uint_as_float(r[j]) + bias[j];
+        x[j] = __uint_as_float(r[j]) + bias3[j];
         mx = fmaxf(mx, x[j]);
       }
       float se = 0.f;
@@ -488,47 +518,37 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     LINK_END();
 
     STAMP(5);
-    // ================= dZ2 = (dZ3 . W3) * (H2 > 0)  (every CTA) =================
+    // ================= dZ2^T[feature, batch] = (W3^T . dZ3^T) * (H2 > 0)  (every CTA) =================
     if (issuer) {
       if (lane == 0) {
-        // K = the 16 output rows of W3; B is the same W3 boxes read MN-major (N = its 128 columns)
-        umma_bf16(tmem + cDg3, make_smem_desc(sb + oDZ3), mn_desc(sb + oW3, kBoxW3), make_idesc(128, 2), 0u);
+        // A = the W3 boxes read MN-major (M = its 128 columns, K = its 16 rows), B = dZ3 (N = batch rows)
+        umma_bf16(tmem + cDg3, mn_desc(sb + oW3, kBoxW3), make_smem_desc(sb + oDZ3), make_idesc(32, 1), 0u);
         umma_commit(smem_u32(&mb_mma));
       }
       __syncwarp();
-    } else if (q0) {
-      const uint32_t hbox = sb + oH2 + (g >> 1) * kBoxX, dbox = sb + oDZ2 + (g >> 1) * kBoxX;
-      uint4 hv[4];
+    }
+    {
+      const uint32_t o = 32u * q + lane;
+      const uint32_t off = (o >> 6) * kBoxX + (((o & 63u) >> 3) << 4) + ((o & 7u) << 1);
+      float h[8];
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch) hv[ch] = ld_shared_u4(chunk_addr(hbox, lane, (g & 1) * 4 + ch));
+      for (int k = 0; k < 8; ++k) {
+        const uint32_t b = 8u * g + k;
+        h[k] = ld_shared_bf16((sb + oH2 + off + b * 128u) ^ ((b & 7u) << 4));
+      }
       LINK_WAIT();
-      uint32_t r[32];
-      tmem_ld32(tmem + cDg3 + 32 * g, r);
-      float x[32];
+      uint32_t r[8];
+      tmem_ld8(tmem + lane_base + cDg3 + 8 * g, r);
+      float part = 0.f;
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch) {
-        const uint32_t w[4] = {hv[ch].x, hv[ch].y, hv[ch].z, hv[ch].w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          x[ch * 8 + 2 * k] = (__uint_as_float(w[k] << 16) > 0.f) ? __uint_as_float(r[ch * 8 + 2 * k]) : 0.f;
-          x[ch * 8 + 2 * k + 1] = (__uint_as_float(w[k] & 0xFFFF0000u) > 0.f) ? __uint_as_float(r[ch * 8 + 2 * k + 1]) : 0.f;
-        }
+      for (int k = 0; k < 8; ++k) {
+        const uint32_t b = 8u * g + k;
+        const float d = h[k] > 0.f ? __uint_as_float(r[k]) : 0.f;
+        part += d;
+        st_shared_b16((sb + oDZ2 + off + b * 128u) ^ ((b & 7u) << 4), __float2bfloat16_rn(d));
       }
-      uint4 u[4];
-      pack32(x, u);
-#pragma unroll
-      for (int ch = 0; ch < 4; ++ch) st_shared_u4(chunk_addr(dbox, lane, (g & 1) * 4 + ch), u[ch]);
-      if ((int)(c >> 2) == g) {
-        // this CTA owns rows 8c..8c+7 of W2: batch sums of its 8 columns of dZ2 = its slice of db2
-        const uint32_t off = (c & 3u) * 8u;
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          if ((uint32_t)(j >> 3) == (c & 3u)) {  // warp-uniform: the same 8 columns for every lane
-            const float s = warp_sum(x[j]);
-            if ((uint32_t)lane == (uint32_t)j - off) g_b2 = s;
-          }
-        }
-      }
+      // this CTA owns rows 8c..8c+7 of W2 (and of b2): their batch sums, one partial per warp group
+      if (o - kR2 * c < (uint32_t)kR2) s_db2[g][o - kR2 * c] = part;
       fence_async_smem();
     }
     LINK_END();
@@ -596,17 +616,7 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       }
       __syncwarp();
     }
-    // What Adam reads besides the gradients does not depend on this step: fetch it while the MMAs
-    // run - the fp32 masters of this thread's W1 elements, and master + moments of its W2 elements.
-    float p1[2][16];
-#pragma unroll
-    for (int sl = 0; sl < 2; ++sl) {
-      const int tt = g + 4 * sl;
-      const uint32_t i = 128u * tt + 32u * q + lane;
-      const float* src = a.flat + kW1Off + (kR1 * c) * D0 + i;
-#pragma unroll
-      for (int j = 0; j < 16; ++j) p1[sl][j] = (tt < 7 && i < (uint32_t)D0) ? __ldcg(src + j * D0) : 0.f;
-    }
+    // What Adam reads for W2 besides the gradient does not depend on this step: fetch it while the MMAs run
     float p2[kR2], m2[kR2], v2[kR2];
     const uint32_t w2base = kW2Off + (kR2 * c) * D1 + 128u * (g & 1) + 32u * q + lane;
     if (g < 2) {
@@ -648,8 +658,12 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       adam_column<D3>(a, ak, r, kW3Off + i, D2, p);
     }
     // --- biases: the lanes that hold the batch sums
-    if (warp == 0 && lane < kR1) adam_bias(a, ak, kB1Off + kR1 * c + lane, g_b1);
-    if (q0 && (int)(c >> 2) == g && lane < kR2) adam_bias(a, ak, kB2Off + kR2 * c + lane, g_b2);
+    if (warp == 0 && lane < kR1) {
+      s_b1[lane] = adam_bias(a, ak, kB1Off + kR1 * c + lane, g_b1);
+    }
+    if (warp == 2 && lane < kR2) {
+      adam_bias(a, ak, kB2Off + kR2 * c + lane, (s_db2[0][lane] + s_db2[1][lane]) + (s_db2[2][lane] + s_db2[3][lane]));
+    }
     if (warp == 0 && c == (uint32_t)kW3Owner && lane < D3) adam_bias(a, ak, kB3Off + lane, g_b3);
     // --- W1 rows of this CTA: 7 tiles of 128 input features, two tiles per warp group; the moments
     // live in TMEM beside the gradient
@@ -657,35 +671,36 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     for (int sl = 0; sl < 2; ++sl) {
       const int tt = g + 4 * sl;
       if (tt < 7) {  // warp-uniform
-        uint32_t r[16], rm[16], rv[16];
+        uint32_t r[16], rm[16], rv[16], rp[16];
         tmem_ld16(tmem + lane_base + cWg1 + 16 * tt, r);
         tmem_ld16(tmem + lane_base + cM + 16 * tt, rm);
         tmem_ld16(tmem + lane_base + cV + 16 * tt, rv);
+        tmem_ld16(tmem + lane_base + cP + 16 * tt, rp);
         const uint32_t i = 128u * tt + 32u * q + lane;
         const bool valid = i < (uint32_t)D0;
         const uint32_t sdst = sb + oW1 + (i >> 6) * kBoxW1 + (((i & 63u) >> 3) << 4) + ((i & 7u) << 1);
-        float* pdst = a.flat + kW1Off + (kR1 * c) * D0 + i;
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-          float mj = __uint_as_float(rm[j]), vj = __uint_as_float(rv[j]);
+          float pj = __uint_as_float(rp[j]), mj = __uint_as_float(rm[j]), vj = __uint_as_float(rv[j]);
           if (!valid) r[j] = 0u;
-          adam_one(ak, __uint_as_float(r[j]), p1[sl][j], mj, vj);
+          adam_one(ak, __uint_as_float(r[j]), pj, mj, vj);
+          rp[j] = __float_as_uint(pj);
           rm[j] = __float_as_uint(mj);
           rv[j] = __float_as_uint(vj);
-          if (valid) {
-            pdst[j * D0] = p1[sl][j];
-            // this CTA's resident bf16 rows: row j, column i of the K-major swizzled boxes
-            st_shared_b16(sdst + j * 128u ^ ((uint32_t)(j & 7) << 4), __float2bfloat16_rn(p1[sl][j]));
-          }
+          // this CTA's resident bf16 rows: row j, column i of the K-major swizzled boxes
+          if (valid) st_shared_b16(sdst + j * 128u ^ ((uint32_t)(j & 7) << 4), __float2bfloat16_rn(pj));
         }
         tmem_st16(tmem + lane_base + cM + 16 * tt, rm);
         tmem_st16(tmem + lane_base + cV + 16 * tt, rv);
+        tmem_st16(tmem + lane_base + cP + 16 * tt, rp);
         if (valid && (last || a.grads)) {
+          // the epoch ends: master, moments and the bf16 copy go back to global memory
           const uint32_t idx0 = kW1Off + (kR1 * c) * D0 + i;
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             if (last) {
-              a.w16[idx0 + j * D0] = __float2bfloat16_rn(p1[sl][j]);
+              a.flat[idx0 + j * D0] = __uint_as_float(rp[j]);
+              a.w16[idx0 + j * D0] = __float2bfloat16_rn(__uint_as_float(rp[j]));
               a.m[idx0 + j * D0] = __uint_as_float(rm[j]);
               a.v[idx0 + j * D0] = __uint_as_float(rv[j]);
             }
@@ -698,10 +713,15 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     STAMP(9);
     fence_async_smem();      // the rewritten W1 rows vs. the next step's layer-1 MMAs
     fence_async_global();    // W2 / W3 in global memory vs. the other CTAs' TMA reloads (the barrier releases them)
-    STAMP(10);
     par ^= 1u;
     tc_fence_before();
-    cluster_barrier();  // (b) every owner has published its rows
+    __syncthreads();         // this CTA's rows of W1 are rewritten, its accumulators are drained
+    tc_fence_after();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");  // (b), first half
+    if (one && !last) issue_layer1(t + 1);  // issued and run while the other CTAs arrive
+    __syncwarp();
+    STAMP(10);
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");  // (b) every owner has published its rows
     tc_fence_after();
     STAMP(11);
     if (one && t + 1 < a.n_steps) {
@@ -714,6 +734,7 @@ mlp_epoch_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
 #undef LINK_WAIT
 #undef LINK_END
 #undef STAMP
+#undef STAMP1
 
   tc_fence_before();
   __syncthreads();
@@ -781,7 +802,7 @@ void launch_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr, cudaStrea
 #ifdef P2PFL_BRINGUP
 static long long* g_mlp_stamps = nullptr;
 #endif
-// Bring-up builds only (-DP2PFL_BRINGUP): `device_buffer` (int64 [16][16], NULL = off) receives the
+// Bring-up builds only (-DP2PFL_BRINGUP): `device_buffer` (int64 [16][32], NULL = off) receives the
 // SM-clock stamps every CTA's warp 0 takes at the phase boundaries of one steady-state step.
 extern "C" int p2pfl_mlp_epoch_set_stamps(void* device_buffer) {
 #ifdef P2PFL_BRINGUP
