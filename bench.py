@@ -281,7 +281,10 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     Settings.VOTE_TIMEOUT = 120.0
 
     if world > 1:
-        from p2pfl_b200.communication.nvlink import NvlinkCommunicationProtocol as Proto
+        if args.control == "grpc":
+            from p2pfl_b200.communication.nvlink import NvlinkCommunicationProtocol as Proto
+        else:
+            from p2pfl_b200.communication.nvlink import NvlinkSocketProtocol as Proto
 
         port0 = int(os.environ.get("MASTER_PORT", "29500")) + 211
         address = f"127.0.0.1:{port0 + rank}"
@@ -428,7 +431,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         "impl": "p2pfl_b200",
         "config": bench_config(world, n_train),
         "arm": {
-            "control_plane": "in-memory (1 node)" if world == 1 else "gRPC loopback + NVLink device data plane",
+            "control_plane": "in-memory (1 node)" if world == 1 else f"{args.control} loopback + NVLink device data plane",
             "timing": "CUDA events on the learner's stream, max over ranks",
         },
         "final": {"test_loss": float(fm_t[0]), "test_accuracy": float(fm_t[1]), "round": fm.get("round"),
@@ -504,6 +507,8 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ref-fast", action="store_true", help="zero the reference's pacing sleeps (not the stock path)")
     ap.add_argument("--timeout", type=float, default=1500.0)
+    ap.add_argument("--control", default="socket", choices=["socket", "grpc"],
+                    help="control-plane transport between the ranks (the data plane is NVLink either way)")
     ap.add_argument("--ref-budget", type=float, default=600.0,
                     help="reference arm: seconds after which the timed region is closed at the last finished round")
     args = ap.parse_args()

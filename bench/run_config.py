@@ -109,7 +109,10 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
 
         addr = lambda g: f"cfg-node-{g}"  # noqa: E731
     else:
-        from p2pfl_b200.communication.nvlink import NvlinkCommunicationProtocol as Proto
+        if args.control == "grpc":
+            from p2pfl_b200.communication.nvlink import NvlinkCommunicationProtocol as Proto
+        else:
+            from p2pfl_b200.communication.nvlink import NvlinkSocketProtocol as Proto
         from p2pfl_b200.learning.b200_learner import B200Learner as Learner
 
         addr = lambda g: f"127.0.0.1:{port0 + g}"  # noqa: E731
@@ -210,6 +213,7 @@ def main() -> None:
     ap.add_argument("--timeout", type=float, default=900.0)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ref-fast", action="store_true")
+    ap.add_argument("--control", default="socket", choices=["socket", "grpc"])
     args = ap.parse_args()
     if args.impl == "reference":
         from baseline.reference_configs import run_reference_config

@@ -1,3 +1,7 @@
-from p2pfl_b200.communication.nvlink.nvlink_protocol import NvlinkCommunicationProtocol, NvlinkMemoryProtocol
+from p2pfl_b200.communication.nvlink.nvlink_protocol import (
+    NvlinkCommunicationProtocol,
+    NvlinkMemoryProtocol,
+    NvlinkSocketProtocol,
+)
 
-__all__ = ["NvlinkCommunicationProtocol", "NvlinkMemoryProtocol"]
+__all__ = ["NvlinkCommunicationProtocol", "NvlinkMemoryProtocol", "NvlinkSocketProtocol"]

@@ -97,7 +97,15 @@ class NvlinkCommunicationProtocol(BaseProtocol):
     control = "grpc"
 
     def __init__(self, addr: str = "127.0.0.1") -> None:
-        transport: Transport = GrpcTransport(addr) if self.control == "grpc" else MemoryTransport(addr)
+        transport: Transport
+        if self.control == "grpc":
+            transport = GrpcTransport(addr)
+        elif self.control == "socket":
+            from p2pfl_b200.communication.sockets import SocketTransport
+
+            transport = SocketTransport(addr)
+        else:
+            transport = MemoryTransport(addr)
         super().__init__(transport)
         self._node: Any = None
         self._peers: Dict[str, PeerInfo] = {}
@@ -638,6 +646,13 @@ def _abort_stream(self: NvlinkCommunicationProtocol, learner: Any) -> torch.cuda
 
 
 NvlinkCommunicationProtocol._abort_stream = _abort_stream  # type: ignore[attr-defined]
+
+
+class NvlinkSocketProtocol(NvlinkCommunicationProtocol):
+    """Same data plane; control plane over framed stream sockets (one process per GPU, all nodes
+    of this framework: several times cheaper per message than gRPC)."""
+
+    control = "socket"
 
 
 class NvlinkMemoryProtocol(NvlinkCommunicationProtocol):

@@ -8,11 +8,12 @@ import pytest
 from p2pfl_b200.communication.grpc import GrpcCommunicationProtocol
 from p2pfl_b200.communication.grpc.address import AddressParser
 from p2pfl_b200.communication.memory import InMemoryCommunicationProtocol
+from p2pfl_b200.communication.sockets import SocketCommunicationProtocol
 from p2pfl_b200.node import Node
 from p2pfl_b200.settings import Settings
 from p2pfl_b200.utils import full_connection, wait_convergence
 
-PROTOCOLS = [InMemoryCommunicationProtocol, GrpcCommunicationProtocol]
+PROTOCOLS = [InMemoryCommunicationProtocol, GrpcCommunicationProtocol, SocketCommunicationProtocol]
 
 
 def _nodes(n, protocol):

@@ -19,7 +19,9 @@ from p2pfl_b200.settings import Settings
 from p2pfl_b200.stages.base_node.vote_train_set_stage import tally_votes
 from p2pfl_b200.utils import check_equal_models, wait_4_results, wait_convergence
 
-PROTOCOLS = [InMemoryCommunicationProtocol, GrpcCommunicationProtocol]
+from p2pfl_b200.communication.sockets import SocketCommunicationProtocol  # noqa: E402
+
+PROTOCOLS = [InMemoryCommunicationProtocol, GrpcCommunicationProtocol, SocketCommunicationProtocol]
 
 
 def _dm(i=0, n=1):
