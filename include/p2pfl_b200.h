@@ -165,6 +165,26 @@ int p2pfl_gossip_fused_group(int device, void* stream, int n_members,
                              const p2pfl_group_member* members_dev, uint64_t n, uint32_t tile,
                              uint32_t seq, const p2pfl_push_table* push_tables_dev,
                              const p2pfl_reduce_table* reduce_tables_dev, uint64_t timeout_cycles);
+/* G1 / G3 with the copy engine (cp.async.bulk): every 16384-element tile of src[begin, end) is
+ * fetched into shared memory by one bulk load, converted there when the table's wire is bf16, and
+ * stored into every peer of the table by one bulk store each; then the tile's flag takes `seq`.
+ * With `inbox` entries pointing at slot[me] this is the push of the fused exchange (mode B); with
+ * entries pointing at the peers' PARAMETERS (fp32 wire) it is the model store of init / diffusion
+ * (start_learning_stage.py:95-136, gossip_model_stage.py:85-132) - `begin` / `end` select a
+ * sub-range of the arena (whole tiles; SURVEY appendix C rule 5).  The arenas' tile must be 16384. */
+int p2pfl_gossip_push_bulk(int device, void* stream, const float* src, uint64_t n, uint64_t begin,
+                           uint64_t end, uint32_t seq, const p2pfl_push_table* table);
+/* G1 mode A: the sender scales its tiles by `weight` and the copy engine ADDS them into each
+ * peer's fp32 accumulator (cp.reduce.async.bulk ... add.f32, performed in the peer's L2: no SM of
+ * the receiver takes part); `inbox` entries are the accumulators, `flags` per-tile arrival counters.
+ * The order of the additions is not fixed, so results are not bit-reproducible (fedavg.py:49-54). */
+int p2pfl_gossip_push_reduce_bulk(int device, void* stream, const float* src, uint64_t n, float weight,
+                                  const p2pfl_push_table* table);
+/* Receiver side of mode A: per tile wait for `n_senders` arrivals, then params = acc + self_weight
+ * * params (+ bf16 copy); acc and the counters are left zeroed for the next exchange. */
+int p2pfl_gossip_finalize_acc(int device, void* stream, float* params, void* params_bf16 /* nullable */,
+                              float* acc, uint32_t* counts, uint64_t n, int n_senders, float self_weight,
+                              uint64_t timeout_cycles, int32_t* status /* nullable */);
 /* Single-GPU emulation of R ranks exchanging through one cooperative launch
  * (test harness for machines with fewer GPUs than ranks). */
 int p2pfl_gossip_fused_emulated(int device, void* stream, int n_ranks, float* const* params,

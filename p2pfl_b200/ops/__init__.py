@@ -652,6 +652,37 @@ def gossip_fused_emulated(params: List[torch.Tensor], tile: int, seq: int, push_
     _count()
 
 
+def gossip_push_bulk(src: torch.Tensor, seq: int, table: PushTable, begin: int = 0, end: Optional[int] = None) -> None:
+    """Copy-engine push (cp.async.bulk) of ``src[begin:end]`` (whole 16384-element tiles) into every
+    peer of ``table`` - inbox slots (fused exchange) or parameter regions (init / diffusion)."""
+    n = src.numel()
+    _check(
+        lib().p2pfl_gossip_push_bulk(
+            _dev(src), _stream(), _p(src), C.c_uint64(n), C.c_uint64(begin), C.c_uint64(n if end is None else end),
+            C.c_uint32(seq), C.byref(table),
+        )
+    )  # fmt: skip
+    _count()
+
+
+def gossip_push_reduce_bulk(src: torch.Tensor, weight: float, table: PushTable) -> None:
+    """Mode A: ``weight * src`` is ADDED into every peer's fp32 accumulator by the copy engine
+    (cp.reduce.async.bulk); the table's ``flags`` are per-tile arrival counters."""
+    _check(lib().p2pfl_gossip_push_reduce_bulk(_dev(src), _stream(), _p(src), C.c_uint64(src.numel()), C.c_float(weight), C.byref(table)))
+    _count()
+
+
+def gossip_finalize_acc(params, params_bf16, acc, counts, n_senders: int, self_weight: float, timeout_cycles: int = 0, status=None) -> None:
+    """Receiver side of mode A: params = acc + self_weight * params once every sender's tile arrived."""
+    _check(
+        lib().p2pfl_gossip_finalize_acc(
+            _dev(params), _stream(), _p(params), _p(params_bf16), _p(acc), _p(counts), C.c_uint64(params.numel()),
+            C.c_int(n_senders), C.c_float(self_weight), C.c_uint64(timeout_cycles), _p(status),
+        )
+    )  # fmt: skip
+    _count()
+
+
 def tables_to_device(tables: Sequence[C.Structure], device: torch.device) -> torch.Tensor:
     raw = b"".join(bytes(t) for t in tables)
     return torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(device)
