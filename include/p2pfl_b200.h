@@ -210,8 +210,9 @@ int p2pfl_gossip_fused_emulated(int device, void* stream, int n_ranks, float* co
  *              16-byte aligned; overwritten with the weighted average
  *   weights[r] (host array) normalised FedAvg weight of rank r
  *   n          elements per model: a multiple of 8, at most 262144
- *   status_out (nullable, device int32[4 * n_ranks]) per-rank status words,
- *              same meaning as for the reduce kernels
+ *   status_out (nullable; a DEVICE pointer, int32[4 * n_ranks] - it is filled by a
+ *              device-to-device copy on `stream`, a host pointer would fault) per-rank
+ *              status words, same meaning as for the reduce kernels
  *
  * Anything larger (more ranks, bigger models) is refused with a non-zero return
  * and a message in p2pfl_last_error(); use p2pfl_gossip_fused_emulated with inboxes

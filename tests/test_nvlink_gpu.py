@@ -145,3 +145,53 @@ def test_fused_exchange_with_non_trainers():
     stats = _run_federation([f"cuda:{i}" for i in range(ng)], NvlinkMemoryProtocol, rounds=2, train_set=2, n=ng + 1)
     assert all(s["host"] == 0 for s in stats), stats
     assert sum(s["pulled"] for s in stats) > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_fused_kernel_dead_peer_is_aborted_from_the_host():
+    """The real (one launch per GPU) fused kernel with a peer on ANOTHER GPU that never pushes: the
+    kernel has pushed its own tiles and spins on the peer's flags; the host flips the abort word,
+    the kernel ends, reports who was missing, and the snapshot still holds the pre-exchange model."""
+    import time
+
+    from p2pfl_b200 import ops
+    from p2pfl_b200.parallel.arena import DeviceArena
+
+    n = 4 * 16384
+    a = DeviceArena(n, slots=2, tile=16384, wire_bf16=True, device=0)
+    b = DeviceArena(n, slots=2, tile=16384, wire_bf16=True, device=1)  # the peer that stays silent
+    try:
+        ops.rt_enable_peer(0, 1)
+        torch.manual_seed(5)
+        model = torch.randn(n, device="cuda:0")
+        a.params.copy_(model)
+        snap = torch.full_like(model, float("nan"))
+        push = ops.make_push_table([b.slot_ptr(0, 1)], [b.flag_ptr(0, 1)], True)
+        red = ops.make_reduce_table([a.slot_ptr(1, 1)], [a.flag_ptr(1, 1)], [0.5], 0, 0.5, True, True)
+        side = torch.cuda.Stream(device="cuda:0")
+        with torch.cuda.device(0):
+            a.status.zero_()
+            a.abort.zero_()
+            torch.cuda.synchronize(0)
+            with torch.cuda.stream(side):
+                ops.gossip_fused(a.params, None, 16384, 1, push, red, a.abort, 0, a.status, snapshot=snap)  # no device timeout
+                done = torch.cuda.Event()
+                done.record(side)
+            time.sleep(0.05)
+            assert not done.query(), "the kernel must still be waiting for the silent peer"
+            a.abort.fill_(1)  # (default stream: the kernel runs on `side`)
+            t0 = time.time()
+            while not done.query() and time.time() - t0 < 10:
+                time.sleep(0.001)
+            assert done.query(), "the abort word did not release the kernel"
+            torch.cuda.synchronize(0)
+        st = a.status.cpu()
+        assert int(st[0]) == 1 and int(st[2]) == 1  # aborted; table position 0 (the peer) was missing
+        assert torch.equal(snap, model)  # what the host puts back before it falls back to add_model
+        # our own tiles did reach the peer's inbox before the wait
+        torch.cuda.synchronize(1)
+        assert torch.equal(b.slot_tensor(0, 1).to("cuda:0").float(), model.bfloat16().float())
+    finally:
+        a.close()
+        b.close()

@@ -67,9 +67,35 @@ def test_static_exchange_matches_the_allocating_entry_point_twice():
         st2 = status.view(ranks, 4).cpu()
         assert st2[:, 0].sum().item() == 0, "a rank timed out"
         assert (st2[:, 1] > 0).all(), "status words were not written"
+        # and against plain PyTorch: the fp32 weighted sum of the models as they travel (bf16 wire)
+        oracle = sum(w * m.bfloat16().float() for w, m in zip(weights, models))
         for r in range(ranks):
             assert torch.allclose(mine[r], expect[r], atol=1e-5), f"call {call} rank {r}: {(mine[r] - expect[r]).abs().max().item()}"
+            assert torch.allclose(mine[r], oracle, atol=2e-6 * (call + 1), rtol=1e-5), f"call {call} rank {r} vs fp32 oracle"
             assert torch.equal(mine[r], mine[0]), "ranks disagree bit-wise"
+
+
+def test_static_exchange_at_its_limits():
+    """The largest case the built-in scratch holds: 8 ranks x 262144 elements (a whole number of
+    tiles), and 8 ranks with a partial last tile - both against the fp32 PyTorch sum."""
+    from p2pfl_b200 import ops
+
+    lib = ops.lib()
+    lib.p2pfl_last_error.restype = C.c_char_p
+    torch.cuda.set_device(0)
+    for n in (262144, 262144 - 16384 + 8):
+        torch.manual_seed(n)
+        models = [torch.randn(n, device=DEV) for _ in range(8)]
+        weights = [(r + 1) / 36.0 for r in range(8)]
+        mine = [m.clone() for m in models]
+        status = torch.full((32,), -1, dtype=torch.int32, device=DEV)
+        assert _static_exchange(lib, mine, weights, status=status) == 0, lib.p2pfl_last_error()
+        torch.cuda.synchronize()
+        assert status.view(8, 4)[:, 0].sum().item() == 0
+        oracle = sum(w * m.bfloat16().float() for w, m in zip(weights, models))
+        for r in range(8):
+            assert torch.allclose(mine[r], oracle, atol=2e-6, rtol=1e-5), (n, r)
+            assert torch.equal(mine[r], mine[0])
 
 
 def test_static_exchange_refuses_what_does_not_fit():
