@@ -93,3 +93,34 @@ if what in ("all", "gemm"):
         ops.gemm_tn(A, K, B, K, M, N, K, out_bf16=out, ld_bf16=N)
     torch.cuda.synchronize()
     print("gemm ok")
+
+if what == "evidence":
+    # One pass over every kernel family for the per-kernel ncu summaries (profiles/r2/ncu_*.md):
+    # the whole-epoch MLP kernel, the CNN and ResNet steps (GEMM, im2col, BatchNorm, pooling, Adam),
+    # evaluation, FedAvg, the co-located exchange (one cooperative launch) and the copy-engine push.
+    from p2pfl_b200.learning.data import Cifar10FederatedDM  # noqa: E402
+    from p2pfl_b200.models import CNN, ResNet18  # noqa: E402
+    from p2pfl_b200.parallel.arena import emulate_exchange  # noqa: E402
+
+    dm = MnistFederatedDM(0, 1, n_train=1280, n_test=256)
+    lr = B200Learner(MLP(seed=0), dm, "prof", epochs=1, device="cuda:0")
+    lr.fit()
+    lr.fit()
+    print("mlp eval", lr.evaluate())
+    cnn = B200Learner(CNN(seed=0), MnistFederatedDM(0, 1, n_train=256, n_test=64), "prof-cnn", epochs=1, device="cuda:0")
+    cnn.fit()
+    print("cnn eval", cnn.evaluate())
+    rn = B200Learner(ResNet18(seed=0), Cifar10FederatedDM(0, 1, n_train=128, n_test=64, batch_size=64), "prof-rn", epochs=1, device="cuda:0")
+    rn.fit()
+    print("resnet eval", rn.evaluate())
+    n = 11_173_984 // 32 * 32
+    models = [torch.randn(n, device="cuda:0") for _ in range(4)]
+    out = torch.empty(n, device="cuda:0")
+    ops.fedavg_into(models, [0.25] * 4, out, None)
+    emulate_exchange(models, [1, 2, 3, 4])
+    a = DeviceArena(n, slots=2, tile=16384, wire_bf16=True, device=0)
+    b = DeviceArena(n, slots=2, tile=16384, wire_bf16=True, device=0)
+    a.params.copy_(models[0])
+    ops.gossip_push_bulk(a.params, 3, ops.make_push_table([b.slot_ptr(0, 1)], [b.flag_ptr(0, 1)], True))
+    torch.cuda.synchronize()
+    print("evidence ok")
