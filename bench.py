@@ -260,7 +260,10 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     from p2pfl_b200 import ops
     from p2pfl_b200.learning.b200_learner import B200Learner
     from p2pfl_b200.learning.data import MnistFederatedDM
+    from p2pfl_b200 import ops as _ops
     from p2pfl_b200.management.logger import logger
+
+    _ops.thread_uses_cuda()
     from p2pfl_b200.models import MLP
     from p2pfl_b200.node import Node
     from p2pfl_b200.settings import Settings

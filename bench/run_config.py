@@ -79,7 +79,10 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     if world > 1:
         dist.init_process_group("nccl" if on_gpu else "gloo", **({"device_id": torch.device(f"cuda:{local}")} if on_gpu else {}))
 
+    from p2pfl_b200 import ops as _ops
     from p2pfl_b200.management.logger import logger
+
+    _ops.thread_uses_cuda()
     from p2pfl_b200.node import Node
     from p2pfl_b200.settings import Settings
     from p2pfl_b200.utils import wait_convergence

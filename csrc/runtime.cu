@@ -113,6 +113,17 @@ int p2pfl_rt_memset32(int device, void* stream, void* ptr, uint32_t value, uint6
   return -1;
 }
 
+/* Threads of this framework call CUDA while ANOTHER thread may be capturing a graph (several
+ * federated nodes per process, each building its epoch graph on first use).  A thread in CUDA's
+ * default "global" capture mode is refused every potentially unsafe call (cudaMalloc, a device
+ * synchronize, ...) while any capture is running - and the refusal also invalidates that capture.
+ * In thread-local mode a thread is only restricted by captures of its own. */
+int p2pfl_rt_thread_capture_mode_local(void) {
+  cudaStreamCaptureMode mode = cudaStreamCaptureModeThreadLocal;
+  P2PFL_CUDA_OK(cudaThreadExchangeStreamCaptureMode(&mode));
+  return 0;
+}
+
 int p2pfl_rt_sm_clock_khz(int device, int* out_khz) {
   P2PFL_REQUIRE(out_khz != nullptr, "null argument");
   P2PFL_CUDA_OK(cudaDeviceGetAttribute(out_khz, cudaDevAttrClockRate, device));

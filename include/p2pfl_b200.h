@@ -36,6 +36,10 @@ int p2pfl_rt_ipc_close(int device, void* ptr);
 int p2pfl_rt_enable_peer(int device, int peer_device);
 int p2pfl_rt_can_access_peer(int device, int peer_device, int* out_yes);
 int p2pfl_rt_memset32(int device, void* stream, void* ptr, uint32_t value, uint64_t count);
+/* Puts the CALLING thread in CUDA's thread-local stream-capture mode: calls it makes (allocations,
+ * device synchronisation) are no longer refused - nor do they invalidate the capture - while some
+ * other thread of the process captures a graph.  Call once per thread that uses CUDA. */
+int p2pfl_rt_thread_capture_mode_local(void);
 /* peak SM clock in kHz (converts the device-side timeouts, which count SM cycles, from seconds) */
 int p2pfl_rt_sm_clock_khz(int device, int* out_khz);
 int p2pfl_rt_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, uint64_t* total_mem);

@@ -96,6 +96,12 @@ class Gossiper(threading.Thread):
             self._cv.notify()
 
     def run(self) -> None:
+        try:  # this thread sends models, which may stage them on the device
+            from p2pfl_b200 import ops
+
+            ops.thread_uses_cuda()
+        except Exception:
+            pass
         while True:
             with self._cv:
                 while not self._pending and not self._stop_flag:

@@ -557,14 +557,17 @@ class FusedExchange:
         wire_bf16 = arena.geo.wire_bf16
         # host watchdog: flip the abort word if a contributor disappears, somebody cancels or the experiment stops
         t0 = time.time()
+        polls = 0
         while not done.query():
-            gone = [n for n in others if n not in proto.get_neighbors(only_direct=False)]
-            if gone or self.state.round is None or proto.fused_cancelled(rnd) or time.time() - t0 > Settings.AGGREGATION_TIMEOUT:
-                with torch.cuda.stream(proto._abort_stream(learner)):
-                    arena.abort.fill_(1)
-                done.synchronize()
-                break
-            time.sleep(0.0002)
+            polls += 1
+            if polls % 64 == 0:  # the liveness checks take locks and copy dictionaries: not on every poll
+                gone = [n for n in others if n not in proto.get_neighbors(only_direct=False)]
+                if gone or self.state.round is None or proto.fused_cancelled(rnd) or time.time() - t0 > Settings.AGGREGATION_TIMEOUT:
+                    with torch.cuda.stream(proto._abort_stream(learner)):
+                        arena.abort.fill_(1)
+                    done.synchronize()
+                    break
+            time.sleep(0.00003)
         status = arena.status.cpu()
         self.complete = int(status[0]) == 0
         proto.stats["fused_ms"] += began.elapsed_time(done)  # includes the wait for the slowest peer's tiles

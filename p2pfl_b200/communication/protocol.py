@@ -136,6 +136,15 @@ def _deliver_many_sequential(transport: "Transport", targets: List[Any], env: En
     return out
 
 
+def _thread_uses_cuda() -> None:
+    try:
+        from p2pfl_b200 import ops
+
+        ops.thread_uses_cuda()
+    except Exception:
+        pass
+
+
 class _ServerHandle:
     """``protocol._server.stop()`` is reached into by the fault-injection tests
     (reference: test/communication_test.py:195)."""
@@ -498,6 +507,7 @@ class BaseProtocol(CommunicationProtocol):
         """Model message: no dedupe, no relay (reference: grpc_server.py:168-197)."""
         if not self._running:
             return "node not running"
+        _thread_uses_cuda()  # the handler may pull / decode a model on the device
         cmd = self._commands.get(w.cmd)
         if cmd is None:
             return f"Unknown command: {w.cmd}"

@@ -47,6 +47,15 @@ def _default_learner() -> Type:
     return TorchLearner
 
 
+def _thread_uses_cuda() -> None:
+    try:
+        from p2pfl_b200 import ops
+
+        ops.thread_uses_cuda()
+    except Exception:
+        pass
+
+
 class Node:
     def __init__(
         self,
@@ -215,6 +224,7 @@ class Node:
         t.start()
 
     def __start_learning(self, rounds: int, epochs: int) -> None:
+        _thread_uses_cuda()
         workflow = LearningWorkflow()
         self.learning_workflow = workflow
         ctx = LearningContext(

@@ -716,6 +716,22 @@ def rt_ipc_close(device: int, ptr: int) -> None:
     _check(lib().p2pfl_rt_ipc_close(C.c_int(device), C.c_void_p(ptr)))
 
 
+_tls = threading.local()
+
+
+def thread_uses_cuda() -> None:
+    """Once per thread: thread-local stream-capture mode (see ``p2pfl_rt_thread_capture_mode_local``).
+    No-op without the kernel library or without a CUDA device."""
+    if getattr(_tls, "capture_mode_set", False):
+        return
+    _tls.capture_mode_set = True
+    try:
+        if available() and torch.cuda.is_available():
+            lib().p2pfl_rt_thread_capture_mode_local()
+    except Exception:
+        pass
+
+
 _clock_hz: dict = {}
 
 

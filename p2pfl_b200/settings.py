@@ -85,7 +85,7 @@ class Settings:
     """Wire dtype of the device data plane: 'bf16' (inbox mode B) or 'fp32'."""
     DEVICE_TILE_ELEMS: int = 16384
     """Elements per data-plane tile (one arrival flag per tile)."""
-    GIL_SWITCH_INTERVAL: float = 0.0005
+    GIL_SWITCH_INTERVAL: float = float(os.environ.get("P2PFL_GIL_SWITCH_INTERVAL", "0.0005"))
     """``sys.setswitchinterval`` applied when a node starts.  The learning thread shares the
     interpreter with the RPC workers, the gossiper and the heartbeater; with CPython's default
     5 ms a thread returning from a CUDA wait can sit that long before it runs again."""
