@@ -144,8 +144,8 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     def listener(r: int) -> None:
         done_rounds[r] = done_rounds.get(r, 0) + 1
         if done_rounds[r] == n_local and r == W and "t0" not in marks:
-            if on_gpu:
-                torch.cuda.synchronize()
+            # (no device-wide synchronize here: another node of this process may be capturing its
+            # epoch graph, and CUDA refuses a device synchronize while any stream captures)
             marks["t0"] = time.perf_counter()
 
     for n in nodes.values():

@@ -124,6 +124,24 @@ int p2pfl_rt_thread_capture_mode_local(void) {
   return 0;
 }
 
+/* A stream of its own for every learner.  (Streams handed out by a framework's pool are shared
+ * round-robin: with a few dozen federated nodes in one process two learners ended up on ONE stream,
+ * and one's work landed in the other's graph capture.) */
+int p2pfl_rt_stream_create(int device, void** out_stream) {
+  P2PFL_REQUIRE(out_stream != nullptr, "null argument");
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  cudaStream_t s;
+  P2PFL_CUDA_OK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  *out_stream = s;
+  return 0;
+}
+
+int p2pfl_rt_stream_destroy(int device, void* stream) {
+  P2PFL_CUDA_OK(cudaSetDevice(device));
+  P2PFL_CUDA_OK(cudaStreamDestroy(as_stream(stream)));
+  return 0;
+}
+
 int p2pfl_rt_sm_clock_khz(int device, int* out_khz) {
   P2PFL_REQUIRE(out_khz != nullptr, "null argument");
   P2PFL_CUDA_OK(cudaDeviceGetAttribute(out_khz, cudaDevAttrClockRate, device));

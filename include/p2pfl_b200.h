@@ -40,6 +40,9 @@ int p2pfl_rt_memset32(int device, void* stream, void* ptr, uint32_t value, uint6
  * device synchronisation) are no longer refused - nor do they invalidate the capture - while some
  * other thread of the process captures a graph.  Call once per thread that uses CUDA. */
 int p2pfl_rt_thread_capture_mode_local(void);
+/* a non-blocking stream owned by the caller (one per learner: never shared through a pool) */
+int p2pfl_rt_stream_create(int device, void** out_stream);
+int p2pfl_rt_stream_destroy(int device, void* stream);
 /* peak SM clock in kHz (converts the device-side timeouts, which count SM cycles, from seconds) */
 int p2pfl_rt_sm_clock_khz(int device, int* out_khz);
 int p2pfl_rt_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, uint64_t* total_mem);

@@ -40,6 +40,25 @@ from p2pfl_b200.settings import Settings
 
 _capture_lock = threading.Lock()
 
+# Compute streams of the learners: created by the runtime, owned by exactly one live learner at a time,
+# handed to the next learner afterwards and never destroyed (tensors and events of the framework's
+# allocator may still name a stream when the interpreter shuts down).
+_free_streams: Dict[int, List[int]] = {}
+_streams_lock = threading.Lock()
+
+
+def _acquire_stream(device: int) -> int:
+    with _streams_lock:
+        free = _free_streams.setdefault(device, [])
+        if free:
+            return free.pop()
+    return ops.rt_stream_create(device)
+
+
+def _release_stream(device: int, stream: int) -> None:
+    with _streams_lock:
+        _free_streams.setdefault(device, []).append(stream)
+
 
 def _pad8(x: int) -> int:
     return (x + 7) // 8 * 8
@@ -83,7 +102,11 @@ class B200Learner(TorchLearner):
         self.d2h_bytes = 0
         self.kernel_launches_per_epoch = 0
         super().__init__(model, data, self_addr, epochs, device)
-        self.stream = torch.cuda.Stream(device=self.device)
+        # The compute stream captures graphs, so it must be this learner's alone: torch hands its streams
+        # out of a pool of 32 per device, and with a few dozen nodes in one process two learners got the
+        # same one - the work of the first landed inside the capture of the second.
+        self._own_stream = _acquire_stream(self.device.index or 0)
+        self.stream = torch.cuda.ExternalStream(self._own_stream, device=self.device)
         # data-plane copies issued by OTHER threads (inbound pulls) must never touch the
         # compute stream: it may be capturing a graph at that moment
         self.comm_stream = torch.cuda.Stream(device=self.device)
@@ -222,12 +245,23 @@ class B200Learner(TorchLearner):
 
     def close(self) -> None:
         self._graphs = {}
+        self._sync_streams()
         if self.arena is not None:
-            torch.cuda.synchronize(self.device)
             # views into the arena must not outlive it
             self.flat = None
             ArenaPool.release(self.arena)
             self.arena = None
+        own, self._own_stream = getattr(self, "_own_stream", None), None
+        if own:
+            _release_stream(self.device.index or 0, own)  # the next learner of this process may take it
+
+    def _sync_streams(self) -> None:
+        """Wait for this learner's own streams (never ``torch.cuda.synchronize``: CUDA refuses a device-wide
+        synchronize while another node of the process captures a graph)."""
+        for name in ("stream", "comm_stream", "_copy_stream"):
+            st = getattr(self, name, None)
+            if st is not None:
+                st.synchronize()
 
     # ------------------------------------------------------------ parameters
     def export_model(self) -> FlatParams:

@@ -242,13 +242,10 @@ class Node:
         self.live_timings = ctx.timings  # the running experiment's stage timers (read-only for observers)
         try:
             workflow.run(ctx)
-        except Exception as e:
-            if Settings.LOG_LEVEL == "DEBUG":
-                import traceback
+        except Exception:
+            import traceback
 
-                logger.error(self.addr, f"learning thread failed:\n{traceback.format_exc()}")
-            else:
-                logger.error(self.addr, f"learning thread failed: {e!r}")
+            logger.error(self.addr, f"learning thread failed:\n{traceback.format_exc()}")
             self.stop()
         finally:
             self.last_timings = dict(ctx.timings)

@@ -745,6 +745,16 @@ def rt_sm_clock_hz(device: int) -> float:
     return hz
 
 
+def rt_stream_create(device: int) -> int:
+    out = C.c_void_p()
+    _check(lib().p2pfl_rt_stream_create(C.c_int(device), C.byref(out)))
+    return int(out.value)
+
+
+def rt_stream_destroy(device: int, stream: int) -> None:
+    lib().p2pfl_rt_stream_destroy(C.c_int(device), C.c_void_p(stream))
+
+
 def rt_enable_peer(device: int, peer: int) -> None:
     _check(lib().p2pfl_rt_enable_peer(C.c_int(device), C.c_int(peer)))
 

@@ -176,15 +176,19 @@ class DeviceArena:
             return
         geo = self.geo
         nbytes = geo.off_abort + 256 - geo.off_flags
+        # stream-ordered and waited for on that stream only: a device-wide synchronize is refused by
+        # CUDA while any other node of the process captures a graph
         with torch.cuda.device(self.device):
-            torch.cuda.synchronize(self.device)
+            s = torch.cuda.current_stream(self.device)
             tensor_from_ptr(self.base + geo.off_flags, nbytes, torch.uint8, self.device).zero_()
-            torch.cuda.synchronize(self.device)
+            s.synchronize()
 
     def close(self) -> None:
         if not self._closed:
             self._closed = True
-            torch.cuda.synchronize(self.device)
+            # the owner has synchronised the streams that used the arena; here only the caller's stream
+            # (never the whole device: see clear_arrivals)
+            torch.cuda.current_stream(self.device).synchronize()
             self.params = self.outbox = self.status = self.abort = None  # type: ignore[assignment]
             ops.rt_free(self.device, self.base)
 
