@@ -26,6 +26,7 @@ from typing import Any, Callable, Deque, List, Optional, Set, Tuple
 from p2pfl_b200.communication.messages import Message
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.settings import Settings
+from p2pfl_b200.utils.lockcheck import make_condition, make_lock, make_rlock
 
 SendFn = Callable[[str, Any, bool], None]
 
@@ -36,7 +37,7 @@ class Gossiper(threading.Thread):
         self._addr = self_addr
         self._send = send
         self._pending: Deque[Tuple[Message, List[str]]] = collections.deque()
-        self._cv = threading.Condition()
+        self._cv = make_condition("gossiper.queue")
         self._stop_flag = False
         # lazily queued broadcasts wait here (at most BUNDLE_LINGER) for the next ordinary one
         self._lazy: List[Tuple[Message, Any]] = []
@@ -47,7 +48,7 @@ class Gossiper(threading.Thread):
         # duplicate filter: ring + set for O(1) membership
         self._seen_ring: Deque[int] = collections.deque()
         self._seen: Set[int] = set()
-        self._seen_lock = threading.Lock()
+        self._seen_lock = make_lock("gossiper.seen")
 
     # ------------------------------------------------------------ lifecycle
     def stop(self) -> None:

@@ -15,13 +15,14 @@ from typing import Any, Dict, Optional
 from p2pfl_b200.communication.protocol import BaseProtocol, Envelope, Transport
 from p2pfl_b200.communication.messages import Message
 from p2pfl_b200.exceptions import CommunicationError
+from p2pfl_b200.utils.lockcheck import make_condition, make_lock, make_rlock
 
 
 class ServerSingleton:
     """addr -> live endpoint (reference: memory/server_singleton.py:22-43)."""
 
     _endpoints: Dict[str, "MemoryTransport"] = {}
-    _lock = threading.Lock()
+    _lock = make_lock("memory.registry")
     _ids = itertools.count()
 
     @classmethod

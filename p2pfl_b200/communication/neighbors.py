@@ -16,6 +16,7 @@ from dataclasses import dataclass
 from typing import Any, Callable, Dict, Optional
 
 from p2pfl_b200.management.logger import logger
+from p2pfl_b200.utils.lockcheck import make_condition, make_lock, make_rlock
 
 
 @dataclass
@@ -40,7 +41,7 @@ class Neighbors:
         self._close = close_link
         self._on_change = on_change
         self._neis: Dict[str, NeighborEntry] = {}
-        self._lock = threading.RLock()
+        self._lock = make_rlock("neighbors")
 
     def _changed(self) -> None:
         if self._on_change is not None:

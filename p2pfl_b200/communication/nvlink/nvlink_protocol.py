@@ -47,13 +47,14 @@ from p2pfl_b200.management.logger import logger
 from p2pfl_b200.parallel.arena import ArenaGeometry, DeviceArena, PeerArena, tensor_from_ptr
 from p2pfl_b200.parallel.payload import DevicePayload, DeviceRef
 from p2pfl_b200.settings import Settings
+from p2pfl_b200.utils.lockcheck import make_condition, make_lock, make_rlock
 
 _HOST = socket.gethostname()
 _PID = os.getpid()
 
 # arenas of nodes living in THIS process: addr -> DeviceArena
 _local_arenas: Dict[str, DeviceArena] = {}
-_local_lock = threading.Lock()
+_local_lock = make_lock("nvlink.local_arenas")
 
 
 class ArenaInfoCommand(Command):
@@ -109,7 +110,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         super().__init__(transport)
         self._node: Any = None
         self._peers: Dict[str, PeerInfo] = {}
-        self._peers_lock = threading.Lock()
+        self._peers_lock = make_lock("nvlink.peers")
         self._nonce = 0
         self._no_arena: set = set()
         self._my_peerinfo: Optional[PeerInfo] = None
@@ -421,7 +422,7 @@ class _DeviceGroup:
     def __init__(self, expected: List[str]) -> None:
         self.expected = list(expected)
         self.members: Dict[str, Dict[str, Any]] = {}
-        self.cond = threading.Condition()
+        self.cond = make_condition("nvlink.group")
         self.done: Optional[torch.cuda.Event] = None
         self.began: Optional[torch.cuda.Event] = None
         self.failed: Optional[str] = None
@@ -430,7 +431,7 @@ class _DeviceGroup:
 
 
 _groups: Dict[Tuple[int, int], _DeviceGroup] = {}
-_groups_lock = threading.Lock()
+_groups_lock = make_lock("nvlink.groups")
 _group_streams: Dict[int, torch.cuda.Stream] = {}
 
 

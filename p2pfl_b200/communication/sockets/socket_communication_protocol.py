@@ -35,6 +35,7 @@ from p2pfl_b200.communication.messages import Message
 from p2pfl_b200.communication.protocol import BaseProtocol, Envelope, Transport
 from p2pfl_b200.exceptions import CommunicationError
 from p2pfl_b200.settings import Settings
+from p2pfl_b200.utils.lockcheck import make_condition, make_lock, make_rlock
 
 K_HANDSHAKE, K_DISCONNECT, K_MESSAGE, K_WEIGHTS = 1, 2, 3, 4
 _HDR = struct.Struct("<IB")
@@ -70,7 +71,7 @@ class _Link:
     def __init__(self, addr: str, timeout: float) -> None:
         self.addr = addr
         self.sock = _connect(addr, timeout)
-        self.lock = threading.Lock()
+        self.lock = make_lock("socket.link")
 
     def write(self, kind: int, body: bytes) -> None:
         self.sock.sendall(_HDR.pack(len(body), kind) + body)
@@ -97,7 +98,7 @@ class SocketTransport(Transport):
         self._addr = AddressParser(addr).get_parsed_address()
         self._listener: Optional[socket.socket] = None
         self._conns: List[socket.socket] = []
-        self._lock = threading.Lock()
+        self._lock = make_lock("socket.conns")
         self._stopped = threading.Event()
         self._stopped.set()
 

@@ -25,6 +25,7 @@ from typing import Any, Dict, List, Optional, Tuple
 from p2pfl_b200.exceptions import NoModelsToAggregateError
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.settings import Settings
+from p2pfl_b200.utils.lockcheck import make_condition, make_lock, make_rlock
 
 ModelEntry = Tuple[Any, int]
 
@@ -37,7 +38,7 @@ class Aggregator:
         self._train_set: List[str] = []
         self._waiting = False
         self._models: Dict[str, ModelEntry] = {}
-        self._lock = threading.RLock()
+        self._lock = make_rlock("aggregator")
         self._done = threading.Event()
         self._done.set()  # nothing pending
         self._listeners: List[Any] = []

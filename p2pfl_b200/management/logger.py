@@ -34,6 +34,7 @@ from p2pfl_b200.management.metric_storage import (
 )
 from p2pfl_b200.management.node_monitor import NodeMonitor
 from p2pfl_b200.settings import Settings
+from p2pfl_b200.utils.lockcheck import make_condition, make_lock, make_rlock
 
 _GREY, _YELLOW, _RED, _BOLD_RED, _CYAN, _RESET = (
     "\033[90m",
@@ -105,7 +106,7 @@ class Logger:
 
         self._web: Any = None
         self._nodes: Dict[str, Tuple[Optional[NodeMonitor], Any]] = {}
-        self._nodes_lock = threading.Lock()
+        self._nodes_lock = make_lock("logger.nodes")
         self.local_metrics = LocalMetricStorage()
         self.global_metrics = GlobalMetricStorage()
 

@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import threading
 from typing import Dict, List, Tuple, Union
+from p2pfl_b200.utils.lockcheck import make_condition, make_lock, make_rlock
 
 Number = Union[int, float]
 MetricsType = Dict[str, List[Tuple[int, float]]]
@@ -32,7 +33,7 @@ class LocalMetricStorage:
 
     def __init__(self) -> None:
         self._logs: LocalLogsType = {}
-        self._lock = threading.Lock()
+        self._lock = make_lock("metrics")
 
     def add_log(self, exp_name: str, round: int, metric: str, node: str, val: Number, step: int) -> None:
         with self._lock:
@@ -66,7 +67,7 @@ class GlobalMetricStorage:
 
     def __init__(self) -> None:
         self._logs: GlobalLogsType = {}
-        self._lock = threading.Lock()
+        self._lock = make_lock("metrics")
 
     def add_log(self, exp_name: str, round: int, metric: str, node: str, val: Number) -> None:
         with self._lock:

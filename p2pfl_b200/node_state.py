@@ -12,6 +12,7 @@ from __future__ import annotations
 
 import threading
 from typing import Any, Callable, Dict, List, Optional
+from p2pfl_b200.utils.lockcheck import make_condition, make_lock, make_rlock
 
 
 class NodeState:
@@ -44,7 +45,7 @@ class NodeState:
 
         # payloads that arrived before this node could use them (learner not
         # built yet / train set not armed yet); replayed by the stages
-        self.stash_lock = threading.Lock()
+        self.stash_lock = make_lock("state.stash")
         self.pending_init: Optional[Callable[[], None]] = None
         self.pending_models: List[Any] = []
 
@@ -52,8 +53,8 @@ class NodeState:
         self.round_listeners: List[Callable[[int], None]] = []
 
         # one condition for "something changed" - all waits are predicate waits
-        self.changed = threading.Condition()
-        self.start_thread_lock = threading.Lock()
+        self.changed = make_condition("state.changed")
+        self.start_thread_lock = make_lock("state.start")
         # set once this node holds the experiment's initial weights
         self.model_initialized = threading.Event()
         # set when the experiment ended on this node (normally or by stop)
