@@ -15,6 +15,8 @@ import sys
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(ROOT, "p2pfl_b200", "lib", "libp2pfl_b200.so")
+ORACLE_SRC = os.path.join(ROOT, "csrc", "oracle", "oracle.cpp")
+ORACLE_OUT = os.path.join(ROOT, "p2pfl_b200", "lib", "libp2pfl_oracle.so")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 
@@ -30,9 +32,23 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def build_oracle(force: bool = False) -> str:
+    """The plain C++ oracles / timed CPU baselines (csrc/oracle): g++, no CUDA."""
+    if not force and os.path.exists(ORACLE_OUT) and os.path.getmtime(ORACLE_OUT) >= os.path.getmtime(ORACLE_SRC):
+        return ORACLE_OUT
+    os.makedirs(os.path.dirname(ORACLE_OUT), exist_ok=True)
+    res = subprocess.run([shutil.which("g++") or "g++", "-O2", "-std=c++17", "-fPIC", "-shared", ORACLE_SRC, "-o", ORACLE_OUT],
+                         capture_output=True, text=True)  # fmt: skip
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError("g++ failed on the oracle library")
+    return ORACLE_OUT
+
+
 def build(force: bool = False, verbose: bool = False, bringup: bool = False) -> str:
     """``bringup``: compile the per-link clock stamps and the mbarrier-wait trap into the GEMM kernels
     (-DP2PFL_BRINGUP, for experiments with tools/profile_target.py only; never for a measured run)."""
+    build_oracle(force)
     if not force and not needs_build():
         return OUT
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
