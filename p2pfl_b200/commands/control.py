@@ -78,7 +78,7 @@ class NeighborsHintCommand(Command):
         return "neighbors_hint"
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
-        self._on_neighbors(source, list(args))
+        self._on_neighbors(source, list(args), int(round))
 
 
 class StartLearningCommand(Command):
@@ -123,8 +123,10 @@ class ModelInitializedCommand(Command):
         return "model_initialized"
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
-        self._state.nei_status[source] = max(self._state.nei_status.get(source, -1), -1)
-        self._state.notify()
+        st = self._state
+        with st.changed:
+            st.nei_status[source] = max(st.nei_status.get(source, -1), -1)
+            st.changed.notify_all()
 
 
 class VoteTrainSetCommand(Command):
@@ -141,16 +143,18 @@ class VoteTrainSetCommand(Command):
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
         st = self._state
-        # ballots are filed under their round: early ones (a faster node pre-voting for a later
-        # round) are kept until this node gets there; stale ones are dropped
-        if st.round is None or not (st.round <= round <= st.round + 3):
-            logger.debug(st.addr, f"vote from {source} for round {round} ignored (mine: {st.round})")
-            return
         if len(args) % 2:
             raise ValueError("vote_train_set needs (candidate, weight) pairs")
         votes = {args[i]: int(args[i + 1]) for i in range(0, len(args), 2)}
-        st.train_set_votes.setdefault(round, {})[source] = votes
-        st.notify()
+        # ballots are filed under their round: early ones (a faster node pre-voting for a later
+        # round) are kept until this node gets there; stale ones are dropped.  Under the state's
+        # lock: the learning thread switches rounds (and prunes this table) concurrently.
+        with st.changed:
+            if st.round is None or not (st.round <= round <= st.round + 3):
+                logger.debug(st.addr, f"vote from {source} for round {round} ignored (mine: {st.round})")
+                return
+            st.train_set_votes.setdefault(round, {})[source] = votes
+            st.changed.notify_all()
 
 
 class ModelsAggregatedCommand(Command):
@@ -166,11 +170,12 @@ class ModelsAggregatedCommand(Command):
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
         st = self._state
-        if round == st.round:
-            st.models_aggregated[source] = list(args)
-            st.notify()
-        elif st.round is not None and round == st.round + 1:
-            st.early_aggregated[source] = (round, list(args))  # installed when this node reaches that round
+        with st.changed:  # the round may switch between the comparison and the write otherwise
+            if round == st.round:
+                st.models_aggregated[source] = list(args)
+                st.changed.notify_all()
+            elif st.round is not None and round == st.round + 1:
+                st.early_aggregated[source] = (round, list(args))  # installed when this node reaches that round
 
 
 class ModelsReadyCommand(Command):
@@ -187,11 +192,12 @@ class ModelsReadyCommand(Command):
 
     def execute(self, source: str, round: int, *args: Any, **kwargs: Any) -> None:
         st = self._state
-        if st.round is None:
-            return
-        if round in (st.round - 1, st.round, st.round + 1):
-            st.nei_status[source] = max(st.nei_status.get(source, -1), round)
-            st.notify()
+        with st.changed:
+            if st.round is None:
+                return
+            if round in (st.round - 1, st.round, st.round + 1):
+                st.nei_status[source] = max(st.nei_status.get(source, -1), round)
+                st.changed.notify_all()
 
 
 class MetricsCommand(Command):

@@ -25,6 +25,7 @@ from p2pfl_b200.communication.neighbors import Neighbors
 from p2pfl_b200.exceptions import CommunicationError, NeighborNotConnectedError
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.settings import Settings
+from p2pfl_b200.utils.lockcheck import make_lock
 
 Envelope = Union[Message, Weights]
 
@@ -176,11 +177,14 @@ class BaseProtocol(CommunicationProtocol):
         from p2pfl_b200.commands.control import HeartbeatCommand, NeighborsHintCommand
 
         self._extended: set = set()  # peers known to understand this framework's extra commands
-        self.add_command(HeartbeatCommand(self._heartbeater, self._extended.add))
+        self.add_command(HeartbeatCommand(self._heartbeater, self._note_extended))
         self.add_command(NeighborsHintCommand(self.note_direct_neighbors_of))
         self._running = False
         self._terminated = threading.Event()
-        self._direct_of: Dict[str, Any] = {}  # node -> set of its direct neighbours (from its beats)
+        self._direct_of: Dict[str, Any] = {}  # node -> set of its direct neighbours (from its hints)
+        self._direct_of_version: Dict[str, int] = {}
+        self._hint_lock = make_lock("protocol.hint")
+        self._hint_version = 0
         self._temp_links: Dict[str, Any] = {}  # cached links to non-neighbours (create_connection sends)
 
     # ------------------------------------------------------------ lifecycle
@@ -215,6 +219,12 @@ class BaseProtocol(CommunicationProtocol):
         self._on_neighbors_change = fn
 
     def _neighbors_changed(self) -> None:
+        known = self._neighbors.get_all()
+        with self._hint_lock:  # a node that left may come back as a new process: forget its hints
+            for gone in [a for a in self._direct_of if a not in known]:
+                self._direct_of.pop(gone, None)
+                self._direct_of_version.pop(gone, None)
+        self._advertise_direct()
         fn = self._on_neighbors_change
         if fn is not None:
             try:
@@ -403,13 +413,43 @@ class BaseProtocol(CommunicationProtocol):
 
     def _broadcast_beat(self, now: float) -> None:
         self.broadcast(self._beat_msg(now))
-        # tell extended direct neighbours whom I reach directly, so that they need not relay
-        # my broadcasts there (sent point-to-point, ttl 1: a reference node never sees it)
-        direct = list(self._neighbors.get_all(only_direct=True))
-        if Settings.RELAY_PRUNING and len(direct) <= Settings.RELAY_PRUNING_MAX_LIST:
-            hint = self.build_msg("neighbors_hint", sorted(direct))
-            hint.ttl = 1
+        hint = self._hint_msg()
+        if hint is not None:
             self.broadcast(hint)
+
+    def _hint_msg(self) -> Optional[Message]:
+        """``neighbors_hint``: tells extended direct neighbours whom I reach directly, so that they
+        need not relay my broadcasts there (point-to-point, ttl 1: a reference node never sees it)."""
+        with self._hint_lock:
+            # version and list are taken together: of two hints built by two threads the one with the
+            # higher version never carries the older list, whatever order they leave in
+            self._hint_version += 1
+            version = self._hint_version
+            direct = list(self._neighbors.get_all(only_direct=True))
+        if not Settings.RELAY_PRUNING or len(direct) > Settings.RELAY_PRUNING_MAX_LIST:
+            return None
+        hint = self.build_msg("neighbors_hint", sorted(direct), round=version)
+        hint.ttl = 1
+        return hint
+
+    def _note_extended(self, addr: str) -> None:
+        """``addr`` sent a beat carrying this framework's mark."""
+        if addr in self._extended:
+            return
+        self._extended.add(addr)
+        self._advertise_direct()
+
+    def _advertise_direct(self) -> None:
+        """The set of direct neighbours, or of those known to understand the hint, changed: advertise
+        it NOW (queued to the gossiper thread).  Waiting for the next periodic beat left a freshly
+        connected full mesh of 8 nodes flooding every broadcast through every other node for up to
+        ``HEARTBEAT_PERIOD``: 7 copies of each message per receiver, 5 ms per round instead of 0.5
+        (bench/control_plane_bench.py)."""
+        if not self._running or not self._extended:
+            return
+        hint = self._hint_msg()
+        if hint is not None:
+            self._gossiper.add_broadcast(hint, self.broadcast)
 
     def _greet(self, addr: str) -> None:
         """Right after a link comes up: an immediate beat, so both ends learn at once whether
@@ -418,8 +458,12 @@ class BaseProtocol(CommunicationProtocol):
 
         self._gossiper.add_message(self._beat_msg(_time.time()), [addr])
 
-    def note_direct_neighbors_of(self, source: str, names: List[str]) -> None:
-        self._direct_of[source] = set(names)
+    def note_direct_neighbors_of(self, source: str, names: List[str], version: int = -1) -> None:
+        with self._hint_lock:
+            if version >= 0 and version < self._direct_of_version.get(source, -1):
+                return  # an older hint that was overtaken on its way
+            self._direct_of_version[source] = version
+            self._direct_of[source] = set(names)
 
     # ------------------------------------------------------------ neighbours
     def connect(self, addr: str, non_direct: bool = False) -> bool:

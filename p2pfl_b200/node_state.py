@@ -76,47 +76,54 @@ class NodeState:
     def set_experiment(self, exp_name: str, total_rounds: int) -> None:
         """Begin an experiment (reference: node_state.py:83-95).  Unlike the
         reference every per-experiment field is reset here (Q19)."""
-        self.status = "Learning"
-        self.actual_exp_name = exp_name
-        self.total_rounds = total_rounds
-        self.round = 0
-        self.models_aggregated = {}
-        self.early_aggregated = {}
-        self.train_set = []
-        self.train_set_votes = {}
-        self.finished.clear()
-        self.notify()
+        with self.changed:
+            self.status = "Learning"
+            self.actual_exp_name = exp_name
+            self.total_rounds = total_rounds
+            self.round = 0
+            self.models_aggregated = {}
+            self.early_aggregated = {}
+            self.train_set = []
+            self.train_set_votes = {}
+            self.finished.clear()
+            self.changed.notify_all()
 
     def increase_round(self) -> None:
         """Advance one round (reference: node_state.py:97-108)."""
         if self.round is None:
             raise ValueError("round not initialised")
-        self.round += 1
-        self.models_aggregated = {src: args for src, (rnd, args) in self.early_aggregated.items() if rnd == self.round}
-        self.early_aggregated = {}
-        # drop votes of rounds that are over
-        for r in [r for r in self.train_set_votes if r < self.round]:
-            del self.train_set_votes[r]
-        self.notify()
+        # The per-round tables are also written by the message handlers (ballots and notices of
+        # faster peers arrive at any time): both sides hold ``changed`` while they touch them, so the
+        # round switch neither iterates a dictionary that grows under it nor loses a notice filed
+        # between "copy the early ones" and "clear them".
+        with self.changed:
+            self.round += 1
+            self.models_aggregated = {src: args for src, (rnd, args) in self.early_aggregated.items() if rnd == self.round}
+            self.early_aggregated = {}
+            # drop votes of rounds that are over
+            for r in [r for r in self.train_set_votes if r < self.round]:
+                del self.train_set_votes[r]
+            self.changed.notify_all()
         for fn in list(self.round_listeners):
             fn(self.round)
 
     def clear(self) -> None:
         """Back to idle (reference: node_state.py:110-115, plus Q19 full reset)."""
-        self.status = "Idle"
-        self.actual_exp_name = None
-        self.round = None
-        self.total_rounds = None
-        self.models_aggregated = {}
-        self.early_aggregated = {}
-        self.nei_status = {}
-        self.train_set = []
-        self.train_set_votes = {}
-        self.pending_init = None
-        self.pending_models = []
-        self.model_initialized.clear()
-        self.finished.set()
-        self.notify()
+        with self.changed:
+            self.status = "Idle"
+            self.actual_exp_name = None
+            self.round = None
+            self.total_rounds = None
+            self.models_aggregated = {}
+            self.early_aggregated = {}
+            self.nei_status = {}
+            self.train_set = []
+            self.train_set_votes = {}
+            self.pending_init = None
+            self.pending_models = []
+            self.model_initialized.clear()
+            self.finished.set()
+            self.changed.notify_all()
 
     def __repr__(self) -> str:
         return (

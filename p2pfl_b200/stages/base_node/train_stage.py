@@ -51,12 +51,24 @@ class TrainStage(Stage):
             # Device pipeline of the round: evaluation, the epoch(s), validation and the exchange are
             # queued back to back; the host reads their results afterwards.  Between the last training
             # kernel and the exchange kernel there is no host round trip any more.
-            if will_prevote:
-                TrainStage.prevote(ctx)
             t1 = time.time()
             logger.info(st.addr, "training")
             launched = []
-            st.learner.fit(after_launch=lambda: (fused.launch(seq), launched.append(1)))
+
+            def queued() -> None:
+                fused.launch(seq)
+                launched.append(1)
+                # The pre-vote (and what waits in its bundle) leaves NOW, when the whole round is
+                # queued on the device and this thread is about to block on its results: every node
+                # broadcasts at this point of its round, so the seven inbound bundles are handled while
+                # the hosts wait - not while they issue the launches (handlers and launches share the
+                # interpreter: at 8 nodes the launch phase took 0.6 ms longer than alone).
+                if will_prevote:
+                    TrainStage.prevote(ctx)
+
+            st.learner.fit(after_launch=queued)
+            if will_prevote:
+                TrainStage.prevote(ctx)  # no-op when cast above (fit may not have got that far)
             t2 = time.time()
             results = st.learner.evaluate_finish(handle)
             broadcast_metrics(proto, st, results, lazy=True)  # nobody waits on metrics

@@ -75,7 +75,8 @@ class VoteTrainSetStage(Stage):
         k = min(Settings.TRAIN_SET_SIZE, len(candidates))
         picked = random.sample(candidates, k)
         ballot = {c: math.floor(random.randint(0, 1000) / (i + 1)) for i, c in enumerate(picked)}
-        st.train_set_votes.setdefault(rnd, {})[st.addr] = ballot
+        with st.changed:
+            st.train_set_votes.setdefault(rnd, {})[st.addr] = ballot
         flat: List[str] = []
         for c, w in ballot.items():
             flat += [c, str(w)]

@@ -255,6 +255,51 @@ def test_relay_pruning_in_a_clique_and_reach_on_a_line():
             _stop(nodes)
 
 
+@pytest.mark.parametrize("protocol", [InMemoryCommunicationProtocol, SocketCommunicationProtocol])
+def test_direct_neighbours_are_advertised_when_they_change(protocol):
+    """A freshly connected mesh must not flood for a heartbeat period: the list of direct neighbours
+    goes out the moment it (or the set of peers that understand it) changes, versioned so that an
+    overtaken older list cannot replace a newer one."""
+    Settings.HEARTBEAT_PERIOD = 30.0  # the periodic hint never comes within this test
+    Settings.HEARTBEAT_TIMEOUT = 120.0
+    nodes = _nodes(4, protocol)
+    try:
+        for i in range(4):
+            for j in range(i):
+                nodes[i].connect(nodes[j].addr)
+        wait_convergence(nodes, 3, only_direct=True)
+        addrs = {n.addr for n in nodes}
+
+        def settled():
+            return all(
+                n._communication_protocol._direct_of.get(o.addr) == addrs - {o.addr}
+                for n in nodes for o in nodes if o is not n
+            )  # fmt: skip
+
+        deadline = time.time() + 3
+        while not settled() and time.time() < deadline:
+            time.sleep(0.01)
+        assert settled(), [n._communication_protocol._direct_of for n in nodes]
+        # an older hint arriving late is ignored
+        eng = nodes[0]._communication_protocol
+        v = eng._direct_of_version[nodes[1].addr]
+        eng.note_direct_neighbors_of(nodes[1].addr, [], v - 1)
+        assert eng._direct_of[nodes[1].addr] == addrs - {nodes[1].addr}
+        # a peer that leaves is advertised as gone at once, and its own hints are forgotten
+        gone = nodes[3].addr
+        nodes[3].stop()
+        deadline = time.time() + 3
+        while time.time() < deadline and any(
+            gone in n._communication_protocol._direct_of.get(o.addr, ()) for n in nodes[:3] for o in nodes[:3] if o is not n
+        ):  # fmt: skip
+            time.sleep(0.01)
+        for n in nodes[:3]:
+            d = n._communication_protocol._direct_of
+            assert gone not in d and all(gone not in s for s in d.values()), d
+    finally:
+        _stop(nodes)
+
+
 @pytest.mark.parametrize("protocol", PROTOCOLS)
 def test_bookkeeping_broadcasts_are_bundled(protocol):
     """A lazily queued broadcast waits for the next ordinary one; together they reach an extended

@@ -157,3 +157,82 @@ def test_learning_with_a_node_dying_midway(checked_locks):
             x.stop()
     assert checked_locks == [], checked_locks
     assert lockcheck.violations() == [], lockcheck.violations()
+
+
+def test_round_switch_against_inbound_votes_and_notices():
+    """Ballots and ``models_aggregated`` notices of faster peers arrive on handler threads while the
+    learning thread switches rounds (and prunes the same tables).  Found with
+    bench/control_plane_bench.py: one run in ~20 of 8 nodes x 100 rounds died with "dictionary changed
+    size during iteration" in ``increase_round`` and left the other seven waiting for it."""
+    from p2pfl_b200.commands.control import ModelsAggregatedCommand, VoteTrainSetCommand
+    from p2pfl_b200.node_state import NodeState
+
+    st = NodeState("me")
+    st.set_experiment("exp", 10**9)
+    vote, agg = VoteTrainSetCommand(st), ModelsAggregatedCommand(st)
+    stop = threading.Event()
+    errors = []
+
+    def handler(i: int) -> None:
+        try:
+            k = 0
+            while not stop.is_set():
+                r = st.round or 0
+                vote.execute(f"peer{i}", r + 1 + (k % 3), "a", "1", "b", "2")
+                agg.execute(f"peer{i}", r + 1, "a", "b")
+                k += 1
+        except Exception as e:  # pragma: no cover - the failure being tested for
+            errors.append(e)
+
+    import sys
+
+    old_interval = sys.getswitchinterval()
+    sys.setswitchinterval(1e-6)  # switch threads at (nearly) every opportunity
+    threads = [threading.Thread(target=handler, args=(i,), daemon=True) for i in range(4)]
+    for t in threads:
+        t.start()
+    try:
+        t_end = time.time() + 0.5
+        while time.time() < t_end and not errors:
+            st.increase_round()
+    except Exception as e:
+        errors.append(e)
+    finally:
+        stop.set()
+        for t in threads:
+            t.join(5)
+        sys.setswitchinterval(old_interval)
+    assert not errors, errors
+    assert all(r >= st.round for r in st.train_set_votes)  # pruned, and nothing filed behind the switch
+
+
+def test_round_switch_holds_the_lock_the_handlers_take():
+    """The same race, made deterministic: a ballot for a new round is filed by another thread exactly
+    while ``increase_round`` walks the vote table.  With the table walked outside the state's lock the
+    insertion lands mid-iteration (RuntimeError); with it inside, the handler waits for the switch."""
+    from p2pfl_b200.commands.control import VoteTrainSetCommand
+    from p2pfl_b200.node_state import NodeState
+
+    st = NodeState("me")
+    st.set_experiment("exp", 100)
+    st.round = 5
+    vote = VoteTrainSetCommand(st)
+    filed = []
+
+    class PokingDict(dict):
+        def __iter__(self):
+            first = True
+            for k in dict.__iter__(self):
+                yield k
+                if first:
+                    first = False
+                    t = threading.Thread(target=lambda: (vote.execute("peer", st.round + 3, "a", "1"), filed.append(1)), daemon=True)
+                    t.start()
+                    t.join(0.3)  # old code: the ballot is in by now; new code: the handler is blocked
+
+    st.train_set_votes = PokingDict({4: {"x": {}}, 5: {"x": {}}, 6: {"x": {}}})
+    st.increase_round()  # must not raise
+    deadline = time.time() + 5
+    while not filed and time.time() < deadline:
+        time.sleep(0.01)
+    assert filed and sorted(st.train_set_votes) == [6, 9]
