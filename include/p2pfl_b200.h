@@ -43,6 +43,23 @@ int p2pfl_rt_thread_capture_mode_local(void);
 /* a non-blocking stream owned by the caller (one per learner: never shared through a pool) */
 int p2pfl_rt_stream_create(int device, void** out_stream);
 int p2pfl_rt_stream_destroy(int device, void* stream);
+/* Exchange watchdog (csrc/watchdog.cu): blocks the calling thread until `done_event` (recorded behind
+ * an exchange kernel) has completed - polling in native code, so a Python caller holds no interpreter
+ * lock meanwhile.  It returns early with
+ *   P2PFL_WATCH_SLICE      after `slice_s` seconds (<= 0: never), so that the caller can run checks of
+ *                          its own and call again;
+ *   P2PFL_WATCH_CANCELLED  when `*cancel` (host memory, any thread may set it; may be NULL) is non-zero,
+ *   P2PFL_WATCH_TIMEOUT    after `timeout_s` seconds (< 0: never);
+ * in the last two cases it first writes 1 to `*abort_dev` (DEVICE memory: the abort word the kernel
+ * was given; may be NULL) through a stream of its own and waits up to `grace_s` seconds (< 0: forever)
+ * for the kernel to leave.  `*waited_s` (may be NULL) receives the seconds spent in this call.
+ * Negative / other values: error, see p2pfl_last_error(). */
+#define P2PFL_WATCH_DONE 0
+#define P2PFL_WATCH_CANCELLED 1
+#define P2PFL_WATCH_TIMEOUT 2
+#define P2PFL_WATCH_SLICE 3
+int p2pfl_rt_watch(int device, void* done_event, uint32_t* abort_dev, const volatile int32_t* cancel, double timeout_s,
+                   double slice_s, double grace_s, double* waited_s);
 /* peak SM clock in kHz (converts the device-side timeouts, which count SM cycles, from seconds) */
 int p2pfl_rt_sm_clock_khz(int device, int* out_khz);
 int p2pfl_rt_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, uint64_t* total_mem);

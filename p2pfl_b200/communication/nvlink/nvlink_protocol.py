@@ -115,6 +115,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         self._no_arena: set = set()
         self._my_peerinfo: Optional[PeerInfo] = None
         self._cancelled_round = -1  # highest round whose fused exchange somebody called off
+        self._watch_flags: List[Any] = []  # (round, cancel word) of the native waits in progress
         self.add_command(ArenaInfoCommand(self))
         self.add_command(FusedCancelCommand(self))
         # counts, bytes and DEVICE time (CUDA events on the stream that did the work) per path
@@ -318,9 +319,29 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         except Exception as e:
             logger.debug(self.addr, f"fused_cancel not sent: {e}")
 
+    def _watch_begin(self, rnd: int) -> Any:
+        """A cancel word for one native wait (``ops.rt_watch``) on the exchange of round ``rnd``;
+        ``_note_cancel`` sets the words of the rounds it calls off."""
+        import ctypes
+
+        flag = ctypes.c_int32(0)
+        with self._peers_lock:
+            self._watch_flags.append((rnd, flag))
+        if self.fused_cancelled(rnd):  # after registering: a cancellation cannot slip between the two
+            flag.value = 1
+        return flag
+
+    def _watch_end(self, flag: Any) -> None:
+        with self._peers_lock:
+            self._watch_flags = [(r, f) for r, f in self._watch_flags if f is not flag]
+
     def _note_cancel(self, rnd: int) -> None:
         if rnd > self._cancelled_round:
             self._cancelled_round = rnd
+        with self._peers_lock:
+            for r, f in self._watch_flags:  # wake the native watchdogs at once (they poll this word)
+                if r <= rnd:
+                    f.value = 1
         if self._node is not None:
             st = self._node.state
             if st.fused_complete_round == rnd:
@@ -556,19 +577,23 @@ class FusedExchange:
         learner, arena, proto = self.learner, self.learner.arena, self.proto
         me, rnd = self.state.addr, self.state.round
         wire_bf16 = arena.geo.wire_bf16
-        # host watchdog: flip the abort word if a contributor disappears, somebody cancels or the experiment stops
-        t0 = time.time()
-        polls = 0
-        while not done.query():
-            polls += 1
-            if polls % 64 == 0:  # the liveness checks take locks and copy dictionaries: not on every poll
-                gone = [n for n in others if n not in proto.get_neighbors(only_direct=False)]
-                if gone or self.state.round is None or proto.fused_cancelled(rnd) or time.time() - t0 > Settings.AGGREGATION_TIMEOUT:
-                    with torch.cuda.stream(proto._abort_stream(learner)):
-                        arena.abort.fill_(1)
-                    done.synchronize()
+        # Watchdog (native, csrc/watchdog.cu): this thread waits for the kernel without the interpreter
+        # lock; a cancellation (fused_cancel from a peer, any thread) or AGGREGATION_TIMEOUT makes the
+        # watchdog flip the abort word itself.  Every WATCH_SLICE seconds it hands back for the checks
+        # that need the interpreter: a contributor that left the network, an experiment that stopped.
+        cancel = proto._watch_begin(rnd)
+        try:
+            t0 = time.time()
+            while True:
+                left = Settings.AGGREGATION_TIMEOUT - (time.time() - t0)
+                verdict, _ = ops.rt_watch(arena.device, done, arena.abort, cancel, max(0.0, left), Settings.WATCH_SLICE)
+                if verdict != ops.WATCH_SLICE:
                     break
-            time.sleep(0.00003)
+                gone = [n for n in others if n not in proto.get_neighbors(only_direct=False)]
+                if gone or self.state.round is None or proto.fused_cancelled(rnd):
+                    cancel.value = 1
+        finally:
+            proto._watch_end(cancel)
         status = arena.status.cpu()
         self.complete = int(status[0]) == 0
         proto.stats["fused_ms"] += began.elapsed_time(done)  # includes the wait for the slowest peer's tiles
@@ -640,16 +665,6 @@ class FusedExchange:
             done = torch.cuda.Event(enable_timing=True)
             done.record(gs)
         grp.began, grp.done = began, done
-
-
-def _abort_stream(self: NvlinkCommunicationProtocol, learner: Any) -> torch.cuda.Stream:
-    s = getattr(self, "_abort_s", None)
-    if s is None:
-        s = self._abort_s = torch.cuda.Stream(device=learner.device)
-    return s
-
-
-NvlinkCommunicationProtocol._abort_stream = _abort_stream  # type: ignore[attr-defined]
 
 
 class NvlinkSocketProtocol(NvlinkCommunicationProtocol):

@@ -15,7 +15,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 import threading
-from typing import List, Optional, Sequence
+from typing import Any, List, Optional, Sequence, Tuple
 
 import torch
 
@@ -743,6 +743,25 @@ def rt_sm_clock_hz(device: int) -> float:
         _check(lib().p2pfl_rt_sm_clock_khz(C.c_int(device), C.byref(khz)))
         hz = _clock_hz[device] = float(khz.value) * 1e3 if khz.value > 0 else 1.9e9
     return hz
+
+
+WATCH_DONE, WATCH_CANCELLED, WATCH_TIMEOUT, WATCH_SLICE = 0, 1, 2, 3
+
+
+def rt_watch(device: int, done_event: Any, abort_word: Any = None, cancel: Any = None, timeout_s: float = -1.0,
+             slice_s: float = 0.0, grace_s: float = 30.0) -> Tuple[int, float]:  # fmt: skip
+    """Native wait for ``done_event`` (a recorded ``torch.cuda.Event``): see ``p2pfl_rt_watch`` in the
+    header.  ``abort_word``: device int32 tensor; ``cancel``: a ``ctypes.c_int32`` other threads may
+    set.  The interpreter lock is released for the whole call.  Returns (verdict, seconds waited)."""
+    waited = C.c_double(0.0)
+    rc = lib().p2pfl_rt_watch(
+        C.c_int(device), C.c_void_p(int(done_event.cuda_event)), _p(abort_word),
+        C.byref(cancel) if cancel is not None else None, C.c_double(timeout_s), C.c_double(slice_s), C.c_double(grace_s),
+        C.byref(waited),
+    )  # fmt: skip
+    if rc not in (WATCH_DONE, WATCH_CANCELLED, WATCH_TIMEOUT, WATCH_SLICE):
+        _check(rc if rc != 0 else -1)
+    return rc, float(waited.value)
 
 
 def rt_stream_create(device: int) -> int:

@@ -154,6 +154,10 @@ class Settings:
     """Longest a trainer waits for a train-set member's ``arena_info`` before deciding how to
     exchange.  The decision must come out the same on every trainer, so a missing announcement is
     waited for (every node of this framework announces, arena or not), not guessed around."""
+    WATCH_SLICE: float = 0.002
+    """The native exchange watchdog (``p2pfl_rt_watch``) hands back to Python this often, for the
+    liveness checks that need the interpreter (a contributor that left, an experiment that stopped);
+    cancellations and the aggregation timeout are handled inside the native wait."""
     ARENA_INFO_WAIT: float = 2.0
     """Longest a sender waits for the announcement of an extended peer that is still building its
     learner before it falls back to a host payload for that peer."""

@@ -342,6 +342,61 @@ def test_gossip_push_then_reduce_and_timeout(ops):
         b.close()
 
 
+def test_native_watchdog(ops):
+    """``p2pfl_rt_watch`` (csrc/watchdog.cu): returns with the event; on a timeout or a cancel word set
+    by another thread it flips the device abort word itself and the waiting kernel leaves (renormalised
+    result, status says incomplete); a slice hands back while the kernel is still waiting."""
+    import ctypes
+    import threading
+    import time
+
+    from p2pfl_b200.parallel.arena import DeviceArena
+
+    n, tile = 65536, 16384
+    b = DeviceArena(n, slots=2, tile=tile, wire_bf16=True, device=0)
+    try:
+        ev = torch.cuda.Event()
+        ev.record()
+        verdict, _ = ops.rt_watch(0, ev, None, None, 1.0, 0.0)
+        assert verdict == ops.WATCH_DONE
+        budget = int(30 * ops.rt_sm_clock_hz(0))  # the kernel would give up by itself after 30 s
+        for k, mode in enumerate(("timeout", "cancel", "slice")):
+            torch.manual_seed(k)
+            own = torch.randn(n, device=DEV)
+            b.params.copy_(own)
+            b.abort.zero_()
+            b.status.zero_()
+            seq = 5 + 2 * k  # nobody ever pushes for it
+            red = ops.make_reduce_table([b.slot_ptr(0, bank=1)], [b.flag_ptr(0, bank=1)], [0.5], 1, 0.5, True, True)
+            ops.gossip_reduce(b.params, None, tile, seq, red, b.abort, budget, b.status)
+            ev = torch.cuda.Event()
+            ev.record()
+            cancel = ctypes.c_int32(0)
+            t0 = time.time()
+            if mode == "timeout":
+                verdict, waited = ops.rt_watch(0, ev, b.abort, cancel, 0.1, 0.0, 5.0)
+                assert verdict == ops.WATCH_TIMEOUT and 0.09 < waited < 3.0
+            elif mode == "cancel":
+                threading.Timer(0.05, lambda: setattr(cancel, "value", 1)).start()
+                verdict, waited = ops.rt_watch(0, ev, b.abort, cancel, 20.0, 0.0, 5.0)
+                assert verdict == ops.WATCH_CANCELLED and 0.04 < waited < 3.0
+            else:
+                verdict, waited = ops.rt_watch(0, ev, b.abort, cancel, 20.0, 0.01, 5.0)
+                assert verdict == ops.WATCH_SLICE and 0.009 < waited < 1.0
+                assert not ev.query()  # still waiting for its contributor
+                cancel.value = 1
+                verdict, _ = ops.rt_watch(0, ev, b.abort, cancel, 20.0, 0.01, 5.0)
+                assert verdict == ops.WATCH_CANCELLED
+            assert time.time() - t0 < 6.0
+            assert ev.query()
+            torch.cuda.synchronize()
+            assert int(b.abort.item()) == 1 and int(b.status[0].item()) == 1
+            # the missing contributor was dropped and the tile renormalised: the own model (bf16-rounded)
+            assert torch.allclose(b.params, own.to(torch.bfloat16).float(), atol=1e-5)
+    finally:
+        b.close()
+
+
 # ------------------------------------------------- launch-reduction variants
 def test_gemm_grouped_matches_single_launches(ops):
     """A layer's wgrad and dgrad in ONE launch (different shapes, tile widths, epilogues)."""
