@@ -270,6 +270,16 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     from p2pfl_b200.utils import wait_convergence
 
     ops.lib()
+    fp32 = args.dtype == "fp32"
+    if fp32:
+        # precision-parity arm: the eager PyTorch learner of this framework, strict fp32 like the
+        # reference (its Lightning loop, TF32 off) - same control plane, same round, library GEMMs
+        from p2pfl_b200.learning.torch_learner import TorchLearner as Learner
+
+        torch.backends.cuda.matmul.allow_tf32 = False
+        torch.backends.cudnn.allow_tf32 = False
+    else:
+        Learner = B200Learner
     logger.set_level("WARNING")
     Settings.LOG_LEVEL = "WARNING"
     Settings.TRAIN_SET_SIZE = world
@@ -298,7 +308,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
 
     dm = MnistFederatedDM(rank % PARTS, PARTS, batch_size=BATCH, n_train=SAMPLES_POOL, n_test=TEST_POOL, seed=1234 + rank // PARTS)
     n_train, _ = dm.num_samples()
-    node = Node(MLP(seed=rank), dm, address=address, learner=B200Learner, protocol=Proto, device=f"cuda:{local}")
+    node = Node(MLP(seed=rank), dm, address=address, learner=Learner, protocol=Proto, device=f"cuda:{local}")
     node.start()
     if world > 1:
         dist.barrier()
@@ -312,14 +322,19 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     W, K = args.warmup, args.steps
     total_rounds = W + K + 1  # one untimed cool-down round so the K-th boundary is an ordinary one
 
+    def stream_of(lr: Any) -> Any:
+        # the fused learner computes on a stream of its own, the eager one on its thread's current stream
+        return getattr(lr, "stream", None) or torch.cuda.current_stream()
+
     def measure(data_mode: str) -> Dict[str, Any]:
-        node.learner_kwargs["data_mode"] = data_mode
+        if not fp32:
+            node.learner_kwargs["data_mode"] = data_mode
         marks: Dict[str, Any] = {}
         sampler = ClockSampler(local)
 
         def on_round(r: int) -> None:
             # r = number of rounds completed on this node
-            with torch.cuda.stream(node.state.learner.stream):
+            with torch.cuda.stream(stream_of(node.state.learner)):
                 flush.zero_()  # L2 flush between rounds (inputs are smaller than the 126 MB L2)
             if r == W:
                 torch.cuda.synchronize()
@@ -337,7 +352,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
                 marks["e0"].record(torch.cuda.current_stream())
             elif r == W + K:
                 lr = node.state.learner
-                lr.stream.synchronize()
+                stream_of(lr).synchronize()
                 marks["e1"] = torch.cuda.Event(enable_timing=True)
                 marks["e1"].record(torch.cuda.current_stream())
                 torch.cuda.synchronize()
@@ -390,16 +405,17 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         }  # fmt: skip
 
     dev = measure("resident")
-    e2e = measure("stream")
+    # the eager learner has one data path: every batch comes from host memory inside the timed region
+    e2e = dev if fp32 else measure("stream")
 
     # Correctness of what was just timed: after the last round every node holds the same aggregate
     # (all nodes are trainers; the fused exchange sums in train-set order => identical bits), so a
     # checksum of the live parameters must agree across ranks; and the model must have learned.
     lr = node.state.learner
-    with torch.cuda.stream(lr.stream):
+    with torch.cuda.stream(stream_of(lr)):
         flat = lr.flat.double()
         chk = torch.stack([flat.sum(), flat.abs().sum(), (flat * flat).sum()])
-    lr.stream.synchronize()
+    stream_of(lr).synchronize()
     lo, hi = chk.clone(), chk.clone()
     if world > 1:
         dist.all_reduce(lo, op=dist.ReduceOp.MIN)
@@ -429,13 +445,16 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         "higher_is_better": True,
         "scaling": "weak",
         "vs_baseline": None,
-        "dtype": "bf16",
+        "dtype": args.dtype,
         "data": "synthetic",
         "impl": "p2pfl_b200",
         "config": bench_config(world, n_train),
         "arm": {
             "control_plane": "in-memory (1 node)" if world == 1 else f"{args.control} loopback + NVLink device data plane",
             "timing": "CUDA events on the learner's stream, max over ranks",
+            "learner": "TorchLearner: eager PyTorch, strict fp32 (TF32 off), library GEMMs - the precision-parity arm; "
+                       "gpu_launches counts this library's kernels only" if fp32
+                       else "B200Learner: whole-epoch tcgen05 cluster kernel, bf16 operands, fp32 accumulate / master weights / Adam",
         },
         "final": {"test_loss": float(fm_t[0]), "test_accuracy": float(fm_t[1]), "round": fm.get("round"),
                   "param_checksum": [float(v) for v in chk], "ranks_equal": ranks_equal, "bit_identical": bit_identical},
@@ -448,7 +467,8 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
             "h2d_bytes_per_step": e2e["h2d"] / K / world,
             "d2h_bytes_per_step": e2e["d2h"] / K / world,
             "clocks": e2e["clocks"],
-            "note": "per round: train/val/test splits copied from pinned host memory, loss+metric read back",
+            "note": "every batch copied from host memory, loss+metric read back" if fp32
+                    else "per round: train/val/test splits copied from pinned host memory, loss+metric read back",
         },
         "gpu_launches": dev["launches"],
         "wall_ms_per_step": dev["wall_ms"] / K,
@@ -510,6 +530,8 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ref-fast", action="store_true", help="zero the reference's pacing sleeps (not the stock path)")
     ap.add_argument("--timeout", type=float, default=1500.0)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"],
+                    help="own arm: bf16 = the fused learner (product path); fp32 = the eager fp32 learner (precision parity with the reference)")
     ap.add_argument("--control", default="socket", choices=["socket", "grpc"],
                     help="control-plane transport between the ranks (the data plane is NVLink either way)")
     ap.add_argument("--ref-budget", type=float, default=600.0,

@@ -6,17 +6,29 @@ MNIST-shaped MLP family (mlp.py:53-69):
 
 * parameters live in a peer-mappable device arena (fp32 master) with a bf16
   working copy and a bf16 transposed copy of each weight for the dgrad GEMM;
-* every Linear forward / dgrad / wgrad is the tcgen05 GEMM with bias + ReLU +
-  ReLU-mask + bias-gradient fused in its epilogue; by default ONE thread-block
-  cluster walks all of them plus the loss as dependent links of one launch
-  (``ops.gemm_chain(..., cluster=16)``, ``Settings.MLP_CHAIN_CLUSTER``), and
-  Adam over the whole arena (+ bf16 refresh + transposed copies) is the
-  second launch of the step; ``MLP_CHAIN_CLUSTER = 0`` runs one launch per
-  link instead (swap-AB GEMMs, a fused log-softmax + cross-entropy kernel);
+* the 784-256-128-10 MLP at batch 32 (the benchmark's model) trains a WHOLE
+  EPOCH in one launch of the cluster kernel ``ops.mlp_epoch``
+  (csrc/mlp_cluster.cu, ``Settings.MLP_EPOCH_KERNEL``): 16 CTAs keep the bf16
+  weights in shared memory and the fp32 master weights and Adam moments of
+  layer 1 in tensor memory across steps, hand activations to each other
+  through distributed shared memory, and apply Adam where the weight slice
+  lives - 11.7 us per step;
+* other MLP shapes / batch sizes run every Linear forward / dgrad / wgrad as the
+  tcgen05 GEMM with bias + ReLU + ReLU-mask + bias-gradient fused in its
+  epilogue: ONE thread-block cluster walks all of them plus the loss as dependent
+  links of one launch (``ops.gemm_chain(..., cluster=16)``,
+  ``Settings.MLP_CHAIN_CLUSTER``) and Adam over the whole arena (+ bf16 refresh
+  + transposed copies) is the second launch of the step; ``MLP_CHAIN_CLUSTER = 0``
+  runs one launch per link instead (swap-AB GEMMs, a fused log-softmax +
+  cross-entropy kernel);
 * the CNN and ResNet-18 families get their own plans (``b200_cnn.py``,
   ``b200_resnet.py``) behind the same learner;
 * the dataset is resident on the device, shuffled by one gather kernel per
-  epoch, and a whole epoch is ONE CUDA graph launch (no host work per step).
+  epoch, and a whole epoch is ONE CUDA graph launch (no host work per step);
+* a round is a device pipeline: ``evaluate_async`` / ``fit(after_launch=...)`` /
+  ``evaluate_finish`` queue evaluation, the epochs, validation and (through
+  ``after_launch``) the model exchange back to back on the learner's own
+  stream; the host reads the results afterwards.
 
 Models without a fused plan (GPT-2) fall back to eager autograd for forward/backward
 (``TorchLearner``) but keep the arena, so the gossip data plane is identical.

@@ -62,6 +62,9 @@ class TorchLearner(NodeLearner):
         self._optimizer: Optional[torch.optim.Optimizer] = None
         self._interrupt = threading.Event()
         self._round_steps = 0
+        # bytes moved between host and device by this learner (bench.py's end-to-end accounting)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
         if model is not None:
             self.set_model(model)
         self.set_data(data)
@@ -266,8 +269,7 @@ class TorchLearner(NodeLearner):
                 if self._interrupt.is_set():
                     logger.info(self.addr, "fit interrupted")
                     return
-                x = x.to(self.device, non_blocking=True)
-                y = y.to(self.device, non_blocking=True)
+                x, y = self._to_device(x, y)
                 opt.zero_grad(set_to_none=True)
                 with self._autocast():
                     loss = self._loss(self.model(x), y)
@@ -275,6 +277,7 @@ class TorchLearner(NodeLearner):
                 opt.step()
                 if step % self.LOG_EVERY == 0:
                     logger.log_metric(self.addr, "train_loss", float(loss.detach()), step=step)
+                    self.d2h_bytes += 4
                 step += 1
             # per-epoch validation, as Lightning does for the reference (mlp.py:82-91)
             val = self._score(self.data.val_dataloader()) if hasattr(self.data, "val_dataloader") else None
@@ -295,8 +298,7 @@ class TorchLearner(NodeLearner):
         correct = torch.zeros((), device=self.device)
         count = 0
         for x, y in loader:
-            x = x.to(self.device, non_blocking=True)
-            y = y.to(self.device, non_blocking=True)
+            x, y = self._to_device(x, y)
             with self._autocast():
                 logits = self.model(x)
             if logits.dim() == 3:
@@ -306,7 +308,13 @@ class TorchLearner(NodeLearner):
             count += y.numel()
         if count == 0:
             return None
+        self.d2h_bytes += 8
         return float(loss_sum) / count, float(correct) / count
+
+    def _to_device(self, x: torch.Tensor, y: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        if x.device != self.device:
+            self.h2d_bytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+        return x.to(self.device, non_blocking=True), y.to(self.device, non_blocking=True)
 
     def evaluate(self) -> Dict[str, float]:
         if self.epochs <= 0 or self.model is None:
