@@ -274,7 +274,10 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     if fp32:
         # precision-parity arm: the eager PyTorch learner of this framework, strict fp32 like the
         # reference (its Lightning loop, TF32 off) - same control plane, same round, library GEMMs
-        from p2pfl_b200.learning.torch_learner import TorchLearner as Learner
+        if args.eager:
+            from p2pfl_b200.learning.torch_learner import TorchLearner as Learner
+        else:  # same operators and precision, one CUDA graph replay per step instead of ~30 launches
+            from p2pfl_b200.learning.graphed_learner import GraphedTorchLearner as Learner
 
         torch.backends.cuda.matmul.allow_tf32 = False
         torch.backends.cudnn.allow_tf32 = False
@@ -327,8 +330,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         return getattr(lr, "stream", None) or torch.cuda.current_stream()
 
     def measure(data_mode: str) -> Dict[str, Any]:
-        if not fp32:
-            node.learner_kwargs["data_mode"] = data_mode
+        node.learner_kwargs["data_mode"] = data_mode  # (ignored by learners without the parameter)
         marks: Dict[str, Any] = {}
         sampler = ClockSampler(local)
 
@@ -406,7 +408,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
 
     dev = measure("resident")
     # the eager learner has one data path: every batch comes from host memory inside the timed region
-    e2e = dev if fp32 else measure("stream")
+    e2e = dev if (fp32 and args.eager) else measure("stream")
 
     # Correctness of what was just timed: after the last round every node holds the same aggregate
     # (all nodes are trainers; the fused exchange sums in train-set order => identical bits), so a
@@ -452,8 +454,8 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         "arm": {
             "control_plane": "in-memory (1 node)" if world == 1 else f"{args.control} loopback + NVLink device data plane",
             "timing": "CUDA events on the learner's stream, max over ranks",
-            "learner": "TorchLearner: eager PyTorch, strict fp32 (TF32 off), library GEMMs - the precision-parity arm; "
-                       "gpu_launches counts this library's kernels only" if fp32
+            "learner": ("TorchLearner: eager PyTorch" if args.eager else "GraphedTorchLearner: PyTorch operators, one CUDA-graph replay per step")
+                       + ", strict fp32 (TF32 off), library GEMMs - the precision-parity arm; gpu_launches counts this library's kernels only" if fp32
                        else "B200Learner: whole-epoch tcgen05 cluster kernel, bf16 operands, fp32 accumulate / master weights / Adam",
         },
         "final": {"test_loss": float(fm_t[0]), "test_accuracy": float(fm_t[1]), "round": fm.get("round"),
@@ -467,7 +469,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
             "h2d_bytes_per_step": e2e["h2d"] / K / world,
             "d2h_bytes_per_step": e2e["d2h"] / K / world,
             "clocks": e2e["clocks"],
-            "note": "every batch copied from host memory, loss+metric read back" if fp32
+            "note": "every batch copied from host memory, loss+metric read back" if (fp32 and args.eager)
                     else "per round: train/val/test splits copied from pinned host memory, loss+metric read back",
         },
         "gpu_launches": dev["launches"],
@@ -534,6 +536,7 @@ def main() -> None:
                     help="own arm: bf16 = the fused learner (product path); fp32 = the eager fp32 learner (precision parity with the reference)")
     ap.add_argument("--control", default="socket", choices=["socket", "grpc"],
                     help="control-plane transport between the ranks (the data plane is NVLink either way)")
+    ap.add_argument("--eager", action="store_true", help="with --dtype fp32: the plain eager learner instead of the graphed one")
     ap.add_argument("--ref-budget", type=float, default=600.0,
                     help="reference arm: seconds after which the timed region is closed at the last finished round")
     args = ap.parse_args()

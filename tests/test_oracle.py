@@ -58,7 +58,7 @@ def test_kernels_agree_with_the_cpp_oracles(oracle):
     B = (torch.randn(80, 256) / 8).bfloat16()
     bias = torch.randn(80)
     out = torch.full((96, 80), float("nan"), device=dev)
-    ops.gemm_tn(A.to(dev), 256, B.to(dev), 256, 96, 80, 256, bias=bias.to(dev), relu=True, out_f32=out, ld_f32=80)
+    ops.gemm_tn(A.to(dev), 256, B.to(dev), 256, 96, 80, 256, bias=bias.to(dev), bias_per_row=False, relu=True, out_f32=out, ld_f32=80)
     torch.cuda.synchronize()
     assert torch.allclose(out.cpu(), oracle.gemm_tn(A.float(), B.float(), bias, relu=True), atol=2e-3, rtol=1e-3)
     # FedAvg
