@@ -263,6 +263,7 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     from p2pfl_b200 import ops as _ops
     from p2pfl_b200.management.logger import logger
 
+    _ops.set_home_device(local)  # one process per GPU: every thread of this process works on it
     _ops.thread_uses_cuda()
     from p2pfl_b200.models import MLP
     from p2pfl_b200.node import Node
@@ -283,8 +284,9 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         torch.backends.cudnn.allow_tf32 = False
     else:
         Learner = B200Learner
-    logger.set_level("WARNING")
-    Settings.LOG_LEVEL = "WARNING"
+    level = os.environ.get("P2PFL_BENCH_LOG", "WARNING")  # DEBUG / INFO while chasing a problem
+    logger.set_level(level)
+    Settings.LOG_LEVEL = level
     Settings.TRAIN_SET_SIZE = world
     Settings.DEVICE_INBOX_SLOTS = max(world, 2)
     Settings.GOSSIP_MODELS_PERIOD = 0.05

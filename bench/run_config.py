@@ -82,6 +82,8 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
     from p2pfl_b200 import ops as _ops
     from p2pfl_b200.management.logger import logger
 
+    if on_gpu:
+        _ops.set_home_device(local)
     _ops.thread_uses_cuda()
     from p2pfl_b200.node import Node
     from p2pfl_b200.settings import Settings

@@ -10,7 +10,7 @@ from __future__ import annotations
 from typing import Any, Callable, List, Optional
 
 from p2pfl_b200.commands.command import Command
-from p2pfl_b200.exceptions import DecodingParamsError, ModelNotMatchingError
+from p2pfl_b200.exceptions import DecodingParamsError, ModelNotMatchingError, PayloadUnavailableError
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.node_state import NodeState
 
@@ -61,6 +61,11 @@ class InitModelCommand(Command):
             return
         try:
             learner.set_parameters(_decode_from(learner, weights, source))
+        except PayloadUnavailableError as e:
+            # not a bad model: device memory this node cannot read (yet).  Dropped; the initiator's
+            # gossip loop offers the weights again until this node announces ``model_initialized``.
+            logger.warning(st.addr, f"initial model from {source} not readable yet ({e}); waiting for the next offer")
+            return
         except (DecodingParamsError, ModelNotMatchingError) as e:
             logger.error(st.addr, f"initial model unusable ({e!r}); stopping node")
             self._stop()
@@ -142,6 +147,9 @@ class AddModelCommand(Command):
             model = _decode_from(learner, weights, source)
             learner.check_parameters(model)
             held = self._aggregator.add_model(model, list(contributors), int(weight))
+        except PayloadUnavailableError as e:
+            logger.warning(st.addr, f"model from {source} not readable here ({e}); dropped, the sender will offer it again")
+            return
         except (DecodingParamsError, ModelNotMatchingError) as e:
             logger.error(st.addr, f"received model unusable ({e!r}); stopping node")
             self._stop()

@@ -116,6 +116,7 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         self._my_peerinfo: Optional[PeerInfo] = None
         self._cancelled_round = -1  # highest round whose fused exchange somebody called off
         self._watch_flags: List[Any] = []  # (round, cancel word) of the native waits in progress
+        self._announced_to: set = set()  # peers that certainly hold this node's current arena_info
         self.add_command(ArenaInfoCommand(self))
         self.add_command(FusedCancelCommand(self))
         # counts, bytes and DEVICE time (CUDA events on the stream that did the work) per path
@@ -163,7 +164,21 @@ class NvlinkCommunicationProtocol(BaseProtocol):
                     str(int(bool(Settings.FUSED_EXCHANGE)))]  # fmt: skip
         self._my_info = args
         self._my_peerinfo = PeerInfo(args)
+        # who certainly has this announcement: the extended direct neighbours of this moment (the
+        # broadcast is synchronous).  Anybody else is sent a copy right before the first device
+        # reference that needs it (``_lower_payload``), on the same ordered link.
+        direct = self._neighbors.get_all(only_direct=True)
+        self._announced_to = {n for n in direct if n in self._extended}
         self.broadcast(self.build_msg("arena_info", args))
+
+    def _note_extended(self, addr: str) -> None:
+        """A peer showed this framework's mark only now: an ``arena_info`` broadcast before that moment
+        skipped it (extended commands go to extended peers only), so it gets its copy here."""
+        fresh = addr not in self._extended
+        super()._note_extended(addr)
+        args = getattr(self, "_my_info", None)
+        if fresh and args is not None and self._running:
+            self._gossiper.add_message(self.build_msg("arena_info", args), [addr])
 
     def _on_arena_info(self, source: str, args: List[str]) -> None:
         info = PeerInfo(args)
@@ -246,6 +261,13 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         if not reachable:
             self.stats["host"] += 1
             return Weights(w.source, w.cmd, w.round, learner.encode_parameters(params=payload.params), w.contributors, w.weight)
+        if nei not in self._announced_to:
+            # the receiver resolves the reference against MY announcement: make sure it has one (it may
+            # have shown up as an extended peer after the broadcast, or be reachable only indirectly)
+            self._announced_to.add(nei)
+            note = self.build_msg("arena_info", self._my_info)
+            note.ttl = 1
+            super().send(nei, note, True)
         flat = payload.params.flat
         if flat.data_ptr() == arena.params.data_ptr():
             region = "params"
@@ -286,7 +308,14 @@ class NvlinkCommunicationProtocol(BaseProtocol):
             raise DecodingParamsError(f"device reference of {ref.addr} arrived in a message from {source}")
         peer = self._map_peer(ref.addr)
         if peer is None:
-            raise RuntimeError(f"arena of {ref.addr} is not mapped")
+            # Typically the reference overtook its sender's arena_info (which goes out when the sender
+            # learns that this node speaks the extended commands).  No waiting here: with one stream
+            # socket per neighbour the announcement queues up BEHIND the very message this thread is
+            # handling.  The payload is reported as unavailable, the command drops it, and the
+            # sender's gossip loop offers the model again a period later.
+            from p2pfl_b200.exceptions import PayloadUnavailableError
+
+            raise PayloadUnavailableError(f"arena of {ref.addr} is not mapped here")
         if int(ref.n) != learner.layout.total or int(ref.n) != peer.geo.n:
             raise DecodingParamsError(f"device reference has {ref.n} elements, the layout has {learner.layout.total}")
         dev = learner.arena.device

@@ -45,3 +45,9 @@ class ArenaError(Exception):
 
 class ExtensionMissingError(RuntimeError):
     """The in-tree CUDA extension is required on this path and is not built."""
+
+
+class PayloadUnavailableError(RuntimeError):
+    """A model payload that names device memory cannot be read from here (yet): the sender's arena is
+    not known or not mappable.  Transient from the receiver's point of view - the message is dropped,
+    the sender's gossip loop offers the model again - unlike a payload that decodes to a wrong model."""

@@ -719,14 +719,40 @@ def rt_ipc_close(device: int, ptr: int) -> None:
 _tls = threading.local()
 
 
+_home_device: Optional[int] = None
+
+
+def set_home_device(device: Optional[int]) -> None:
+    """The GPU of this PROCESS (one process per GPU): threads of the framework make it their current
+    device before their first CUDA call.  A new thread's current device is 0; its first runtime call
+    then builds a context on GPU 0 - about 200 ms and half a gigabyte on every other rank, during which
+    that thread (the gossiper that should deliver the greeting beat, the handler that should stash the
+    initial model) is stuck.  Defaults to ``LOCAL_RANK`` when a launcher sets it."""
+    global _home_device
+    _home_device = device
+
+
+def home_device() -> Optional[int]:
+    if _home_device is not None:
+        return _home_device
+    try:
+        return int(os.environ["LOCAL_RANK"])
+    except (KeyError, ValueError):
+        return None
+
+
 def thread_uses_cuda() -> None:
-    """Once per thread: thread-local stream-capture mode (see ``p2pfl_rt_thread_capture_mode_local``).
+    """Once per thread: current device = the process's home device (if it has one), and thread-local
+    stream-capture mode (see ``p2pfl_rt_thread_capture_mode_local``).
     No-op without the kernel library or without a CUDA device."""
     if getattr(_tls, "capture_mode_set", False):
         return
     _tls.capture_mode_set = True
     try:
         if available() and torch.cuda.is_available():
+            dev = home_device()
+            if dev is not None and 0 <= dev < torch.cuda.device_count():
+                torch.cuda.set_device(dev)
             lib().p2pfl_rt_thread_capture_mode_local()
     except Exception:
         pass
