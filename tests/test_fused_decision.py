@@ -101,3 +101,71 @@ def test_a_local_mapping_failure_is_announced_and_a_cancellation_is_honoured():
     st2.fused_complete_round = 1
     q._commands["fused_cancel"].execute("a", 1)
     assert st2.fused_complete_round is None
+
+
+def test_arena_announcement_reaches_a_peer_before_the_first_device_reference():
+    """An ``arena_info`` broadcast skips peers not yet known to speak the extended commands (found on
+    two GPUs: rank 1's greeting beat was 200 ms late, rank 0 announced meanwhile, and the first device
+    reference rank 1 received named an arena it had never heard of).  Whatever the timing: the sender
+    delivers its announcement ahead of the first reference on the same link, and re-announces to a peer
+    that shows the mark later."""
+    import torch
+
+    from p2pfl_b200.commands.command import Command
+    from p2pfl_b200.communication.nvlink import NvlinkSocketProtocol
+    from p2pfl_b200.learning.params import FlatParams
+    from p2pfl_b200.parallel.payload import DevicePayload, DeviceRef
+
+    def learner_for(tag):
+        params = torch.zeros(GEO.n)
+        arena = SimpleNamespace(geo=GEO, device=0, params=params, outbox=torch.zeros(GEO.n), ipc_handle=lambda: bytes([tag]) * 64)
+        return SimpleNamespace(arena=arena, layout=SimpleNamespace(hash="abc", total=GEO.n), get_num_samples=lambda: (100, 10), flat=params)
+
+    a, b = NvlinkSocketProtocol("127.0.0.1"), NvlinkSocketProtocol("127.0.0.1")
+    arrivals = []
+
+    class Init(Command):
+        @staticmethod
+        def get_name():
+            return "init_model"
+
+        def execute(self, source, round, *args, weights=None, **kw):
+            arrivals.append(("init_model", DeviceRef.is_ref(weights), source in b._peers))
+
+    for p in (a, b):
+        p.bind_node(SimpleNamespace(state=NodeState(p.addr)))
+    b.add_command(Init())
+    real_info = b._on_arena_info
+    b._on_arena_info = lambda src, args: (arrivals.append(("arena_info", src)), real_info(src, args))[1]  # type: ignore[method-assign]
+    a.start()
+    b.start()
+    try:
+        assert b.connect(a.addr)
+        deadline = time.time() + 5
+        while not (b.addr in a._extended and a.addr in b._extended) and time.time() < deadline:
+            time.sleep(0.01)
+        la, lb = learner_for(1), learner_for(2)
+        a._extended.discard(b.addr)  # "b's greeting beat has not arrived yet"
+        a.publish_arena(la)
+        time.sleep(0.1)
+        assert a.addr not in b._peers and not arrivals  # the broadcast skipped b
+        a._extended.add(b.addr)
+        b.publish_arena(lb)  # a learns that b has an arena -> it will send references
+        assert b.addr in a._peers
+        payload = DevicePayload(FlatParams(la.flat, la.layout, {}), la)
+        a.send(b.addr, a.build_weights("init_model", 0, payload))
+        assert arrivals == [("arena_info", a.addr), ("init_model", True, True)], arrivals
+        # a second reference does not repeat the announcement
+        a.send(b.addr, a.build_weights("init_model", 0, payload))
+        assert [x[0] for x in arrivals] == ["arena_info", "init_model", "init_model"]
+        # a peer that shows the mark after the announcement gets its copy
+        arrivals.clear()
+        a._extended.discard(b.addr)
+        a._note_extended(b.addr)
+        deadline = time.time() + 5
+        while not arrivals and time.time() < deadline:
+            time.sleep(0.01)
+        assert arrivals == [("arena_info", a.addr)]
+    finally:
+        a.stop()
+        b.stop()
