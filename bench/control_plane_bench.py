@@ -41,7 +41,7 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
 
     logger.set_level("WARNING")
     Settings.LOG_LEVEL = "WARNING"
-    Settings.TRAIN_SET_SIZE = n
+    Settings.TRAIN_SET_SIZE = args.train_set or n
     if args.no_advertise:  # A/B: neighbour lists travel with the periodic beat only (the behaviour before the fix)
         from p2pfl_b200.communication.protocol import BaseProtocol
 
@@ -61,6 +61,7 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
 
         def __init__(self, state: Any, train_set: List[str]) -> None:
             self.state, self.train_set = state, train_set
+            self.members = [int(a.rsplit(":", 1)[1]) - port0 for a in train_set]
             self.seq = 0
 
         def launch(self, seq: int) -> None:
@@ -68,7 +69,7 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
             counters[rank] = self.seq  # "my tiles are on their way"
 
         def finish(self) -> Optional[Tuple[List[str], int]]:
-            while min(counters[:n]) < self.seq:  # the kernel's wait for every peer's arrival flags
+            while min(counters[m] for m in self.members) < self.seq:  # the kernel's wait for every peer's arrival flags
                 time.sleep(args.poll_us * 1e-6)
             return list(self.train_set), 100 * len(self.train_set)
 
@@ -94,7 +95,7 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
                 waits["handle"].append((time.perf_counter() - t) * 1e3)
 
         def plan_fused_exchange(self, state: Any, learner: Any) -> Any:
-            if len(state.train_set) < 2:
+            if len(state.train_set) < 2 or args.no_fused:
                 return None
             state_seq_base[0] = state.seq_base
             return EmuFused(state, sorted(state.train_set))
@@ -117,7 +118,9 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
             return pickle.dumps([self.flat.numpy()])
 
         def decode_parameters(self, data: Any) -> Any:
-            return self.flat
+            import pickle
+
+            return {"w": torch.from_numpy(pickle.loads(data)[0])}
 
         def check_parameters(self, params: Any) -> None: ...
         def set_parameters(self, params: Any) -> None: ...
@@ -273,6 +276,8 @@ def main() -> None:
     ap.add_argument("--settle", type=float, default=0.0, help="seconds between the last connect and the start of learning")
     ap.add_argument("--poll-us", type=float, default=30.0, help="sleep between two polls of the emulated exchange")
     ap.add_argument("--stuck-after", type=float, default=40.0, help="dump every rank's state if the run has not finished by then")
+    ap.add_argument("--no-fused", action="store_true", help="exchange models through add_model messages (the host path)")
+    ap.add_argument("--train-set", type=int, default=0, help="TRAIN_SET_SIZE (default: every node trains)")
     ap.add_argument("--no-advertise", action="store_true", help="A/B: do not advertise direct neighbours on change")
     ap.add_argument("--profile", action="store_true")
     args = ap.parse_args()
