@@ -342,10 +342,13 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
                 flush.zero_()  # L2 flush between rounds (inputs are smaller than the 126 MB L2)
             if r == W:
                 torch.cuda.synchronize()
+                # before the barrier: starting the sampler (NVML initialisation, a thread) takes 5-15 ms and
+                # differs per rank; started after it, the fastest rank's timed region began with a wait for
+                # the slowest rank's sampler (rank intervals of 2.98-3.81 ms per round in one 8-GPU run)
+                sampler.start()
                 if world > 1:
                     dist.barrier()
                 torch.cuda.synchronize()
-                sampler.start()
                 marks["launch0"] = ops.launch_count()
                 lr = node.state.learner
                 marks["h2d0"], marks["d2h0"] = lr.h2d_bytes, lr.d2h_bytes
