@@ -261,11 +261,12 @@ class NvlinkCommunicationProtocol(BaseProtocol):
         if not reachable:
             self.stats["host"] += 1
             return Weights(w.source, w.cmd, w.round, learner.encode_parameters(params=payload.params), w.contributors, w.weight)
-        if nei not in self._announced_to:
+        mine = getattr(self, "_my_info", None)
+        if mine is not None and nei not in self._announced_to:
             # the receiver resolves the reference against MY announcement: make sure it has one (it may
             # have shown up as an extended peer after the broadcast, or be reachable only indirectly)
             self._announced_to.add(nei)
-            note = self.build_msg("arena_info", self._my_info)
+            note = self.build_msg("arena_info", mine)
             note.ttl = 1
             super().send(nei, note, True)
         flat = payload.params.flat
