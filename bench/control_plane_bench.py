@@ -1,17 +1,19 @@
 #!/usr/bin/env python
 """Host-side cost of a federated round, measured WITHOUT a GPU.
 
-One process per node (as on the 8-GPU box), the real node / stage machine / socket control plane, and
-an emulated device: ``fit`` sleeps for the device time of the round (the GIL is released, as it is
-while the host waits on a CUDA event) and the fused exchange is a counter per rank in shared memory
-that every rank waits on (what the exchange kernel's arrival flags do).  Round time minus the emulated
-device time is what the Python control plane costs per round - the quantity that bounds weak scaling
-of ``bench.py`` at 8 GPUs.
+Real nodes, stage machine and socket control plane - one process per "GPU", ``--per-proc`` nodes in
+each - and an emulated device: ``fit`` sleeps for the device time of the round (the GIL is released,
+as it is while the host waits on a CUDA event) and the fused exchange is a counter per node in shared
+memory that every trainer waits on (what the exchange kernel's arrival flags do).  Round time minus the
+emulated device time is what the Python control plane costs per round - the quantity that bounds weak
+scaling of ``bench.py`` at 8 GPUs and the rounds/s of the 64-node configuration.
 
-    python bench/control_plane_bench.py --nodes 8 --rounds 60 --device-ms 2.6 [--profile]
+    python bench/control_plane_bench.py --nodes 8 --rounds 60 --device-ms 2.6            # bench.py at 8 GPUs
+    python bench/control_plane_bench.py --nodes 32 --per-proc 4 --topology line --train-set 8   # config 4, scaled down
 
-Prints one JSON line: ms per round (max over ranks), the overhead over the emulated device time and,
-with ``--profile``, rank 0's hottest functions (all threads).
+Prints one JSON line: ms per round (max over the processes' first nodes), the overhead over the
+emulated device time, messages handled per round and node, wait-time percentiles, and the steal time of
+the run (a virtual machine that loses its CPUs makes every number here meaningless: keep runs with low steal).
 """
 
 from __future__ import annotations
@@ -28,24 +30,31 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, out: Any) -> None:
+def _worker(proc: int, n: int, args: Any, counters: Any, gate: Any, out: Any) -> None:
+    import threading
+
     import torch
 
     torch.set_num_threads(1)
     from p2pfl_b200.communication.sockets import SocketCommunicationProtocol
+    from p2pfl_b200.communication.sockets.socket_communication_protocol import SocketTransport
     from p2pfl_b200.learning.learner import NodeLearner
     from p2pfl_b200.management.logger import logger
     from p2pfl_b200.node import Node
     from p2pfl_b200.settings import Settings
+    from p2pfl_b200.stages.base_node.vote_train_set_stage import VoteTrainSetStage
     from p2pfl_b200.utils import wait_convergence
 
     logger.set_level("WARNING")
     Settings.LOG_LEVEL = "WARNING"
     Settings.TRAIN_SET_SIZE = args.train_set or n
+    Settings.TTL = max(10, n)
     if args.no_advertise:  # A/B: neighbour lists travel with the periodic beat only (the behaviour before the fix)
         from p2pfl_b200.communication.protocol import BaseProtocol
 
         BaseProtocol._advertise_direct = lambda self: None  # type: ignore[method-assign]
+    if args.flood_status:  # A/B: models_ready / model_initialized flooded network-wide (the reference's way)
+        Settings.DIRECT_ROUND_STATUS = False
     Settings.GOSSIP_MODELS_PERIOD = 0.05
     Settings.GOSSIP_PERIOD = 0.0
     Settings.WAIT_HEARTBEATS_CONVERGENCE = 0.2
@@ -55,38 +64,46 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
     Settings.AGGREGATION_TIMEOUT = 60.0
     Settings.VOTE_TIMEOUT = 60.0
     device_s = args.device_ms / 1e3
+    port0, k = args.port, args.per_proc
+    mine = list(range(proc * k, min(n, proc * k + k)))
+    waits: Dict[str, List[float]] = {"vote": [], "finish": [], "handle": [], "deliver_many": []}
+    counts: Dict[str, int] = {}
+
+    def index_of(addr: str) -> int:
+        return int(addr.rsplit(":", 1)[1]) - port0
 
     class EmuFused:
         can_prelaunch = True
 
         def __init__(self, state: Any, train_set: List[str]) -> None:
             self.state, self.train_set = state, train_set
-            self.members = [int(a.rsplit(":", 1)[1]) - port0 for a in train_set]
+            self.me = index_of(state.addr)
+            self.members = [index_of(a) for a in train_set]
             self.seq = 0
 
         def launch(self, seq: int) -> None:
-            self.seq = seq - state_seq_base[0]
-            counters[rank] = self.seq  # "my tiles are on their way"
+            self.seq = seq - self.state.seq_base
+            counters[self.me] = self.seq  # "my tiles are on their way"
 
         def finish(self) -> Optional[Tuple[List[str], int]]:
-            while min(counters[m] for m in self.members) < self.seq:  # the kernel's wait for every peer's arrival flags
+            t = time.perf_counter()
+            while min(counters[m] for m in self.members) < self.seq:  # the kernel's wait for its peers' arrival flags
                 time.sleep(args.poll_us * 1e-6)
+            if self.me == mine[0]:
+                waits["finish"].append((time.perf_counter() - t) * 1e3)
             return list(self.train_set), 100 * len(self.train_set)
 
         def run(self, seq: int) -> Optional[Tuple[List[str], int]]:
             self.launch(seq)
             return self.finish()
 
-    state_seq_base = [0]
-    waits: Dict[str, List[float]] = {"vote": [], "finish": [], "handle": [], "deliver_many": []}
-
-    counts: Dict[str, int] = {}
-
     class EmuProtocol(SocketCommunicationProtocol):
         def on_message(self, msg: Any, via: Any = None) -> Any:
-            k = msg.cmd if via is None else "in:" + msg.cmd
-            counts[k] = counts.get(k, 0) + 1
-            if via is not None:
+            first = self.addr.endswith(f":{port0 + mine[0]}")
+            if first:
+                key = msg.cmd if via is None else "in:" + msg.cmd
+                counts[key] = counts.get(key, 0) + 1
+            if via is not None or not first:
                 return super().on_message(msg, via)
             t = time.perf_counter()
             try:
@@ -97,7 +114,6 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
         def plan_fused_exchange(self, state: Any, learner: Any) -> Any:
             if len(state.train_set) < 2 or args.no_fused:
                 return None
-            state_seq_base[0] = state.seq_base
             return EmuFused(state, sorted(state.train_set))
 
     class EmuLearner(NodeLearner):
@@ -149,10 +165,6 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
                 after_launch()
             time.sleep(device_s)  # the host waits for the validation result of the epoch
 
-    from p2pfl_b200.stages.base_node.vote_train_set_stage import VoteTrainSetStage
-
-    from p2pfl_b200.communication.sockets.socket_communication_protocol import SocketTransport
-
     orig_many = SocketTransport.deliver_many
 
     def timed_many(self: Any, targets: Any, env: Any) -> Any:
@@ -170,53 +182,37 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
         try:
             return orig_agg(ctx)
         finally:
-            waits["vote"].append((time.perf_counter() - t) * 1e3)
+            if ctx.state.addr.endswith(f":{port0 + mine[0]}"):
+                waits["vote"].append((time.perf_counter() - t) * 1e3)
 
     VoteTrainSetStage._aggregate_votes = staticmethod(timed_agg)  # type: ignore[method-assign]
-    orig_finish = EmuFused.finish
 
-    def timed_finish(self: Any) -> Any:
-        t = time.perf_counter()
-        try:
-            return orig_finish(self)
-        finally:
-            waits["finish"].append((time.perf_counter() - t) * 1e3)
-
-    EmuFused.finish = timed_finish  # type: ignore[method-assign]
-
-    node = Node(None, None, address=f"127.0.0.1:{port0 + rank}", learner=EmuLearner, protocol=EmuProtocol)
-    node.start()
+    nodes = [Node(None, None, address=f"127.0.0.1:{port0 + i}", learner=EmuLearner, protocol=EmuProtocol) for i in mine]
+    for nd in nodes:
+        nd.start()
     gate.wait()
-    for r in range(rank):
-        node.connect(f"127.0.0.1:{port0 + r}")
+    for i, nd in zip(mine, nodes):
+        peers = range(i) if args.topology == "full" else ([i - 1] if i > 0 else [])
+        for r in peers:
+            nd.connect(f"127.0.0.1:{port0 + r}")
     gate.wait()
-    wait_convergence([node], n - 1, wait=30, only_direct=True)
+    wait_convergence(nodes, n - 1, wait=60, only_direct=args.topology == "full")
     time.sleep(args.settle)
     gate.wait()
 
     W, K = args.warmup, args.rounds
-    marks: Dict[str, float] = {}
-    prof = None
+    marks: Dict[str, Any] = {}
+    first = nodes[0]
 
     def on_round(r: int) -> None:
-        nonlocal prof
         if r == W:
             marks["t0"] = time.perf_counter()
-            marks["tim0"] = dict(node.live_timings)  # type: ignore[assignment]
-            marks["c0"] = dict(counts)  # type: ignore[assignment]
-            if args.profile and rank == 0:
-                import cProfile
-                import threading
-
-                prof = cProfile.Profile()
-                prof.enable()
-                threading.setprofile(lambda *a: None)  # (other threads: see --profile-threads)
+            marks["tim0"] = dict(first.live_timings)
+            marks["c0"] = dict(counts)
         elif r == W + K:
-            if prof is not None:
-                prof.disable()
             marks["t1"] = time.perf_counter()
-            marks["tim1"] = dict(node.live_timings)  # type: ignore[assignment]
-            marks["c1"] = dict(counts)  # type: ignore[assignment]
+            marks["tim1"] = dict(first.live_timings)
+            marks["c1"] = dict(counts)
 
     def dump_if_stuck() -> None:
         time.sleep(args.stuck_after)
@@ -224,65 +220,63 @@ def _worker(rank: int, n: int, args: Any, port0: int, counters: Any, gate: Any, 
             return
         import traceback
 
-        st = node.state
-        lines = [f"[rank {rank}] STUCK: round {st.round} status {st.status} train_set {len(st.train_set)} "
-                 f"votes {{r: sorted(v) for r, v in st.train_set_votes.items()}} = { {r: len(v) for r, v in st.train_set_votes.items()} } "
-                 f"counters {list(counters[:n])} neighbors {len(node._communication_protocol.get_neighbors())}"]  # fmt: skip
+        lines = []
+        for nd in nodes:
+            st = nd.state
+            lines.append(f"[node {index_of(st.addr)}] STUCK: round {st.round} status {st.status} train_set {len(st.train_set)} "
+                         f"votes { {r: len(v) for r, v in st.train_set_votes.items()} } counters {list(counters[:n])} "
+                         f"neighbors {len(nd._communication_protocol.get_neighbors())}")  # fmt: skip
         for tid, frame in sys._current_frames().items():
-            name = next((t.name for t in __import__("threading").enumerate() if t.ident == tid), str(tid))
-            if "learning" in name.lower() or "gossiper" in name.lower():
-                lines.append(f"--- {name}\n" + "".join(traceback.format_stack(frame)[-6:]))
+            name = next((t.name for t in threading.enumerate() if t.ident == tid), str(tid))
+            if "learning" in name.lower():
+                lines.append(f"--- {name}\n" + "".join(traceback.format_stack(frame)[-5:]))
         sys.stderr.write("\n".join(lines) + "\n")
         sys.stderr.flush()
 
-    import threading as _th
-
-    _th.Thread(target=dump_if_stuck, daemon=True).start()
-    node.state.round_listeners = [on_round]
-    if rank == 0:
-        node.set_start_learning(rounds=W + K + 1, epochs=1)
-    deadline = time.time() + 120
-    while node.state.finished.is_set() and time.time() < deadline:
+    threading.Thread(target=dump_if_stuck, daemon=True).start()
+    first.state.round_listeners = [on_round]
+    if proc == 0:
+        first.set_start_learning(rounds=W + K + 1, epochs=1)
+    deadline = time.time() + args.stuck_after + 60
+    while first.state.finished.is_set() and time.time() < deadline:
         time.sleep(0.001)
-    node.wait_learning_finished(120)
-    res: Dict[str, Any] = {"rank": rank}
+    for nd in nodes:
+        nd.wait_learning_finished(max(1.0, deadline - time.time()))
+    res: Dict[str, Any] = {"proc": proc}
     if "t1" in marks:
         res["ms_per_round"] = (marks["t1"] - marks["t0"]) * 1e3 / K
         t0, t1 = marks["tim0"], marks["tim1"]
-        res["stages"] = {k: round((v - t0.get(k, 0.0)) * 1e3 / K, 3) for k, v in t1.items()}  # type: ignore[union-attr]
-        res["msgs_per_round"] = {k: round((v - marks["c0"].get(k, 0)) / K, 2) for k, v in marks["c1"].items()}  # type: ignore[union-attr]
-        for k, v in waits.items():
-            v = sorted(v[-(K if k in ("vote", "finish") else 7 * K):])
+        res["stages"] = {k_: round((v - t0.get(k_, 0.0)) * 1e3 / K, 3) for k_, v in t1.items()}
+        res["msgs_per_round"] = {k_: round((v - marks["c0"].get(k_, 0)) / K, 2) for k_, v in marks["c1"].items()}
+        for k_, v in waits.items():
+            v = sorted(v[-(K if k_ in ("vote", "finish") else 7 * K):])
             if v:
-                res[f"wait_{k}_ms"] = {"p50": round(v[len(v) // 2], 3), "p90": round(v[int(len(v) * 0.9)], 3), "max": round(v[-1], 3)}
-    if prof is not None:
-        import io
-        import pstats
-
-        s = io.StringIO()
-        pstats.Stats(prof, stream=s).sort_stats("tottime").print_stats(25)
-        res["profile"] = s.getvalue()
+                res[f"wait_{k_}_ms"] = {"p50": round(v[len(v) // 2], 3), "p90": round(v[int(len(v) * 0.9)], 3), "max": round(v[-1], 3)}
     out.put(res)
-    node.stop()
+    for nd in nodes:
+        nd.stop()
 
 
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--nodes", type=int, default=8)
+    ap.add_argument("--per-proc", type=int, default=1, help="nodes per process (config 4: 8 per GPU)")
+    ap.add_argument("--topology", default="full", choices=["full", "line"])
     ap.add_argument("--rounds", type=int, default=60)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--device-ms", type=float, default=2.6)
-    ap.add_argument("--port", type=int, default=41200)
+    ap.add_argument("--port", type=int, default=21200)
     ap.add_argument("--settle", type=float, default=0.0, help="seconds between the last connect and the start of learning")
     ap.add_argument("--poll-us", type=float, default=30.0, help="sleep between two polls of the emulated exchange")
-    ap.add_argument("--stuck-after", type=float, default=40.0, help="dump every rank's state if the run has not finished by then")
+    ap.add_argument("--stuck-after", type=float, default=60.0, help="dump every node's state if the run has not finished by then")
     ap.add_argument("--no-fused", action="store_true", help="exchange models through add_model messages (the host path)")
     ap.add_argument("--train-set", type=int, default=0, help="TRAIN_SET_SIZE (default: every node trains)")
     ap.add_argument("--no-advertise", action="store_true", help="A/B: do not advertise direct neighbours on change")
-    ap.add_argument("--profile", action="store_true")
+    ap.add_argument("--flood-status", action="store_true", help="A/B: flood models_ready / model_initialized network-wide")
     args = ap.parse_args()
     ctx = mp.get_context("spawn")
     n = args.nodes
+    n_proc = (n + args.per_proc - 1) // args.per_proc
 
     def steal() -> int:
         try:
@@ -293,30 +287,26 @@ def main() -> None:
 
     steal0 = steal()
     counters = ctx.Array("q", n, lock=False)
-    gate = ctx.Barrier(n)
+    gate = ctx.Barrier(n_proc)
     out = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, n, args, args.port, counters, gate, out)) for r in range(n)]
+    procs = [ctx.Process(target=_worker, args=(p, n, args, counters, gate, out)) for p in range(n_proc)]
     for p in procs:
         p.start()
-    res = [out.get(timeout=300) for _ in procs]
+    res = sorted((out.get(timeout=args.stuck_after + 240) for _ in procs), key=lambda r: r["proc"])
     for p in procs:
         p.join(30)
     ms = max(r.get("ms_per_round", float("nan")) for r in res)
+    r0 = res[0]
     line = {
-        "bench": "control_plane", "nodes": n, "rounds": args.rounds, "device_ms_emulated": args.device_ms,
+        "bench": "control_plane", "nodes": n, "per_proc": args.per_proc, "topology": args.topology,
+        "train_set": args.train_set or n, "fused": not args.no_fused, "rounds": args.rounds, "device_ms_emulated": args.device_ms,
         "ms_per_round": round(ms, 3), "host_overhead_ms": round(ms - args.device_ms, 3),
-        "stages_rank0": next(r.get("stages") for r in res if r["rank"] == 0),
-        "msgs_per_round_rank0": next(r.get("msgs_per_round") for r in res if r["rank"] == 0),
-        "waits": {r["rank"]: [r.get("wait_vote_ms", {}).get("p50"), r.get("wait_vote_ms", {}).get("p90"),
-                              r.get("wait_finish_ms", {}).get("p50"), r.get("wait_finish_ms", {}).get("p90")] for r in sorted(res, key=lambda r: r["rank"])},
-        "bundles_in_per_rank": [r.get("msgs_per_round", {}).get("bundle") for r in sorted(res, key=lambda r: r["rank"])],
-        "rank0_ms": {k: v for r in res if r["rank"] == 0 for k, v in r.items() if k.startswith("wait_")},
-        "cpus": os.cpu_count(), "steal_jiffies_whole_run": steal() - steal0, "advertise_on_change": not args.no_advertise,
+        "stages_node0": r0.get("stages"), "msgs_per_round_node0": r0.get("msgs_per_round"),
+        "node0_ms": {k: v for k, v in r0.items() if k.startswith("wait_")},
+        "cpus": os.cpu_count(), "steal_jiffies_whole_run": steal() - steal0,
+        "advertise_on_change": not args.no_advertise, "direct_round_status": not args.flood_status,
     }  # fmt: skip
     print(json.dumps(line), flush=True)
-    for r in res:
-        if "profile" in r:
-            print(r["profile"])
 
 
 if __name__ == "__main__":

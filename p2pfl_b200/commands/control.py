@@ -13,6 +13,7 @@ from typing import Any, Callable
 from p2pfl_b200.commands.command import Command
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.node_state import NodeState
+from p2pfl_b200.settings import Settings
 
 
 # value of a beat's `round` field that says "the originator speaks this framework's extensions";
@@ -150,7 +151,7 @@ class VoteTrainSetCommand(Command):
         # round) are kept until this node gets there; stale ones are dropped.  Under the state's
         # lock: the learning thread switches rounds (and prunes this table) concurrently.
         with st.changed:
-            if st.round is None or not (st.round <= round <= st.round + 3):
+            if st.round is None or not (st.round <= round <= st.round + 2 * max(1, Settings.PREVOTE_AHEAD) + 1):
                 logger.debug(st.addr, f"vote from {source} for round {round} ignored (mine: {st.round})")
                 return
             st.train_set_votes.setdefault(round, {})[source] = votes

@@ -158,7 +158,20 @@ class AddModelCommand(Command):
             logger.error(st.addr, f"unexpected error adding a model ({e!r}); stopping node")
             self._stop()
             return
-        if held:
+        if set(contributors) >= set(st.train_set) and st.train_set:
+            # whoever sends the finished aggregate of this round holds it: no need to wait for its
+            # ``models_ready`` (which travels on another thread and often arrives later) before
+            # deciding that it needs nothing from this node - without this, the last node of a line
+            # regularly sent the model straight back to the neighbour it had just got it from
+            with st.changed:
+                st.nei_status[source] = max(st.nei_status.get(source, -1), round)
+                st.changed.notify_all()
+        if held and st.addr in st.train_set:
+            # who holds whose model only steers the exchange among the round's TRAINERS (TrainStage:
+            # candidates are train-set members); a node that merely receives the finished aggregate
+            # has nothing to tell them (the reference floods this notice from every receiver,
+            # add_model_command.py:84-91: on a 64-node line with 16 trainers that is 48 useless floods
+            # per round)
             from p2pfl_b200.stages.common import announce_aggregated
 
             announce_aggregated(self._protocol, st, held)

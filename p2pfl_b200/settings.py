@@ -99,6 +99,12 @@ class Settings:
     PREVOTE: bool = True
     """Cast the ballot for round r+1 while round r trains (ballots are random and
     ``vote_train_set`` already accepts round+1), so the vote is no barrier between rounds."""
+    PREVOTE_AHEAD: int = 2
+    """How many rounds ahead ballots are cast (with ``PREVOTE``).  One round is enough when every node
+    is a hop away; on a long line a ballot needs dozens of relay hops, and the node that finishes a
+    round last also votes last, so with 1 every round still ended in a wait for its ballot.  With k,
+    a node can be at most k rounds ahead of the slowest one, so ballots arrive for up to round+2k:
+    the handler accepts that window."""
     ASYNC_BOOKKEEPING: bool = True
     """``metrics`` / ``models_aggregated`` / ``models_ready`` broadcasts leave through the
     gossiper thread instead of blocking the learning thread on N-1 round trips."""
@@ -116,6 +122,12 @@ class Settings:
     round), but over gRPC the same run got slower (2.1 -> 4.6 s per round, 8 processes on a CPU-only
     box): the flooded copies ride in bundles between neighbours, the direct ones are 240 extra
     channels and one RPC each.  Off by default."""
+    DIRECT_ROUND_STATUS: bool = True
+    """``models_ready`` (this node holds round r's aggregate) is only ever read for DIRECT neighbours
+    (who still needs the model diffused to it: GossipModelStage, reference gossip_model_stage.py:85-106),
+    yet the reference floods it through the whole network.  True: it is sent with ttl 1.  On a line of
+    64 nodes that is 126 deliveries per round instead of 4032 - the same order as the ballots, which do
+    have to reach everybody."""
     BUNDLE_LINGER: float = 0.02
     """Longest a lazily queued broadcast waits for company before it is sent on its own."""
     NVTX_RANGES: bool = os.environ.get("P2PFL_NVTX", "0") not in ("", "0")

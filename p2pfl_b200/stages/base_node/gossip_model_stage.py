@@ -39,12 +39,19 @@ class GossipModelStage(Stage):
         contributors = agg.get_aggregated_models()
         # after a complete fused exchange nobody waits for this round's models_ready: it may ride
         # with the next round's metrics / pre-vote bundle
+        # ... provided every direct neighbour is such a trainer: a neighbour outside the train set waits
+        # for this notice in its own diffusion loop (it would offer the model to this node otherwise)
+        train_set = set(st.train_set)
         lazy = (
             getattr(st, "fused_complete_round", None) == st.round
             and st.total_rounds is not None
             and st.round + 1 < st.total_rounds
+            and all(n in train_set for n in proto.get_neighbors(only_direct=True))
         )
-        send_async(proto, proto.build_msg("models_ready", [], round=st.round), lazy)
+        ready = proto.build_msg("models_ready", [], round=st.round)
+        if Settings.DIRECT_ROUND_STATUS:
+            ready.ttl = 1  # only direct neighbours ever look at it (candidates() / pending() below)
+        send_async(proto, ready, lazy)
         t1 = time.time()
         GossipModelStage._diffuse(ctx, params, contributors, t1)
         ctx.timings["aggregate"] = ctx.timings.get("aggregate", 0.0) + t1 - t0

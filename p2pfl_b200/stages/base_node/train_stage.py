@@ -129,13 +129,19 @@ class TrainStage(Stage):
 
     @staticmethod
     def prevote(ctx: LearningContext) -> None:
-        """Cast next round's ballot now, so that it travels while this round trains."""
+        """Cast the ballots of the next ``PREVOTE_AHEAD`` rounds now (those not cast yet), so that they
+        travel while this round trains."""
+        from p2pfl_b200.settings import Settings
+
         st = ctx.state
         if not TrainStage.will_prevote(ctx):
             return
         from p2pfl_b200.stages.base_node.vote_train_set_stage import VoteTrainSetStage
 
-        VoteTrainSetStage.cast_ballot(ctx, st.round + 1, background=True)
+        for ahead in range(1, max(1, Settings.PREVOTE_AHEAD) + 1):
+            if st.round is None or st.total_rounds is None or st.round + ahead >= st.total_rounds:
+                break
+            VoteTrainSetStage.cast_ballot(ctx, st.round + ahead, background=True)
 
     @staticmethod
     def replay_early_models(ctx: LearningContext) -> None:
