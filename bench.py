@@ -304,6 +304,12 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         else:
             from p2pfl_b200.communication.nvlink import NvlinkSocketProtocol as Proto
 
+        if args.exchange == "nccl":
+            # baseline arm: same node / stages / learner / control plane, the round's exchange
+            # done by NCCL all-gather + average instead of the fused push+FedAvg kernel
+            from p2pfl_b200.communication.nvlink.collective_exchange import with_collective_exchange
+
+            Proto = with_collective_exchange(Proto)
         port0 = int(os.environ.get("MASTER_PORT", "29500")) + 211
         address = f"127.0.0.1:{port0 + rank}"
     else:
@@ -459,6 +465,8 @@ def run_ours(args: argparse.Namespace) -> Dict[str, Any]:
         "arm": {
             "control_plane": "in-memory (1 node)" if world == 1 else f"{args.control} loopback + NVLink device data plane",
             "timing": "CUDA events on the learner's stream, max over ranks",
+            "exchange": "NCCL all-gather + average (library baseline)" if (world > 1 and args.exchange == "nccl")
+                        else "fused push+FedAvg kernel over NVLink peer memory" if world > 1 else "none (1 node)",
             "learner": ("TorchLearner: eager PyTorch" if args.eager else "GraphedTorchLearner: PyTorch operators, one CUDA-graph replay per step")
                        + ", strict fp32 (TF32 off), library GEMMs - the precision-parity arm; gpu_launches counts this library's kernels only" if fp32
                        else "B200Learner: whole-epoch tcgen05 cluster kernel, bf16 operands, fp32 accumulate / master weights / Adam",
@@ -541,6 +549,8 @@ def main() -> None:
                     help="own arm: bf16 = the fused learner (product path); fp32 = the eager fp32 learner (precision parity with the reference)")
     ap.add_argument("--control", default="socket", choices=["socket", "grpc"],
                     help="control-plane transport between the ranks (the data plane is NVLink either way)")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="own arm, N>1: fused = the product's exchange kernel; nccl = all-gather + average baseline")
     ap.add_argument("--eager", action="store_true", help="with --dtype fp32: the plain eager learner instead of the graphed one")
     ap.add_argument("--ref-budget", type=float, default=600.0,
                     help="reference arm: seconds after which the timed region is closed at the last finished round")
