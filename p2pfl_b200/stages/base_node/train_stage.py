@@ -138,7 +138,13 @@ class TrainStage(Stage):
             return
         from p2pfl_b200.stages.base_node.vote_train_set_stage import VoteTrainSetStage
 
-        for ahead in range(1, max(1, Settings.PREVOTE_AHEAD) + 1):
+        # further than one round ahead only among nodes of this framework: a reference node files
+        # ballots for its current and next round and drops later ones (vote_train_set_command.py:54-67)
+        proto = ctx.communication_protocol
+        extended = getattr(proto, "_extended", None)
+        known = proto.get_neighbors(only_direct=False)
+        ours_only = extended is not None and all(n in extended for n in known)
+        for ahead in range(1, (max(1, Settings.PREVOTE_AHEAD) if ours_only else 1) + 1):
             if st.round is None or st.total_rounds is None or st.round + ahead >= st.total_rounds:
                 break
             VoteTrainSetStage.cast_ballot(ctx, st.round + ahead, background=True)

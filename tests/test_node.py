@@ -294,3 +294,44 @@ def test_early_models_aggregated_notice_is_kept_for_the_next_round():
     assert st.round == 1 and st.models_aggregated == {"peer": ["c"]}
     st.increase_round()
     assert st.models_aggregated == {}
+
+
+def test_prevote_goes_two_rounds_ahead_only_among_extended_nodes():
+    """Ballots are cast ``PREVOTE_AHEAD`` rounds ahead when every known node is one of this framework;
+    a reference node files ballots for its current and next round only, so with one in the network the
+    pre-vote stays one round ahead.  The handler's window covers what can arrive."""
+    from types import SimpleNamespace
+
+    from p2pfl_b200.commands.control import VoteTrainSetCommand
+    from p2pfl_b200.node_state import NodeState
+    from p2pfl_b200.stages.base_node.train_stage import TrainStage
+
+    Settings.PREVOTE, Settings.VOTE_EVERY_ROUND, Settings.PREVOTE_AHEAD = True, True, 2
+    for extended, want in (({"b", "c"}, [1, 2]), ({"b"}, [1])):
+        st = NodeState("a")
+        st.set_experiment("exp", 10)
+        sent = []
+        proto = SimpleNamespace(
+            _extended=extended,
+            get_neighbors=lambda only_direct=False: {"b": None, "c": None},
+            build_msg=lambda cmd, args=None, round=None: SimpleNamespace(cmd=cmd, args=args, round=round),
+            broadcast_async=lambda msg, lazy=False: sent.append(msg.round),
+            broadcast=lambda msg: sent.append(msg.round),
+        )
+        ctx = SimpleNamespace(state=st, communication_protocol=proto)
+        TrainStage.prevote(ctx)
+        assert sent == want and sorted(st.train_set_votes) == want
+        TrainStage.prevote(ctx)  # idempotent
+        assert sent == want
+        st.round = 8  # rounds 9 is the last one: nothing beyond it is voted for
+        sent.clear()
+        TrainStage.prevote(ctx)
+        assert sent == [9]
+    # window of the handler: a node can be PREVOTE_AHEAD rounds ahead and votes that far ahead of itself
+    st = NodeState("a")
+    st.set_experiment("exp", 20)
+    st.round = 3
+    cmd = VoteTrainSetCommand(st)
+    for r in (2, 3, 7, 8, 9):
+        cmd.execute("b", r, "a", "5")
+    assert sorted(st.train_set_votes) == [3, 7, 8]
