@@ -252,6 +252,11 @@ def _worker(proc: int, n: int, args: Any, counters: Any, gate: Any, out: Any) ->
             v = sorted(v[-(K if k_ in ("vote", "finish") else 7 * K):])
             if v:
                 res[f"wait_{k_}_ms"] = {"p50": round(v[len(v) // 2], 3), "p90": round(v[int(len(v) * 0.9)], 3), "max": round(v[-1], 3)}
+    from p2pfl_b200.utils import lockcheck
+
+    if lockcheck.enabled():  # P2PFL_LOCKCHECK=1: cycles in the lock-order graph seen during the run
+        res["lock_order_violations"] = [list(v) for v in lockcheck.violations()]
+        res["lock_order_edges"] = sum(len(v) for v in lockcheck.edges().values())
     out.put(res)
     for nd in nodes:
         nd.stop()
@@ -306,6 +311,9 @@ def main() -> None:
         "cpus": os.cpu_count(), "steal_jiffies_whole_run": steal() - steal0,
         "advertise_on_change": not args.no_advertise, "direct_round_status": not args.flood_status,
     }  # fmt: skip
+    if any("lock_order_violations" in r for r in res):
+        line["lock_order_violations"] = [v for r in res for v in r.get("lock_order_violations", [])]
+        line["lock_order_edges"] = max(r.get("lock_order_edges", 0) for r in res)
     print(json.dumps(line), flush=True)
 
 
