@@ -187,6 +187,34 @@ def _worker(proc: int, n: int, args: Any, counters: Any, gate: Any, out: Any) ->
 
     VoteTrainSetStage._aggregate_votes = staticmethod(timed_agg)  # type: ignore[method-assign]
 
+    timeline: List[Any] = []
+    if args.timeline:  # stage entries / exits and model sends of this process's first node, for the last rounds
+        from p2pfl_b200.stages.base_node import gossip_model_stage, round_finished_stage, train_stage, wait_agg_models_stage
+
+        for cls in (train_stage.TrainStage, wait_agg_models_stage.WaitAggregatedModelsStage, gossip_model_stage.GossipModelStage,
+                    round_finished_stage.RoundFinishedStage, VoteTrainSetStage):  # fmt: skip
+            def wrap(cls: Any = cls) -> None:
+                inner = cls.execute
+
+                def execute(ctx: Any) -> Any:
+                    t = time.time()
+                    try:
+                        return inner(ctx)
+                    finally:
+                        if ctx.state.addr.endswith(f":{port0 + mine[0]}"):
+                            timeline.append((round(t * 1e3 % 1e6, 1), index_of(ctx.state.addr), ctx.state.round, cls.__name__, round((time.time() - t) * 1e3, 1)))
+
+                cls.execute = staticmethod(execute)
+
+            wrap()
+        orig_on_weights = EmuProtocol.on_weights
+
+        def on_weights(self: Any, w: Any) -> Any:
+            if self.addr.endswith(f":{port0 + mine[0]}"):
+                timeline.append((round(time.time() * 1e3 % 1e6, 1), index_of(self.addr), w.round, f"<- {w.cmd} from {index_of(w.source)}", 0))
+            return orig_on_weights(self, w)
+
+        EmuProtocol.on_weights = on_weights  # type: ignore[method-assign]
     nodes = [Node(None, None, address=f"127.0.0.1:{port0 + i}", learner=EmuLearner, protocol=EmuProtocol) for i in mine]
     for nd in nodes:
         nd.start()
@@ -257,6 +285,8 @@ def _worker(proc: int, n: int, args: Any, counters: Any, gate: Any, out: Any) ->
     if lockcheck.enabled():  # P2PFL_LOCKCHECK=1: cycles in the lock-order graph seen during the run
         res["lock_order_violations"] = [list(v) for v in lockcheck.violations()]
         res["lock_order_edges"] = sum(len(v) for v in lockcheck.edges().values())
+    if timeline:
+        res["timeline"] = timeline[-60:]
     out.put(res)
     for nd in nodes:
         nd.stop()
@@ -274,6 +304,7 @@ def main() -> None:
     ap.add_argument("--settle", type=float, default=0.0, help="seconds between the last connect and the start of learning")
     ap.add_argument("--poll-us", type=float, default=30.0, help="sleep between two polls of the emulated exchange")
     ap.add_argument("--stuck-after", type=float, default=60.0, help="dump every node's state if the run has not finished by then")
+    ap.add_argument("--timeline", action="store_true", help="print the last stage transitions of every process's first node")
     ap.add_argument("--no-fused", action="store_true", help="exchange models through add_model messages (the host path)")
     ap.add_argument("--train-set", type=int, default=0, help="TRAIN_SET_SIZE (default: every node trains)")
     ap.add_argument("--no-advertise", action="store_true", help="A/B: do not advertise direct neighbours on change")
@@ -315,6 +346,9 @@ def main() -> None:
         line["lock_order_violations"] = [v for r in res for v in r.get("lock_order_violations", [])]
         line["lock_order_edges"] = max(r.get("lock_order_edges", 0) for r in res)
     print(json.dumps(line), flush=True)
+    if args.timeline:
+        for e in sorted((e for r in res for e in r.get("timeline", [])), key=lambda e: e[0]):
+            print(e)
 
 
 if __name__ == "__main__":

@@ -143,6 +143,17 @@ class AddModelCommand(Command):
                 )
                 logger.debug(st.addr, f"add_model from {source} stashed: train set not armed yet")
                 return
+        if set(contributors) >= set(st.train_set) and st.train_set:
+            # whoever sends the finished aggregate of this round holds it: no need to wait for its
+            # ``models_ready`` (which travels on another thread and often arrives later) before
+            # deciding that it needs nothing from this node - without this, the last node of a line
+            # regularly sent the model straight back to the neighbour it had just got it from
+            with st.changed:
+                st.nei_status[source] = max(st.nei_status.get(source, -1), round)
+                st.changed.notify_all()
+        if not self._aggregator.would_accept(list(contributors)):
+            logger.debug(st.addr, f"add_model from {source} not needed (contributors {contributors}); not decoded")
+            return
         try:
             model = _decode_from(learner, weights, source)
             learner.check_parameters(model)
@@ -158,14 +169,6 @@ class AddModelCommand(Command):
             logger.error(st.addr, f"unexpected error adding a model ({e!r}); stopping node")
             self._stop()
             return
-        if set(contributors) >= set(st.train_set) and st.train_set:
-            # whoever sends the finished aggregate of this round holds it: no need to wait for its
-            # ``models_ready`` (which travels on another thread and often arrives later) before
-            # deciding that it needs nothing from this node - without this, the last node of a line
-            # regularly sent the model straight back to the neighbour it had just got it from
-            with st.changed:
-                st.nei_status[source] = max(st.nei_status.get(source, -1), round)
-                st.changed.notify_all()
         if held and st.addr in st.train_set:
             # who holds whose model only steers the exchange among the round's TRAINERS (TrainStage:
             # candidates are train-set members); a node that merely receives the finished aggregate

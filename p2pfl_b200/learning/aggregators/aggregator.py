@@ -137,6 +137,23 @@ class Aggregator:
                     pass
         return now_held
 
+    def would_accept(self, contributors: List[str]) -> bool:
+        """``add_model``'s admission rules without the model: lets a receiver skip decoding (a pull over
+        NVLink on the device path) a copy it has no use for - in a mesh every holder of the aggregate
+        offers it to every neighbour that has not announced ``models_ready`` yet, so a waiting node is
+        offered the same model by most of its neighbours within a millisecond."""
+        if not contributors:
+            return False
+        with self._lock:
+            if not self._train_set or self._done.is_set():
+                return False
+            full = set(contributors) == set(self._train_set)
+            if self._waiting:
+                return full
+            if not all(c in self._train_set for c in contributors):
+                return False
+            return full or set(self.get_aggregated_models()).isdisjoint(contributors)
+
     def remove_node(self, node: str) -> None:
         """A train-set member vanished: stop expecting its model."""
         with self._lock:

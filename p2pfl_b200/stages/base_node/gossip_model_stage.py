@@ -100,8 +100,12 @@ class GossipModelStage(Stage):
             return proto.build_weights("add_model", st.round, cache[0], contributors, 1)
 
         def wait_fn(t: float) -> None:
+            # "nobody left to serve" counts as well: the last ``models_ready`` often arrives WHILE the
+            # models of this tick are being sent, i.e. before this snapshot is taken - waiting for a
+            # further change then slept a whole gossip period (50 ms of a 55 ms round in
+            # bench/control_plane_bench.py --train-set 4)
             snap = pending()
-            st.wait_for(lambda: ctx.early_stopping_fn() or pending() != snap, t)
+            st.wait_for(lambda: ctx.early_stopping_fn() or not candidates() or pending() != snap, t)
 
         # Non-trainers are served at once; trainers only once the grace period is
         # over and they still have not announced ``models_ready``.
