@@ -115,4 +115,4 @@ class GossipModelStage(Stage):
             if not pending() or left <= 0:
                 break
             snap = pending()
-            st.wait_for(lambda: ctx.early_stopping_fn() or pending() != snap, left)
+            st.wait_for(lambda: ctx.early_stopping_fn() or not pending() or pending() != snap, left)
