@@ -220,7 +220,9 @@ def _worker(proc: int, n: int, args: Any, counters: Any, gate: Any, out: Any) ->
         nd.start()
     gate.wait()
     for i, nd in zip(mine, nodes):
-        peers = range(i) if args.topology == "full" else ([i - 1] if i > 0 else [])
+        peers = list(range(i)) if args.topology == "full" else ([i - 1] if i > 0 else [])
+        if args.topology == "ring" and i == n - 1 and n > 2:
+            peers.append(0)
         for r in peers:
             nd.connect(f"127.0.0.1:{port0 + r}")
     gate.wait()
@@ -296,7 +298,7 @@ def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--nodes", type=int, default=8)
     ap.add_argument("--per-proc", type=int, default=1, help="nodes per process (config 4: 8 per GPU)")
-    ap.add_argument("--topology", default="full", choices=["full", "line"])
+    ap.add_argument("--topology", default="full", choices=["full", "line", "ring"])
     ap.add_argument("--rounds", type=int, default=60)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--device-ms", type=float, default=2.6)
