@@ -335,3 +335,33 @@ def test_prevote_goes_two_rounds_ahead_only_among_extended_nodes():
     for r in (2, 3, 7, 8, 9):
         cmd.execute("b", r, "a", "5")
     assert sorted(st.train_set_votes) == [3, 7, 8]
+
+
+def test_would_accept_agrees_with_add_model():
+    """``Aggregator.would_accept`` (the check that lets a receiver skip decoding / pulling a model it has
+    no use for) must answer exactly what ``add_model`` would then do, for any sequence of offers."""
+    import copy
+
+    from hypothesis import given, settings
+    from hypothesis import strategies as st_
+
+    from p2pfl_b200.learning.aggregators.fedavg import FedAvg
+
+    names = ["a", "b", "c", "d", "e"]
+    offers = st_.lists(st_.lists(st_.sampled_from(names + ["x"]), min_size=0, max_size=5, unique=True), min_size=1, max_size=8)
+
+    @settings(max_examples=200, deadline=None)
+    @given(train=st_.lists(st_.sampled_from(names), min_size=0, max_size=5, unique=True), waiting=st_.booleans(), seq=offers)
+    def check(train, waiting, seq):
+        agg = FedAvg(node_name="t")
+        if waiting:
+            agg.set_waiting_aggregated_model(train)
+        else:
+            agg.set_nodes_to_aggregate(train)
+        for contributors in seq:
+            predicted = agg.would_accept(list(contributors))
+            before = copy.copy(agg.get_aggregated_models())
+            held = agg.add_model({"w": torch.zeros(1)}, list(contributors), 1)
+            assert predicted == bool(held), (train, waiting, contributors, before, held)
+
+    check()
