@@ -23,6 +23,7 @@ from p2pfl_b200.communication.heartbeater import HEARTBEAT_CMD, Heartbeater
 from p2pfl_b200.communication.messages import Message, Weights, new_message_id
 from p2pfl_b200.communication.neighbors import Neighbors
 from p2pfl_b200.exceptions import CommunicationError, NeighborNotConnectedError
+from p2pfl_b200.management import tracer
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.settings import Settings
 from p2pfl_b200.utils.lockcheck import make_lock
@@ -279,7 +280,8 @@ class BaseProtocol(CommunicationProtocol):
                 link = self._temp_links.get(nei)
                 if link is None:
                     link = self._temp_links[nei] = self._transport.open_link(nei, False)
-            err = self._transport.deliver(nei, link, msg)
+            with tracer.span("send " + msg.cmd, self.addr, "send", to=nei):
+                err = self._transport.deliver(nei, link, msg)
             if err:
                 raise CommunicationError(f"{nei} answered with error: {err}")
         except NeighborNotConnectedError:
@@ -312,7 +314,8 @@ class BaseProtocol(CommunicationProtocol):
         targets = [(n, direct[n].link) for n in names]
         if not targets:
             return
-        results = self._transport.deliver_many(targets, msg)
+        with tracer.span("broadcast " + msg.cmd, self.addr, "send", targets=len(targets)):
+            results = self._transport.deliver_many(targets, msg)
         for (nei, _), res in zip(targets, results):
             if res is None:
                 continue
@@ -395,7 +398,9 @@ class BaseProtocol(CommunicationProtocol):
         if ext:
             bundle = self.build_msg(BUNDLE_CMD, [pack_bundled(m) for m in msgs])
             bundle.ttl = 1
-            for (nei, _), res in zip(ext, self._transport.deliver_many(ext, bundle)):
+            with tracer.span("broadcast bundle", self.addr, "send", targets=len(ext), messages=len(msgs)):
+                results = self._transport.deliver_many(ext, bundle)
+            for (nei, _), res in zip(ext, results):
                 if res is not None:
                     failed[nei] = res
         if plain:
@@ -541,7 +546,8 @@ class BaseProtocol(CommunicationProtocol):
             logger.error(self.addr, f"unknown command '{msg.cmd}' from {msg.source}")
             return f"Unknown command: {msg.cmd}"
         try:
-            cmd.execute(msg.source, msg.round, *msg.args)
+            with tracer.span(msg.cmd, self.addr, "message", source=msg.source, round=msg.round):
+                cmd.execute(msg.source, msg.round, *msg.args)
         except Exception as e:
             logger.error(self.addr, f"command '{msg.cmd}' from {msg.source} failed: {e!r}")
             return f"Error while processing command: {msg.cmd} {msg.args}: {e}"
@@ -556,7 +562,8 @@ class BaseProtocol(CommunicationProtocol):
         if cmd is None:
             return f"Unknown command: {w.cmd}"
         try:
-            cmd.execute(w.source, w.round, weights=w.weights, contributors=list(w.contributors), weight=w.weight)
+            with tracer.span(w.cmd, self.addr, "model", source=w.source, round=w.round, contributors=len(w.contributors)):
+                cmd.execute(w.source, w.round, weights=w.weights, contributors=list(w.contributors), weight=w.weight)
         except Exception as e:
             logger.error(self.addr, f"weights command '{w.cmd}' from {w.source} failed: {e!r}")
             return f"Error while processing model: {w.cmd}: {e}"

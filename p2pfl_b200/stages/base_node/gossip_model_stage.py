@@ -7,6 +7,7 @@ import time
 from typing import Any, List, Optional, Type
 
 from p2pfl_b200.exceptions import NoModelsToAggregateError
+from p2pfl_b200.management import tracer
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.settings import Settings
 from p2pfl_b200.stages.common import pack_model
@@ -54,8 +55,12 @@ class GossipModelStage(Stage):
         send_async(proto, ready, lazy)
         t1 = time.time()
         GossipModelStage._diffuse(ctx, params, contributors, t1)
+        t2 = time.time()
         ctx.timings["aggregate"] = ctx.timings.get("aggregate", 0.0) + t1 - t0
-        ctx.timings["diffuse"] = ctx.timings.get("diffuse", 0.0) + time.time() - t1
+        ctx.timings["diffuse"] = ctx.timings.get("diffuse", 0.0) + t2 - t1
+        if tracer.enabled():
+            tracer.complete("wait for the aggregate", st.addr, t0, t1, "phase", {"round": st.round})
+            tracer.complete("diffuse", st.addr, t1, t2, "phase", {"round": st.round})
         if ctx.early_stopping_fn():
             return None
         return StageFactory.get_stage("RoundFinishedStage")

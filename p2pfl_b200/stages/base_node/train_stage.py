@@ -12,6 +12,7 @@ from __future__ import annotations
 import time
 from typing import Any, List, Optional, Type
 
+from p2pfl_b200.management import tracer
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.stages.common import announce_aggregated, broadcast_metrics, evaluate_and_share, pack_model
 from p2pfl_b200.stages.stage import LearningContext, Stage
@@ -114,6 +115,11 @@ class TrainStage(Stage):
         t3 = time.time()
         for k, dt in (("evaluate", t1 - t0), ("fit", t2 - t1), ("exchange", t3 - t2)):
             ctx.timings[k] = ctx.timings.get(k, 0.0) + dt
+        if tracer.enabled():
+            how = "fused" if result is not None else "messages"
+            tracer.complete("evaluate" if handle is None else "arm + evaluate launch", st.addr, t0, t1, "phase", {"round": st.round})
+            tracer.complete("fit", st.addr, t1, t2, "phase", {"round": st.round, "pipelined": handle is not None})
+            tracer.complete("exchange", st.addr, t2, t3, "phase", {"round": st.round, "how": how})
         if ctx.early_stopping_fn():
             return None
         return StageFactory.get_stage("GossipModelStage")

@@ -10,6 +10,7 @@ from __future__ import annotations
 import time
 from typing import List, Optional, Type
 
+from p2pfl_b200.management import tracer
 from p2pfl_b200.management.logger import logger
 from p2pfl_b200.settings import Settings
 from p2pfl_b200.stages.stage import LearningContext, Stage
@@ -44,7 +45,8 @@ class StageWorkflow:
             if nvtx is not None:  # one range per stage and round, visible in nsys / ncu --nvtx
                 nvtx.range_push(f"{stage.name()}[r{ctx.state.round}]")
             try:
-                self.current_stage = stage.execute(ctx)
+                with tracer.span(stage.name(), ctx.state.addr, "stage", round=ctx.state.round):
+                    self.current_stage = stage.execute(ctx)
             finally:
                 if nvtx is not None:
                     nvtx.range_pop()
