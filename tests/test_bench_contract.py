@@ -55,3 +55,24 @@ def test_reference_arm_reports_when_the_reference_is_not_installed(tmp_path, mon
     monkeypatch.delenv("WORLD_SIZE", raising=False)
     res = bench.run_reference(bench.argparse.Namespace(steps=1, warmup=3, ref_fast=False, timeout=10.0, ref_budget=5.0))
     assert res["impl"] == "reference" and "unavailable" in res
+
+
+def test_home_device_defaults_to_local_rank(monkeypatch):
+    """One process per GPU: framework threads select the process's GPU before their first CUDA call;
+    the default comes from the launcher's LOCAL_RANK, an explicit setting wins, and without either
+    nothing is selected (several GPUs driven from one process, as in the in-process tests)."""
+    from p2pfl_b200 import ops
+
+    monkeypatch.delenv("LOCAL_RANK", raising=False)
+    ops.set_home_device(None)
+    assert ops.home_device() is None
+    monkeypatch.setenv("LOCAL_RANK", "3")
+    assert ops.home_device() == 3
+    ops.set_home_device(5)
+    try:
+        assert ops.home_device() == 5
+    finally:
+        ops.set_home_device(None)
+    monkeypatch.setenv("LOCAL_RANK", "not-a-number")
+    assert ops.home_device() is None
+    ops.thread_uses_cuda()  # no device here: must be a harmless no-op
