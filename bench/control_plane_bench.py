@@ -53,6 +53,8 @@ def _worker(proc: int, n: int, args: Any, counters: Any, gate: Any, out: Any) ->
         from p2pfl_b200.communication.protocol import BaseProtocol
 
         BaseProtocol._advertise_direct = lambda self: None  # type: ignore[method-assign]
+    if args.no_local_shortcut:  # A/B: every hop over the loopback socket, also between nodes of one process
+        Settings.SOCKET_LOCAL_SHORTCUT = False
     if args.flood_status:  # A/B: models_ready / model_initialized flooded network-wide (the reference's way)
         Settings.DIRECT_ROUND_STATUS = False
     Settings.GOSSIP_MODELS_PERIOD = 0.05
@@ -310,6 +312,7 @@ def main() -> None:
     ap.add_argument("--no-fused", action="store_true", help="exchange models through add_model messages (the host path)")
     ap.add_argument("--train-set", type=int, default=0, help="TRAIN_SET_SIZE (default: every node trains)")
     ap.add_argument("--no-advertise", action="store_true", help="A/B: do not advertise direct neighbours on change")
+    ap.add_argument("--no-local-shortcut", action="store_true", help="A/B: nodes of one process also talk over sockets")
     ap.add_argument("--flood-status", action="store_true", help="A/B: flood models_ready / model_initialized network-wide")
     args = ap.parse_args()
     ctx = mp.get_context("spawn")
@@ -342,7 +345,7 @@ def main() -> None:
         "stages_node0": r0.get("stages"), "msgs_per_round_node0": r0.get("msgs_per_round"),
         "node0_ms": {k: v for k, v in r0.items() if k.startswith("wait_")},
         "cpus": os.cpu_count(), "steal_jiffies_whole_run": steal() - steal0,
-        "advertise_on_change": not args.no_advertise, "direct_round_status": not args.flood_status,
+        "advertise_on_change": not args.no_advertise, "direct_round_status": not args.flood_status, "local_shortcut": not args.no_local_shortcut,
     }  # fmt: skip
     if any("lock_order_violations" in r for r in res):
         line["lock_order_violations"] = [v for r in res for v in r.get("lock_order_violations", [])]

@@ -122,6 +122,10 @@ class Settings:
     round), but over gRPC the same run got slower (2.1 -> 4.6 s per round, 8 processes on a CPU-only
     box): the flooded copies ride in bundles between neighbours, the direct ones are 240 extra
     channels and one RPC each.  Off by default."""
+    SOCKET_LOCAL_SHORTCUT: bool = True
+    """Socket transport: a neighbour that is a node of the SAME process is reached by a direct call into
+    its engine (as the in-memory transport does) instead of a frame over the loopback socket.  The
+    tests turn it off so that every message of theirs crosses the wire format."""
     DIRECT_ROUND_STATUS: bool = True
     """``models_ready`` (this node holds round r's aggregate) is only ever read for DIRECT neighbours
     (who still needs the model diffused to it: GossipModelStage, reference gossip_model_stage.py:85-106),
@@ -202,4 +206,5 @@ def set_test_settings() -> None:
     Settings.AGGREGATION_TIMEOUT = 60
     Settings.WAIT_HEARTBEATS_CONVERGENCE = 0.2 * Settings.HEARTBEAT_TIMEOUT
     Settings.INIT_MODEL_TIMEOUT = 30
+    Settings.SOCKET_LOCAL_SHORTCUT = False  # the suites run their nodes in one process: keep them on the wire
     Settings.LOG_LEVEL = "DEBUG"

@@ -421,3 +421,38 @@ def test_rendered_proto_is_current():
     spec.loader.exec_module(mod)
     with open(os.path.join(root, "p2pfl_b200", "communication", "grpc", "proto_schema", "wire_schema.proto")) as fh:
         assert fh.read() == mod.render()
+
+
+def test_socket_transport_reaches_nodes_of_its_own_process_directly():
+    """Several simulated nodes per process (config 4): a neighbour that lives in this process is reached
+    by a call into its engine, not over the loopback socket; a node that goes down is noticed the same
+    way, and a learning experiment over such links ends with equal models."""
+    from p2pfl_b200.communication.sockets.socket_communication_protocol import _LocalLink
+    from p2pfl_b200.learning.data import MnistFederatedDM
+    from p2pfl_b200.models import MLP
+    from p2pfl_b200.utils import check_equal_models, wait_4_results
+
+    Settings.SOCKET_LOCAL_SHORTCUT = True
+    nodes = [Node(MLP(seed=i), MnistFederatedDM(i, 3, n_train=96 * 3, n_test=32 * 3), protocol=SocketCommunicationProtocol, device="cpu") for i in range(3)]
+    for n in nodes:
+        n.start()
+    try:
+        nodes[1].connect(nodes[0].addr)
+        nodes[2].connect(nodes[1].addr)  # a line: 0 - 1 - 2
+        wait_convergence(nodes, 2, only_direct=False)
+        for n in nodes:
+            links = [e.link for e in n._communication_protocol.get_neighbors(only_direct=True).values()]
+            assert links and all(isinstance(l, _LocalLink) for l in links), links
+        nodes[0].set_start_learning(rounds=2, epochs=1)
+        wait_4_results(nodes)
+        check_equal_models(nodes)
+        # a node that stops is evicted by the next send, as over the wire
+        nodes[2]._communication_protocol._server.stop()
+        p1 = nodes[1]._communication_protocol
+        deadline = time.time() + 10
+        while nodes[2].addr in p1.get_neighbors(only_direct=True) and time.time() < deadline:
+            p1.broadcast(p1.build_msg("beat", [str(time.time())]))
+            time.sleep(0.05)
+        assert nodes[2].addr not in p1.get_neighbors(only_direct=True)
+    finally:
+        _stop(nodes)
