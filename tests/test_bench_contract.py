@@ -76,3 +76,27 @@ def test_home_device_defaults_to_local_rank(monkeypatch):
     monkeypatch.setenv("LOCAL_RANK", "not-a-number")
     assert ops.home_device() is None
     ops.thread_uses_cuda()  # no device here: must be a harmless no-op
+
+
+def test_control_plane_harness_runs_a_mixed_line():
+    """bench/control_plane_bench.py end to end, small: 6 nodes on a line, two per process (links inside a
+    process are direct calls, links between processes sockets), 3 voted trainers, the emulated fused
+    exchange and the pipelined round."""
+    import math
+    import socket
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    port = 20000 + port % 10000  # below the ephemeral range: the harness uses port .. port + nodes
+    out = subprocess.run(
+        [sys.executable, os.path.join(ROOT, "bench", "control_plane_bench.py"), "--nodes", "6", "--per-proc", "2", "--topology", "line",
+         "--train-set", "3", "--rounds", "6", "--warmup", "2", "--device-ms", "1.0", "--port", str(port), "--stuck-after", "90"],
+        capture_output=True, text=True, timeout=400,
+    )  # fmt: skip
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "STUCK" not in out.stderr and "Traceback" not in out.stderr, out.stderr[-2000:]
+    line = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+    assert line["nodes"] == 6 and line["per_proc"] == 2 and line["local_shortcut"] is True
+    assert math.isfinite(line["ms_per_round"]) and line["ms_per_round"] > 1.0
+    assert line["msgs_per_round_node0"].get("in:vote_train_set", 0) > 0
